@@ -1,0 +1,178 @@
+/*
+ * rampack_b200.h — C ABI of the B200-native Monte Carlo sweep (librampack_b200.so).
+ *
+ * The reference (PKua007/rampack) has no FFI layer: its boundary for this path is the C++ contract
+ * Simulation -> Packing -> Interaction (src/core/Packing.h:143-390, src/core/Interaction.h:28-130).  This header is
+ * the C ABI a maintainer binds *underneath* the reference's `Packing`.  Every entry point names
+ * the reference method it replaces.  Plain pointers and sizes only; no C++/torch types cross the boundary.
+ *
+ * Conventions
+ *   - all functions return an rp_status; rp_last_error(h) gives the message (thread-local when h == NULL)
+ *   - one host thread per handle; all device work of a handle runs on the handle's CUDA stream
+ *   - shapes cross the boundary in the reference's `Shape` layout (src/core/Shape.h:20-24):
+ *     12 doubles per particle = position[3] followed by the row-major orientation matrix[9]
+ *   - box matrices are row-major 3x3, COLUMNS are the box vectors (src/core/TriclinicBox.h:20-23)
+ *   - "+inf" / "-inf" return conventions of tryMove / tryScaling are kept (src/core/Packing.h:306-352)
+ *   - there is no CPU fallback: every compute entry point fails with RP_ERR_CUDA when no device is usable
+ */
+#ifndef RAMPACK_B200_H
+#define RAMPACK_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rp_handle rp_handle;
+
+typedef enum rp_status {
+    RP_OK = 0,
+    RP_ERR_PRECONDITION = 1,   /* reference: PreconditionException from Expects() (src/utils/Exceptions.h:19-66) */
+    RP_ERR_CUDA = 2,           /* CUDA runtime failure or no usable device */
+    RP_ERR_STATE = 3,          /* reference: std::runtime_error (e.g. un-cached overlap count, Packing.cpp:1059) */
+    RP_ERR_UNSUPPORTED = 4,    /* interaction / mode not implemented on the device yet */
+    RP_ERR_CAPACITY = 5        /* a device-side buffer bound was exceeded (reported, never silently truncated) */
+} rp_status;
+
+/* Hard part of the interaction: replaces Interaction::overlapBetween of the named ShapeTraits */
+typedef enum rp_hard_kind {
+    RP_HARD_NONE = 0,
+    RP_HARD_SPHERE = 1,              /* SphereTraits::HardInteraction        (src/core/shapes/SphereTraits.cpp:56-75) */
+    RP_HARD_SPHEROCYLINDER = 2,      /* SpherocylinderTraits                 (src/core/shapes/SpherocylinderTraits.cpp:28-73) */
+    RP_HARD_POLYSPHERE = 3,          /* PolysphereTraits::HardInteraction    (src/core/shapes/PolysphereTraits.cpp:97-136) */
+    RP_HARD_POLYSPHEROCYLINDER = 4   /* PolyspherocylinderTraits             (src/core/shapes/PolyspherocylinderTraits.cpp:109-170) */
+} rp_hard_kind;
+
+/* Soft part: replaces CentralInteraction::calculateEnergyBetween (src/core/interactions/CentralInteraction.h:58-67) */
+typedef enum rp_soft_kind {
+    RP_SOFT_NONE = 0,
+    RP_SOFT_LJ = 1,    /* LennardJonesInteraction.cpp:8-13           range 3*sigma            */
+    RP_SOFT_WCA = 2,   /* RepulsiveLennardJonesInteraction.cpp:8-16  range 2^(1/6)*sigma      */
+    RP_SOFT_SIC = 3    /* SquareInverseCoreInteraction.cpp:13-15     range sigma              */
+} rp_soft_kind;
+
+#define RP_MAX_CENTRES 16
+
+/*
+ * POD description of an Interaction (the reference hides these parameters behind a vtable; a `describe()` on the
+ * host ShapeTraits emits this — INTEGRATION.md).  Semantics of CompoundInteraction (CompoundInteraction.cpp:5-66)
+ * are expressed by setting both a hard and a soft kind.
+ */
+typedef struct rp_interaction_desc {
+    int32_t hard_kind;                 /* rp_hard_kind */
+    int32_t soft_kind;                 /* rp_soft_kind */
+    double radius;                     /* sphere / spherocylinder radius */
+    double length;                     /* spherocylinder axis length (cap centre to cap centre) */
+    double epsilon;                    /* soft: energy scale */
+    double sigma;                      /* soft: length scale */
+    int32_t n_centres;                 /* Interaction::getInteractionCentres().size(); 0 = one centre in the origin */
+    int32_t reserved;
+    double centres[RP_MAX_CENTRES][3];         /* body-frame centre positions */
+    double centre_radius[RP_MAX_CENTRES];      /* polysphere bead radius / polyspherocylinder radius */
+    double centre_half_axis[RP_MAX_CENTRES][3];/* polyspherocylinder body-frame half axis */
+} rp_interaction_desc;
+
+typedef struct rp_config {
+    int32_t device;        /* CUDA device ordinal */
+    int32_t reserved;
+    uint64_t seed;         /* Philox key for rp_sweep (Simulation's `seed`, src/core/Simulation.cpp:66-68) */
+    void *cuda_stream;     /* cudaStream_t to run on, or NULL for a private stream */
+} rp_config;
+
+/* Geometry of the neighbour grid — NeighbourGrid::getCellDivisions (src/core/NeighbourGrid.cpp:372-374) */
+typedef struct rp_grid_info {
+    int32_t has_grid;            /* 0: reference would run without NG (Packing.cpp:868-881) */
+    int32_t cell_divisions[3];   /* real cells per axis (without the 2 ghost layers) */
+    double cell_size;            /* the requested cell size (Packing.cpp:862-866) */
+    uint64_t num_centres;        /* entries binned */
+    uint32_t max_cell_population;
+    uint32_t reserved;
+} rp_grid_info;
+
+/* One explicit trial move — the arguments of Packing::tryTranslation / tryRotation / tryMove (Packing.cpp:84-164) */
+typedef enum rp_move_kind { RP_MOVE_TRANSLATION = 0, RP_MOVE_ROTATION = 1, RP_MOVE_ROTOTRANSLATION = 2 } rp_move_kind;
+
+typedef struct rp_move {
+    uint64_t particle;       /* particleIdx */
+    int32_t kind;            /* rp_move_kind */
+    int32_t reserved;
+    double translation[3];
+    double rotation[9];      /* row-major rotation matrix, applied as R * orientation (Shape.cpp:14-16) */
+} rp_move;
+
+/* Sampler description for a bulk sweep — MoveSampler semantics (src/core/move_samplers/*.cpp) */
+typedef struct rp_sweep_params {
+    int32_t kind;                 /* rp_move_kind: translation / rotation / rototranslation sampler */
+    int32_t reserved;
+    double translation_step;      /* already clamped by the caller to min box height / 2 (TranslationSampler.cpp:20-37) */
+    double rotation_step;         /* already clamped to pi (RototranslationSampler.cpp:33) */
+    double temperature;           /* Metropolis: u <= exp(-dE/T) (Simulation.cpp:483) */
+    uint64_t cycle;               /* cycle number: part of the Philox counter, makes runs reproducible */
+} rp_sweep_params;
+
+typedef struct rp_sweep_counters {
+    uint64_t attempted;           /* trial moves attempted in this call (== N, Simulation.cpp:431-437) */
+    uint64_t accepted;
+    uint64_t rejected_domain;     /* rejected because the mass centre left the active region (Packing.cpp:95-96) */
+    uint64_t rejected_overlap;
+    uint64_t sub_sweeps;          /* checkerboard colours run */
+    uint64_t kernel_launches;     /* device kernels launched by this call */
+} rp_sweep_counters;
+
+/* One explicit pair for the verdict/energy parity harness — arguments of Interaction::overlapBetween */
+typedef struct rp_pair {
+    double pos1[3]; double orientation1[9]; uint64_t idx1;
+    double pos2[3]; double orientation2[9]; uint64_t idx2;
+    double translation[3];        /* BoundaryConditions::getTranslation result (HardcodedTranslation, Packing.cpp:23-43) */
+} rp_pair;
+
+/* ---- lifetime: replaces Packing ctor / dtor (src/core/Packing.cpp:46-65) ---- */
+rp_status rp_create(const rp_config *config, rp_handle **out);
+void rp_destroy(rp_handle *h);
+const char *rp_last_error(const rp_handle *h);
+const char *rp_version(void);
+
+/* ---- state: Packing::reset / setupForInteraction / begin..end (Packing.cpp:67-82, 931-950) ---- */
+rp_status rp_set_interaction(rp_handle *h, const rp_interaction_desc *desc);
+rp_status rp_upload(rp_handle *h, const double box[9], const double *shapes /* N x 12 */, uint64_t n);
+rp_status rp_download(rp_handle *h, double box_out[9], double *shapes_out /* N x 12 */, uint64_t n);
+rp_status rp_size(const rp_handle *h, uint64_t *n_out);
+
+/* ---- neighbour grid: Packing::rebuildNeighbourGrid (Packing.cpp:858-929), NeighbourGrid::positionToCellNo ---- */
+rp_status rp_rebuild_grid(rp_handle *h);
+rp_status rp_grid_info_get(rp_handle *h, rp_grid_info *out);
+/* cell number of every interaction centre, in the reference's numbering incl. ghost layers (NeighbourGrid.cpp:13-34) */
+rp_status rp_cell_numbers(rp_handle *h, uint64_t *cell_no_out /* num_centres */);
+
+/* ---- full-system recount: Packing::countTotalOverlaps / getTotalEnergy (Packing.cpp:519-559, 690-709) ---- */
+rp_status rp_count_total_overlaps(rp_handle *h, int early_exit, uint64_t *count_out);
+rp_status rp_total_energy(rp_handle *h, double *energy_out);
+
+/* ---- explicit moves (compatibility path): Packing::try* / accept* (Packing.cpp:84-164, 234-302) ---- */
+rp_status rp_try_move(rp_handle *h, const rp_move *move, double *dE_out);
+rp_status rp_accept_move(rp_handle *h);
+
+/* ---- box move: Packing::tryScaling / revertScaling (Packing.cpp:172-208, 363-371) ---- */
+rp_status rp_try_scaling(rp_handle *h, const double new_box[9], double *dE_out);
+rp_status rp_revert_scaling(rp_handle *h);
+
+/* ---- bulk sweep: Simulation::performMoves (Simulation.cpp:365-491) as one call per sampler per cycle ---- */
+rp_status rp_sweep(rp_handle *h, const rp_sweep_params *params, rp_sweep_counters *counters_out);
+
+/* ---- counting mode + walls: Packing::toggleOverlapCounting / getCachedNumberOfOverlaps (Packing.cpp:1049-1060) ---- */
+rp_status rp_toggle_overlap_counting(rp_handle *h, int count_overlaps);
+rp_status rp_cached_overlaps(rp_handle *h, uint64_t *count_out);
+
+/* ---- parity harness: Interaction::overlapBetween / calculateEnergyBetween on explicit pairs ---- */
+rp_status rp_pair_test_batch(rp_handle *h, const rp_pair *pairs, uint64_t n, uint8_t *verdict_out, double *energy_out);
+
+/* ---- timing hook for bench.py: device milliseconds spent inside the kernels of the last call ---- */
+rp_status rp_last_kernel_ms(rp_handle *h, double *sweep_ms, double *rebuild_ms);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* RAMPACK_B200_H */

@@ -1,0 +1,416 @@
+// ref_harness.cpp — TEST INFRASTRUCTURE ONLY.
+//
+// A thin extern "C" shim over the UNMODIFIED reference classes (compiled from the sources where they lie under
+// /root/reference by oracle/Makefile, output only into oracle/_ref/).  It lets tests/ and bench.py's cpu_baseline /
+// `--impl reference` leg call the reference's own Packing / Interaction / NeighbourGrid / Simulation through ctypes.
+// Nothing in the product path (rampack_b200/) may link or load this.
+//
+// The shim contains no algorithm of its own: every function forwards to a reference method (cited inline).
+
+#include <memory>
+#include <vector>
+#include <sstream>
+#include <cstring>
+#include <cstdint>
+#include <limits>
+
+#include "core/Packing.h"
+#include "core/PeriodicBoundaryConditions.h"
+#include "core/NeighbourGrid.h"
+#include "core/Simulation.h"
+#include "core/ObservablesCollector.h"
+#include "core/observables/NumberDensity.h"
+#include "core/shapes/SphereTraits.h"
+#include "core/shapes/SpherocylinderTraits.h"
+#include "core/shapes/PolysphereTraits.h"
+#include "core/shapes/PolyspherocylinderTraits.h"
+#include "core/interactions/LennardJonesInteraction.h"
+#include "core/interactions/RepulsiveLennardJonesInteraction.h"
+#include "core/interactions/SquareInverseCoreInteraction.h"
+#include "core/move_samplers/RototranslationSampler.h"
+#include "core/volume_scalers/TriclinicDeltaScaler.h"
+#include "core/volume_scalers/TriclinicAdapter.h"
+#include "core/volume_scalers/DeltaVolumeScaler.h"
+#include "utils/Logger.h"
+#include "utils/OMPMacros.h"
+
+#include "../include/rampack_b200.h"
+
+namespace {
+    // Same role as the anonymous HardcodedTranslation in src/core/Packing.cpp:23-43 (not exported by the reference)
+    class FixedTranslation : public BoundaryConditions {
+        Vector<3> t;
+    public:
+        explicit FixedTranslation(const Vector<3> &t) : t{t} { }
+        void setBox(const TriclinicBox &) override { }
+        [[nodiscard]] Vector<3> getCorrection(const Vector<3> &) const override { return {}; }
+        [[nodiscard]] Vector<3> getTranslation(const Vector<3> &, const Vector<3> &) const override { return t; }
+        [[nodiscard]] double getDistance2(const Vector<3> &p1, const Vector<3> &p2) const override {
+            return (p2 + t - p1).norm2();
+        }
+    };
+
+    Matrix<3, 3> mat(const double *a) { return Matrix<3, 3>(a); }
+    Vector<3> vec(const double *a) { return Vector<3>{a[0], a[1], a[2]}; }
+
+    struct Traits {
+        std::shared_ptr<ShapeTraits> traits;
+    };
+
+    std::shared_ptr<CentralInteraction> makeSoft(const rp_interaction_desc *d) {
+        switch (d->soft_kind) {
+            case RP_SOFT_LJ:  return std::make_shared<LennardJonesInteraction>(d->epsilon, d->sigma);
+            case RP_SOFT_WCA: return std::make_shared<RepulsiveLennardJonesInteraction>(d->epsilon, d->sigma);
+            case RP_SOFT_SIC: return std::make_shared<SquareInverseCoreInteraction>(d->epsilon, d->sigma);
+            default: return nullptr;
+        }
+    }
+
+    std::vector<Shape> toShapes(const double *shapes, std::uint64_t n) {
+        std::vector<Shape> out;
+        out.reserve(n);
+        for (std::uint64_t i = 0; i < n; i++)
+            out.emplace_back(vec(shapes + 12*i), mat(shapes + 12*i + 3));
+        return out;
+    }
+
+    void fromShape(const Shape &s, double *out) {
+        for (int k = 0; k < 3; k++) out[k] = s.getPosition()[k];
+        for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) out[3 + 3*r + c] = s.getOrientation()(r, c);
+    }
+}
+
+extern "C" {
+
+void *rpr_traits_create(const rp_interaction_desc *d) {
+    try {
+        auto t = new Traits;
+        auto soft = makeSoft(d);
+        switch (d->hard_kind) {
+            case RP_HARD_SPHERE:
+                t->traits = std::make_shared<SphereTraits>(d->radius);
+                break;
+            case RP_HARD_SPHEROCYLINDER:
+                t->traits = std::make_shared<SpherocylinderTraits>(d->length, d->radius);
+                break;
+            case RP_HARD_POLYSPHERE: {
+                std::vector<PolysphereTraits::SphereData> data;
+                for (int i = 0; i < d->n_centres; i++)
+                    data.emplace_back(vec(d->centres[i]), d->centre_radius[i]);
+                PolysphereTraits::PolysphereGeometry geom(std::move(data), Vector<3>{0, 0, 1}, Vector<3>{1, 0, 0});
+                t->traits = std::make_shared<PolysphereTraits>(std::move(geom));
+                break;
+            }
+            case RP_HARD_POLYSPHEROCYLINDER: {
+                std::vector<PolyspherocylinderTraits::SpherocylinderData> data;
+                for (int i = 0; i < d->n_centres; i++)
+                    data.emplace_back(vec(d->centres[i]), vec(d->centre_half_axis[i]), d->centre_radius[i]);
+                PolyspherocylinderTraits::PolyspherocylinderGeometry geom(std::move(data), Vector<3>{0, 0, 1},
+                                                                          Vector<3>{1, 0, 0});
+                t->traits = std::make_shared<PolyspherocylinderTraits>(std::move(geom));
+                break;
+            }
+            case RP_HARD_NONE: {
+                if (!soft) { delete t; return nullptr; }
+                if (d->n_centres == 0) {
+                    t->traits = std::make_shared<SphereTraits>(d->radius, soft);
+                } else {
+                    std::vector<PolysphereTraits::SphereData> data;
+                    for (int i = 0; i < d->n_centres; i++)
+                        data.emplace_back(vec(d->centres[i]), d->centre_radius[i]);
+                    PolysphereTraits::PolysphereGeometry geom(std::move(data), Vector<3>{0, 0, 1}, Vector<3>{1, 0, 0});
+                    t->traits = std::make_shared<PolysphereTraits>(std::move(geom), soft);
+                }
+                break;
+            }
+            default:
+                delete t;
+                return nullptr;
+        }
+        return t;
+    } catch (const std::exception &) {
+        return nullptr;
+    }
+}
+
+void rpr_traits_destroy(void *t) { delete static_cast<Traits *>(t); }
+
+double rpr_range_radius(void *t) { return static_cast<Traits *>(t)->traits->getInteraction().getRangeRadius(); }
+double rpr_total_range_radius(void *t) { return static_cast<Traits *>(t)->traits->getInteraction().getTotalRangeRadius(); }
+
+// Interaction::overlapBetween / calculateEnergyBetween on explicit pairs (src/core/Interaction.h:60-85)
+int rpr_pair_test_batch(void *tp, const rp_pair *pairs, std::uint64_t n, std::uint8_t *verdict, double *energy) {
+    const Interaction &inter = static_cast<Traits *>(tp)->traits->getInteraction();
+    bool hard = inter.hasHardPart(), soft = inter.hasSoftPart();
+    for (std::uint64_t i = 0; i < n; i++) {
+        const rp_pair &p = pairs[i];
+        FixedTranslation bc(vec(p.translation));
+        if (verdict)
+            verdict[i] = hard && inter.overlapBetween(vec(p.pos1), mat(p.orientation1), p.idx1,
+                                                      vec(p.pos2), mat(p.orientation2), p.idx2, bc);
+        if (energy)
+            energy[i] = soft ? inter.calculateEnergyBetween(vec(p.pos1), mat(p.orientation1), p.idx1,
+                                                            vec(p.pos2), mat(p.orientation2), p.idx2, bc) : 0;
+    }
+    return 0;
+}
+
+struct RefPacking {
+    std::unique_ptr<Packing> packing;
+    std::string error;
+};
+
+// Packing::Packing (src/core/Packing.cpp:46-54)
+void *rpr_packing_create(void *tp, const double box[9], const double *shapes, std::uint64_t n, int moveThreads,
+                         int scalingThreads)
+{
+    auto p = new RefPacking;
+    try {
+        const Interaction &inter = static_cast<Traits *>(tp)->traits->getInteraction();
+        p->packing = std::make_unique<Packing>(TriclinicBox(mat(box)), toShapes(shapes, n),
+                                               std::make_unique<PeriodicBoundaryConditions>(), inter,
+                                               moveThreads, scalingThreads);
+    } catch (const std::exception &e) {
+        p->error = e.what();
+        p->packing.reset();
+    }
+    return p;
+}
+
+int rpr_packing_ok(void *pp) { return static_cast<RefPacking *>(pp)->packing != nullptr; }
+const char *rpr_packing_error(void *pp) { return static_cast<RefPacking *>(pp)->error.c_str(); }
+void rpr_packing_destroy(void *pp) { delete static_cast<RefPacking *>(pp); }
+
+void rpr_packing_get(void *pp, double box[9], double *shapes) {
+    const Packing &pk = *static_cast<RefPacking *>(pp)->packing;
+    const auto &dim = pk.getBox().getDimensions();
+    for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) box[3*r + c] = dim(r, c);
+    for (std::size_t i = 0; i < pk.size(); i++)
+        fromShape(pk[i], shapes + 12*i);
+}
+
+int rpr_grid_divisions(void *pp, std::uint64_t out[3]) {
+    const Packing &pk = *static_cast<RefPacking *>(pp)->packing;
+    auto d = pk.getNeighbourGridCellDivisions();
+    out[0] = d[0]; out[1] = d[1]; out[2] = d[2];
+    return 0;
+}
+
+double rpr_average_neighbours(void *pp) {
+    return static_cast<RefPacking *>(pp)->packing->getAverageNumberOfNeighbours();
+}
+
+// Packing::countTotalOverlaps (src/core/Packing.cpp:519-559)
+std::uint64_t rpr_count_total_overlaps(void *pp, void *tp, int earlyExit) {
+    const Interaction &inter = static_cast<Traits *>(tp)->traits->getInteraction();
+    return static_cast<RefPacking *>(pp)->packing->countTotalOverlaps(inter, earlyExit != 0);
+}
+
+// Packing::getTotalEnergy (src/core/Packing.cpp:690-709)
+double rpr_total_energy(void *pp, void *tp) {
+    const Interaction &inter = static_cast<Traits *>(tp)->traits->getInteraction();
+    return static_cast<RefPacking *>(pp)->packing->getTotalEnergy(inter);
+}
+
+// Packing::tryTranslation / tryRotation / tryMove (src/core/Packing.cpp:84-164)
+int rpr_try_move(void *pp, void *tp, const rp_move *m, double *dE) {
+    auto *rp = static_cast<RefPacking *>(pp);
+    const Interaction &inter = static_cast<Traits *>(tp)->traits->getInteraction();
+    try {
+        switch (m->kind) {
+            case RP_MOVE_TRANSLATION:
+                *dE = rp->packing->tryTranslation(m->particle, vec(m->translation), inter);
+                break;
+            case RP_MOVE_ROTATION:
+                *dE = rp->packing->tryRotation(m->particle, mat(m->rotation), inter);
+                break;
+            default:
+                *dE = rp->packing->tryMove(m->particle, vec(m->translation), mat(m->rotation), inter);
+        }
+    } catch (const std::exception &e) {
+        rp->error = e.what();
+        return 1;
+    }
+    return 0;
+}
+
+// Packing::acceptMove (src/core/Packing.cpp:278-302) — what Simulation::tryMove always calls (Simulation.cpp:484)
+void rpr_accept_move(void *pp) { static_cast<RefPacking *>(pp)->packing->acceptMove(); }
+
+// Packing::tryScaling / revertScaling (src/core/Packing.cpp:172-208, 363-371)
+int rpr_try_scaling(void *pp, void *tp, const double newBox[9], double *dE) {
+    auto *rp = static_cast<RefPacking *>(pp);
+    const Interaction &inter = static_cast<Traits *>(tp)->traits->getInteraction();
+    try {
+        *dE = rp->packing->tryScaling(TriclinicBox(mat(newBox)), inter);
+    } catch (const std::exception &e) {
+        rp->error = e.what();
+        return 1;
+    }
+    return 0;
+}
+
+void rpr_revert_scaling(void *pp) { static_cast<RefPacking *>(pp)->packing->revertScaling(); }
+
+void rpr_toggle_overlap_counting(void *pp, void *tp, int on) {
+    const Interaction &inter = static_cast<Traits *>(tp)->traits->getInteraction();
+    static_cast<RefPacking *>(pp)->packing->toggleOverlapCounting(on != 0, inter);
+}
+
+std::uint64_t rpr_cached_overlaps(void *pp) { return static_cast<RefPacking *>(pp)->packing->getCachedNumberOfOverlaps(); }
+
+// NeighbourGrid::positionToCellNo (src/core/NeighbourGrid.cpp:13-34) on a grid built like Packing::rebuildNeighbourGrid
+int rpr_cell_numbers(const double box[9], double cellSize, const double *positions, std::uint64_t n,
+                     std::uint64_t *out, std::uint64_t divisionsOut[3])
+{
+    try {
+        NeighbourGrid ng(TriclinicBox(mat(box)), cellSize, n);
+        auto d = ng.getCellDivisions();
+        divisionsOut[0] = d[0]; divisionsOut[1] = d[1]; divisionsOut[2] = d[2];
+        for (std::uint64_t i = 0; i < n; i++)
+            out[i] = ng.positionToCellNo(vec(positions + 3*i));
+    } catch (const std::exception &) {
+        return 1;
+    }
+    return 0;
+}
+
+// PeriodicBoundaryConditions::getCorrection (src/core/PeriodicBoundaryConditions.cpp:11-22)
+void rpr_pbc_correction(const double box[9], const double pos[3], double out[3]) {
+    PeriodicBoundaryConditions bc;
+    bc.setBox(TriclinicBox(mat(box)));
+    auto c = bc.getCorrection(vec(pos));
+    out[0] = c[0]; out[1] = c[1]; out[2] = c[2];
+}
+
+// TriclinicBox heights / volume / inverse (src/core/TriclinicBox.cpp:27-51)
+void rpr_box_info(const double box[9], double heights[3], double *volume, double inverse[9]) {
+    TriclinicBox b(mat(box));
+    auto h = b.getHeights();
+    heights[0] = h[0]; heights[1] = h[1]; heights[2] = h[2];
+    *volume = b.getVolume();
+    auto inv = b.getDimensions().inverse();
+    for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) inverse[3*r + c] = inv(r, c);
+}
+
+// Matrix<3,3>::rotation (src/geometry/Matrix.tpp:437-449)
+void rpr_rotation_matrix(const double axis[3], double angle, double out[9]) {
+    auto R = Matrix<3, 3>::rotation(vec(axis), angle);
+    for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) out[3*r + c] = R(r, c);
+}
+
+struct rpr_sim_result {
+    double move_seconds;
+    double scaling_seconds;
+    double domain_decomposition_seconds;
+    double total_seconds;
+    std::uint64_t moves_attempted;
+    std::uint64_t moves_accepted;
+    std::uint64_t scalings_attempted;
+    std::uint64_t scalings_accepted;
+    double density_mean;
+    double density_error;
+    double ng_rebuild_seconds;
+    std::uint64_t cycles;
+    int threads;
+    int domains[3];
+};
+
+// Simulation::integrate (src/core/Simulation.cpp:98-199) with a rototranslation sampler and the delta-triclinic /
+// delta-V box scaler, exactly how test/validation_tests/SimulationTest.cpp drives it.
+// box_scaler: 0 = disabled (NVT), 1 = delta_v(step) via TriclinicAdapter, 2 = delta_triclinic(step, independent)
+int rpr_run_simulation(void *tp, const double box[9], const double *shapes, std::uint64_t n, std::uint64_t seed,
+                       double temperature, double pressure, double transStep, double rotStep, int boxScaler,
+                       double boxStep, const int domainDivisions[3], int threads, std::uint64_t thermCycles,
+                       std::uint64_t avgCycles, std::uint64_t avgEvery, double boxOut[9], double *shapesOut,
+                       rpr_sim_result *res, char *err, std::size_t errLen)
+{
+    try {
+        auto traits = static_cast<Traits *>(tp)->traits;
+        const Interaction &inter = traits->getInteraction();
+        std::size_t numDomains = std::size_t(domainDivisions[0]) * domainDivisions[1] * domainDivisions[2];
+        if (threads <= 0) threads = static_cast<int>(numDomains);
+        auto packing = std::make_unique<Packing>(TriclinicBox(mat(box)), toShapes(shapes, n),
+                                                 std::make_unique<PeriodicBoundaryConditions>(), inter, threads,
+                                                 threads);
+        std::unique_ptr<TriclinicBoxScaler> scaler;
+        if (boxScaler == 1)
+            scaler = std::make_unique<TriclinicAdapter>(std::make_unique<DeltaVolumeScaler>(), boxStep);
+        else if (boxScaler == 2)
+            scaler = std::make_unique<TriclinicDeltaScaler>(boxStep, true);
+
+        std::array<std::size_t, 3> dd = {std::size_t(domainDivisions[0]), std::size_t(domainDivisions[1]),
+                                         std::size_t(domainDivisions[2])};
+        std::unique_ptr<Simulation> sim;
+        if (scaler) {
+            sim = std::make_unique<Simulation>(std::move(packing), transStep, rotStep, seed, std::move(scaler), dd,
+                                               false);
+        } else {
+            Simulation::Environment env;
+            std::vector<std::shared_ptr<MoveSampler>> samplers;
+            samplers.push_back(std::make_shared<RototranslationSampler>(transStep, rotStep));
+            env.setMoveSamplers(std::move(samplers));
+            env.disableBoxScaling();
+            sim = std::make_unique<Simulation>(std::move(packing), seed, std::move(env), dd, false);
+        }
+
+        auto collector = std::make_unique<ObservablesCollector>();
+        collector->addObservable(std::make_unique<NumberDensity>(), ObservablesCollector::AVERAGING);
+        std::ostringstream loggerStream;
+        Logger logger(loggerStream);
+
+        std::size_t total = thermCycles + avgCycles;
+        sim->integrate(temperature, pressure, thermCycles, avgCycles, avgEvery == 0 ? 1 : avgEvery, total,
+                       *traits, std::move(collector), {}, logger);
+
+        res->move_seconds = sim->getMoveMicroseconds() * 1e-6;
+        res->scaling_seconds = sim->getScalingMicroseconds() * 1e-6;
+        res->domain_decomposition_seconds = sim->getDomainDecompositionMicroseconds() * 1e-6;
+        res->total_seconds = sim->getTotalMicroseconds() * 1e-6;
+        res->moves_attempted = 0;
+        res->moves_accepted = 0;
+        res->scalings_attempted = 0;
+        res->scalings_accepted = 0;
+        for (const auto &st : sim->getMovesStatistics()) {
+            if (st.groupName == "scaling") {
+                res->scalings_attempted += st.totalMoves;
+                res->scalings_accepted += st.acceptedMoves;
+            } else {
+                res->moves_attempted += st.totalMoves;
+                res->moves_accepted += st.acceptedMoves;
+            }
+        }
+        res->density_mean = 0;
+        res->density_error = 0;
+        if (avgCycles > 0) {
+            auto vals = sim->getObservablesCollector().getFlattenedAverageValues();
+            if (!vals.empty()) {
+                res->density_mean = vals.front().quantity.value;
+                res->density_error = vals.front().quantity.error;
+            }
+        }
+        const Packing &pk = sim->getPacking();
+        res->ng_rebuild_seconds = pk.getNeighbourGridRebuildMicroseconds() * 1e-6;
+        res->cycles = sim->getPerformedCycles();
+        res->threads = threads;
+        for (int i = 0; i < 3; i++) res->domains[i] = domainDivisions[i];
+
+        const auto &dim = pk.getBox().getDimensions();
+        if (boxOut)
+            for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) boxOut[3*r + c] = dim(r, c);
+        if (shapesOut)
+            for (std::size_t i = 0; i < pk.size(); i++)
+                fromShape(pk[i], shapesOut + 12*i);
+    } catch (const std::exception &e) {
+        if (err && errLen > 0) {
+            std::strncpy(err, e.what(), errLen - 1);
+            err[errLen - 1] = 0;
+        }
+        return 1;
+    }
+    return 0;
+}
+
+int rpr_omp_max_threads() { return OMP_MAXTHREADS; }
+
+}

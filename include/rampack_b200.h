@@ -105,7 +105,7 @@ typedef struct rp_move {
 /* Sampler description for a bulk sweep — MoveSampler semantics (src/core/move_samplers/*.cpp) */
 typedef struct rp_sweep_params {
     int32_t kind;                 /* rp_move_kind: translation / rotation / rototranslation sampler */
-    int32_t reserved;
+    int32_t pass;                 /* index of the sampler inside the cycle: part of the Philox counter */
     double translation_step;      /* already clamped by the caller to min box height / 2 (TranslationSampler.cpp:20-37) */
     double rotation_step;         /* already clamped to pi (RototranslationSampler.cpp:33) */
     double temperature;           /* Metropolis: u <= exp(-dE/T) (Simulation.cpp:483) */
@@ -169,7 +169,11 @@ rp_status rp_cached_overlaps(rp_handle *h, uint64_t *count_out);
 rp_status rp_pair_test_batch(rp_handle *h, const rp_pair *pairs, uint64_t n, uint8_t *verdict_out, double *energy_out);
 
 /* ---- timing hook for bench.py: device milliseconds spent inside the kernels of the last call ---- */
-rp_status rp_last_kernel_ms(rp_handle *h, double *sweep_ms, double *rebuild_ms);
+rp_status rp_last_kernel_ms(rp_handle *h, double *sweep_ms, double *sweep_grid_ms, double *rebuild_ms,
+                            double *scaling_ms);
+/* kernels launched by this handle so far (bench.py's gpu_launches) */
+rp_status rp_launch_count(rp_handle *h, uint64_t *launches_out);
+rp_status rp_synchronize(rp_handle *h);
 
 #ifdef __cplusplus
 }

@@ -24,6 +24,7 @@
 #include "core/shapes/SpherocylinderTraits.h"
 #include "core/shapes/PolysphereTraits.h"
 #include "core/shapes/PolyspherocylinderTraits.h"
+#include "core/shapes/CompoundShapeTraits.h"
 #include "core/interactions/LennardJonesInteraction.h"
 #include "core/interactions/RepulsiveLennardJonesInteraction.h"
 #include "core/interactions/SquareInverseCoreInteraction.h"
@@ -126,6 +127,21 @@ void *rpr_traits_create(const rp_interaction_desc *d) {
             default:
                 delete t;
                 return nullptr;
+        }
+        // hard + soft: the reference expresses it as CompoundShapeTraits(main = hard, aux = soft-only shape on the
+        // same centres) (src/core/shapes/CompoundShapeTraits.h:30-34, src/frontend/modes/CasinoMode.cpp:288-289)
+        if (d->hard_kind != RP_HARD_NONE && soft) {
+            std::shared_ptr<ShapeTraits> aux;
+            if (d->n_centres == 0) {
+                aux = std::make_shared<SphereTraits>(d->radius, soft);
+            } else {
+                std::vector<PolysphereTraits::SphereData> data;
+                for (int i = 0; i < d->n_centres; i++)
+                    data.emplace_back(vec(d->centres[i]), d->centre_radius[i]);
+                PolysphereTraits::PolysphereGeometry geom(std::move(data), Vector<3>{0, 0, 1}, Vector<3>{1, 0, 0});
+                aux = std::make_shared<PolysphereTraits>(std::move(geom), soft);
+            }
+            t->traits = std::make_shared<CompoundShapeTraits>(t->traits, aux);
         }
         return t;
     } catch (const std::exception &) {

@@ -1,0 +1,293 @@
+"""TEST INFRASTRUCTURE ONLY — ctypes access to oracle/_ref/librampack_ref*.so (the UNMODIFIED reference classes behind
+the extern "C" shim oracle/ref_harness.cpp) and to oracle/liboracle_port.so (the plain-C restatement).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this module.
+It deliberately does not import anything from rampack_b200/: the struct layouts are restated here from
+include/rampack_b200.h.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+RP_MAX_CENTRES = 16
+
+
+class InteractionDesc(C.Structure):
+    _fields_ = [("hard_kind", C.c_int32), ("soft_kind", C.c_int32),
+                ("radius", C.c_double), ("length", C.c_double), ("epsilon", C.c_double), ("sigma", C.c_double),
+                ("n_centres", C.c_int32), ("reserved", C.c_int32),
+                ("centres", (C.c_double * 3) * RP_MAX_CENTRES),
+                ("centre_radius", C.c_double * RP_MAX_CENTRES),
+                ("centre_half_axis", (C.c_double * 3) * RP_MAX_CENTRES)]
+
+
+class Move(C.Structure):
+    _fields_ = [("particle", C.c_uint64), ("kind", C.c_int32), ("reserved", C.c_int32),
+                ("translation", C.c_double * 3), ("rotation", C.c_double * 9)]
+
+
+class SimResult(C.Structure):
+    _fields_ = [("move_seconds", C.c_double), ("scaling_seconds", C.c_double),
+                ("domain_decomposition_seconds", C.c_double), ("total_seconds", C.c_double),
+                ("moves_attempted", C.c_uint64), ("moves_accepted", C.c_uint64),
+                ("scalings_attempted", C.c_uint64), ("scalings_accepted", C.c_uint64),
+                ("density_mean", C.c_double), ("density_error", C.c_double), ("ng_rebuild_seconds", C.c_double),
+                ("cycles", C.c_uint64), ("threads", C.c_int), ("domains", C.c_int * 3)]
+
+
+PAIR_DTYPE = np.dtype([("pos1", "<f8", 3), ("orientation1", "<f8", 9), ("idx1", "<u8"),
+                       ("pos2", "<f8", 3), ("orientation2", "<f8", 9), ("idx2", "<u8"),
+                       ("translation", "<f8", 3)])
+
+
+def copy_desc(src):
+    """Copies any ctypes struct with the rp_interaction_desc layout into this module's InteractionDesc."""
+    d = InteractionDesc()
+    C.memmove(C.byref(d), C.byref(src), C.sizeof(InteractionDesc))
+    return d
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def ref_path(native=False):
+    return os.path.join(HERE, "_ref", "librampack_ref_native.so" if native else "librampack_ref.so")
+
+
+def ensure_built():
+    """Builds oracle artefacts that can be built where we are (the port always; _ref only where /root/reference is)."""
+    subprocess.check_call(["make", "-C", HERE, "-j8", "all"], stdout=subprocess.DEVNULL)
+
+
+_libs = {}
+
+
+def load_ref(native=False):
+    key = "native" if native else "strict"
+    if key in _libs:
+        return _libs[key]
+    path = ref_path(native)
+    if not os.path.exists(path):
+        raise FileNotFoundError(f"{path} missing: run `make -C oracle ref` where /root/reference is mounted")
+    lib = C.CDLL(path)
+    V = C.c_void_p
+    dp = C.POINTER(C.c_double)
+    u64p = C.POINTER(C.c_uint64)
+    lib.rpr_traits_create.argtypes = [C.POINTER(InteractionDesc)]
+    lib.rpr_traits_create.restype = V
+    lib.rpr_traits_destroy.argtypes = [V]
+    lib.rpr_traits_destroy.restype = None
+    lib.rpr_range_radius.argtypes = [V]
+    lib.rpr_range_radius.restype = C.c_double
+    lib.rpr_total_range_radius.argtypes = [V]
+    lib.rpr_total_range_radius.restype = C.c_double
+    lib.rpr_pair_test_batch.argtypes = [V, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+    lib.rpr_packing_create.argtypes = [V, dp, dp, C.c_uint64, C.c_int, C.c_int]
+    lib.rpr_packing_create.restype = V
+    lib.rpr_packing_ok.argtypes = [V]
+    lib.rpr_packing_error.argtypes = [V]
+    lib.rpr_packing_error.restype = C.c_char_p
+    lib.rpr_packing_destroy.argtypes = [V]
+    lib.rpr_packing_destroy.restype = None
+    lib.rpr_packing_get.argtypes = [V, dp, dp]
+    lib.rpr_packing_get.restype = None
+    lib.rpr_grid_divisions.argtypes = [V, u64p]
+    lib.rpr_average_neighbours.argtypes = [V]
+    lib.rpr_average_neighbours.restype = C.c_double
+    lib.rpr_count_total_overlaps.argtypes = [V, V, C.c_int]
+    lib.rpr_count_total_overlaps.restype = C.c_uint64
+    lib.rpr_total_energy.argtypes = [V, V]
+    lib.rpr_total_energy.restype = C.c_double
+    lib.rpr_try_move.argtypes = [V, V, C.POINTER(Move), dp]
+    lib.rpr_accept_move.argtypes = [V]
+    lib.rpr_accept_move.restype = None
+    lib.rpr_try_scaling.argtypes = [V, V, dp, dp]
+    lib.rpr_revert_scaling.argtypes = [V]
+    lib.rpr_revert_scaling.restype = None
+    lib.rpr_toggle_overlap_counting.argtypes = [V, V, C.c_int]
+    lib.rpr_toggle_overlap_counting.restype = None
+    lib.rpr_cached_overlaps.argtypes = [V]
+    lib.rpr_cached_overlaps.restype = C.c_uint64
+    lib.rpr_cell_numbers.argtypes = [dp, C.c_double, dp, C.c_uint64, u64p, u64p]
+    lib.rpr_pbc_correction.argtypes = [dp, dp, dp]
+    lib.rpr_pbc_correction.restype = None
+    lib.rpr_box_info.argtypes = [dp, dp, dp, dp]
+    lib.rpr_box_info.restype = None
+    lib.rpr_rotation_matrix.argtypes = [dp, C.c_double, dp]
+    lib.rpr_rotation_matrix.restype = None
+    lib.rpr_run_simulation.argtypes = [V, dp, dp, C.c_uint64, C.c_uint64, C.c_double, C.c_double, C.c_double,
+                                       C.c_double, C.c_int, C.c_double, C.POINTER(C.c_int), C.c_int, C.c_uint64,
+                                       C.c_uint64, C.c_uint64, dp, dp, C.POINTER(SimResult), C.c_char_p, C.c_size_t]
+    lib.rpr_omp_max_threads.restype = C.c_int
+    _libs[key] = lib
+    return lib
+
+
+class RefTraits:
+    """A reference ShapeTraits/Interaction object built from an rp_interaction_desc."""
+
+    def __init__(self, desc, native=False):
+        self.lib = load_ref(native)
+        self.desc = copy_desc(desc)
+        self.ptr = self.lib.rpr_traits_create(C.byref(self.desc))
+        if not self.ptr:
+            raise ValueError("the reference rejected this interaction description")
+
+    def __del__(self):
+        if getattr(self, "ptr", None):
+            self.lib.rpr_traits_destroy(self.ptr)
+            self.ptr = None
+
+    @property
+    def range_radius(self):
+        return self.lib.rpr_range_radius(self.ptr)
+
+    @property
+    def total_range_radius(self):
+        return self.lib.rpr_total_range_radius(self.ptr)
+
+    def pair_test_batch(self, pairs, want_verdict=True, want_energy=False):
+        pairs = np.ascontiguousarray(pairs, dtype=PAIR_DTYPE)
+        n = pairs.shape[0]
+        verdict = np.zeros(n, dtype=np.uint8) if want_verdict else None
+        energy = np.zeros(n, dtype=np.float64) if want_energy else None
+        self.lib.rpr_pair_test_batch(self.ptr, pairs.ctypes.data, n,
+                                     verdict.ctypes.data if want_verdict else None,
+                                     energy.ctypes.data if want_energy else None)
+        return verdict, energy
+
+
+class RefPacking:
+    """The reference's Packing (PeriodicBoundaryConditions) driven through the shim."""
+
+    def __init__(self, traits, box, shapes, move_threads=1, scaling_threads=1):
+        self.lib = traits.lib
+        self.traits = traits
+        box = np.ascontiguousarray(box, dtype=np.float64).reshape(9)
+        shapes = np.ascontiguousarray(shapes, dtype=np.float64).reshape(-1, 12)
+        self.n = shapes.shape[0]
+        self.ptr = self.lib.rpr_packing_create(traits.ptr, _dp(box), _dp(shapes), self.n, move_threads,
+                                               scaling_threads)
+        if not self.lib.rpr_packing_ok(self.ptr):
+            msg = self.lib.rpr_packing_error(self.ptr).decode()
+            self.lib.rpr_packing_destroy(self.ptr)
+            self.ptr = None
+            raise ValueError(msg)
+
+    def __del__(self):
+        if getattr(self, "ptr", None):
+            self.lib.rpr_packing_destroy(self.ptr)
+            self.ptr = None
+
+    def get(self):
+        box = np.empty(9)
+        shapes = np.empty((self.n, 12))
+        self.lib.rpr_packing_get(self.ptr, _dp(box), _dp(shapes))
+        return box.reshape(3, 3), shapes
+
+    def grid_divisions(self):
+        out = (C.c_uint64 * 3)()
+        self.lib.rpr_grid_divisions(self.ptr, out)
+        return tuple(out)
+
+    def average_neighbours(self):
+        return self.lib.rpr_average_neighbours(self.ptr)
+
+    def count_total_overlaps(self, early_exit=False):
+        return self.lib.rpr_count_total_overlaps(self.ptr, self.traits.ptr, int(early_exit))
+
+    def total_energy(self):
+        return self.lib.rpr_total_energy(self.ptr, self.traits.ptr)
+
+    def try_move(self, particle, kind, translation=(0, 0, 0), rotation=None):
+        m = Move()
+        m.particle, m.kind = particle, kind
+        for k in range(3):
+            m.translation[k] = float(translation[k])
+        rot = np.eye(3) if rotation is None else np.asarray(rotation, dtype=np.float64)
+        for k in range(9):
+            m.rotation[k] = float(rot.reshape(9)[k])
+        v = C.c_double()
+        if self.lib.rpr_try_move(self.ptr, self.traits.ptr, C.byref(m), C.byref(v)) != 0:
+            raise ValueError(self.lib.rpr_packing_error(self.ptr).decode())
+        return v.value
+
+    def accept_move(self):
+        self.lib.rpr_accept_move(self.ptr)
+
+    def try_scaling(self, new_box):
+        nb = np.ascontiguousarray(new_box, dtype=np.float64).reshape(9)
+        v = C.c_double()
+        if self.lib.rpr_try_scaling(self.ptr, self.traits.ptr, _dp(nb), C.byref(v)) != 0:
+            raise ValueError(self.lib.rpr_packing_error(self.ptr).decode())
+        return v.value
+
+    def revert_scaling(self):
+        self.lib.rpr_revert_scaling(self.ptr)
+
+    def toggle_overlap_counting(self, on):
+        self.lib.rpr_toggle_overlap_counting(self.ptr, self.traits.ptr, int(on))
+
+    def cached_overlaps(self):
+        return self.lib.rpr_cached_overlaps(self.ptr)
+
+
+def ref_cell_numbers(box, cell_size, positions, native=False):
+    lib = load_ref(native)
+    box = np.ascontiguousarray(box, dtype=np.float64).reshape(9)
+    positions = np.ascontiguousarray(positions, dtype=np.float64).reshape(-1, 3)
+    out = np.empty(positions.shape[0], dtype=np.uint64)
+    div = (C.c_uint64 * 3)()
+    if lib.rpr_cell_numbers(_dp(box), cell_size, _dp(positions), positions.shape[0],
+                            out.ctypes.data_as(C.POINTER(C.c_uint64)), div) != 0:
+        raise ValueError("NeighbourGrid construction or positionToCellNo failed")
+    return out, tuple(div)
+
+
+def ref_box_info(box, native=False):
+    lib = load_ref(native)
+    box = np.ascontiguousarray(box, dtype=np.float64).reshape(9)
+    heights, vol, inv = np.empty(3), C.c_double(), np.empty(9)
+    lib.rpr_box_info(_dp(box), _dp(heights), C.byref(vol), _dp(inv))
+    return heights, vol.value, inv.reshape(3, 3)
+
+
+def ref_pbc_correction(box, pos, native=False):
+    lib = load_ref(native)
+    box = np.ascontiguousarray(box, dtype=np.float64).reshape(9)
+    pos = np.ascontiguousarray(pos, dtype=np.float64).reshape(3)
+    out = np.empty(3)
+    lib.rpr_pbc_correction(_dp(box), _dp(pos), _dp(out))
+    return out
+
+
+def ref_rotation_matrix(axis, angle, native=False):
+    lib = load_ref(native)
+    axis = np.ascontiguousarray(axis, dtype=np.float64).reshape(3)
+    out = np.empty(9)
+    lib.rpr_rotation_matrix(_dp(axis), angle, _dp(out))
+    return out.reshape(3, 3)
+
+
+def ref_run_simulation(traits, box, shapes, seed, temperature, pressure, trans_step, rot_step, box_scaler, box_step,
+                       domains, threads, therm_cycles, avg_cycles, avg_every=1):
+    """Simulation::integrate of the reference (rototranslation sampler; box_scaler 0 none / 1 delta_v /
+    2 delta_triclinic).  Returns (SimResult, final box, final shapes)."""
+    lib = traits.lib
+    box = np.ascontiguousarray(box, dtype=np.float64).reshape(9)
+    shapes = np.ascontiguousarray(shapes, dtype=np.float64).reshape(-1, 12)
+    n = shapes.shape[0]
+    res = SimResult()
+    box_out, shapes_out = np.empty(9), np.empty((n, 12))
+    dd = (C.c_int * 3)(*domains)
+    err = C.create_string_buffer(1024)
+    st = lib.rpr_run_simulation(traits.ptr, _dp(box), _dp(shapes), n, seed, temperature, pressure, trans_step,
+                                rot_step, box_scaler, box_step, dd, threads, therm_cycles, avg_cycles, avg_every,
+                                _dp(box_out), _dp(shapes_out), C.byref(res), err, 1024)
+    if st != 0:
+        raise RuntimeError("reference simulation failed: " + err.value.decode())
+    return res, box_out.reshape(3, 3), shapes_out

@@ -1,0 +1,278 @@
+"""ctypes binding of the C ABI in include/rampack_b200.h (librampack_b200.so).
+
+This is plumbing for tests, bench.py and the Python mirror of the reference's `Packing` (rampack_b200/packing.py).
+There is no CPU fallback: if the shared library is missing it is built with nvcc, and if that fails the import
+raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+RP_MAX_CENTRES = 16
+
+RP_OK, RP_ERR_PRECONDITION, RP_ERR_CUDA, RP_ERR_STATE, RP_ERR_UNSUPPORTED, RP_ERR_CAPACITY = range(6)
+RP_HARD_NONE, RP_HARD_SPHERE, RP_HARD_SPHEROCYLINDER, RP_HARD_POLYSPHERE, RP_HARD_POLYSPHEROCYLINDER = range(5)
+RP_SOFT_NONE, RP_SOFT_LJ, RP_SOFT_WCA, RP_SOFT_SIC = range(4)
+RP_MOVE_TRANSLATION, RP_MOVE_ROTATION, RP_MOVE_ROTOTRANSLATION = range(3)
+
+
+class InteractionDesc(C.Structure):
+    _fields_ = [("hard_kind", C.c_int32), ("soft_kind", C.c_int32),
+                ("radius", C.c_double), ("length", C.c_double), ("epsilon", C.c_double), ("sigma", C.c_double),
+                ("n_centres", C.c_int32), ("reserved", C.c_int32),
+                ("centres", (C.c_double * 3) * RP_MAX_CENTRES),
+                ("centre_radius", C.c_double * RP_MAX_CENTRES),
+                ("centre_half_axis", (C.c_double * 3) * RP_MAX_CENTRES)]
+
+
+class Config(C.Structure):
+    _fields_ = [("device", C.c_int32), ("reserved", C.c_int32), ("seed", C.c_uint64), ("cuda_stream", C.c_void_p)]
+
+
+class GridInfo(C.Structure):
+    _fields_ = [("has_grid", C.c_int32), ("cell_divisions", C.c_int32 * 3), ("cell_size", C.c_double),
+                ("num_centres", C.c_uint64), ("max_cell_population", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class Move(C.Structure):
+    _fields_ = [("particle", C.c_uint64), ("kind", C.c_int32), ("reserved", C.c_int32),
+                ("translation", C.c_double * 3), ("rotation", C.c_double * 9)]
+
+
+class SweepParams(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("pass_", C.c_int32), ("translation_step", C.c_double),
+                ("rotation_step", C.c_double), ("temperature", C.c_double), ("cycle", C.c_uint64)]
+
+
+class SweepCounters(C.Structure):
+    _fields_ = [("attempted", C.c_uint64), ("accepted", C.c_uint64), ("rejected_domain", C.c_uint64),
+                ("rejected_overlap", C.c_uint64), ("sub_sweeps", C.c_uint64), ("kernel_launches", C.c_uint64)]
+
+
+# rp_pair as a numpy structured dtype (same layout as the C struct: all members are 8 bytes wide)
+PAIR_DTYPE = np.dtype([("pos1", "<f8", 3), ("orientation1", "<f8", 9), ("idx1", "<u8"),
+                       ("pos2", "<f8", 3), ("orientation2", "<f8", 9), ("idx2", "<u8"),
+                       ("translation", "<f8", 3)])
+assert PAIR_DTYPE.itemsize == 8 * 29
+
+# every symbol include/rampack_b200.h declares (tests/test_abi.py checks the exports against the header)
+SYMBOLS = ["rp_create", "rp_destroy", "rp_last_error", "rp_version", "rp_set_interaction", "rp_upload",
+           "rp_download", "rp_size", "rp_rebuild_grid", "rp_grid_info_get", "rp_cell_numbers",
+           "rp_count_total_overlaps", "rp_total_energy", "rp_try_move", "rp_accept_move", "rp_try_scaling",
+           "rp_revert_scaling", "rp_sweep", "rp_toggle_overlap_counting", "rp_cached_overlaps",
+           "rp_pair_test_batch", "rp_last_kernel_ms", "rp_launch_count", "rp_synchronize"]
+
+_lib = None
+
+
+def library_path():
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "librampack_b200.so")
+
+
+def load():
+    """Loads (building first if needed) librampack_b200.so and declares the prototypes."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = library_path()
+    if not os.path.exists(path):
+        _build.build()
+    lib = C.CDLL(path)
+    H = C.c_void_p
+    dp = C.POINTER(C.c_double)
+    lib.rp_create.argtypes = [C.POINTER(Config), C.POINTER(H)]
+    lib.rp_destroy.argtypes = [H]
+    lib.rp_destroy.restype = None
+    lib.rp_last_error.argtypes = [H]
+    lib.rp_last_error.restype = C.c_char_p
+    lib.rp_version.restype = C.c_char_p
+    lib.rp_set_interaction.argtypes = [H, C.POINTER(InteractionDesc)]
+    lib.rp_upload.argtypes = [H, dp, dp, C.c_uint64]
+    lib.rp_download.argtypes = [H, dp, dp, C.c_uint64]
+    lib.rp_size.argtypes = [H, C.POINTER(C.c_uint64)]
+    lib.rp_rebuild_grid.argtypes = [H]
+    lib.rp_grid_info_get.argtypes = [H, C.POINTER(GridInfo)]
+    lib.rp_cell_numbers.argtypes = [H, C.POINTER(C.c_uint64)]
+    lib.rp_count_total_overlaps.argtypes = [H, C.c_int, C.POINTER(C.c_uint64)]
+    lib.rp_total_energy.argtypes = [H, dp]
+    lib.rp_try_move.argtypes = [H, C.POINTER(Move), dp]
+    lib.rp_accept_move.argtypes = [H]
+    lib.rp_try_scaling.argtypes = [H, dp, dp]
+    lib.rp_revert_scaling.argtypes = [H]
+    lib.rp_sweep.argtypes = [H, C.POINTER(SweepParams), C.POINTER(SweepCounters)]
+    lib.rp_toggle_overlap_counting.argtypes = [H, C.c_int]
+    lib.rp_cached_overlaps.argtypes = [H, C.POINTER(C.c_uint64)]
+    lib.rp_pair_test_batch.argtypes = [H, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+    lib.rp_last_kernel_ms.argtypes = [H, dp, dp, dp, dp]
+    lib.rp_launch_count.argtypes = [H, C.POINTER(C.c_uint64)]
+    lib.rp_synchronize.argtypes = [H]
+    for name in SYMBOLS:
+        fn = getattr(lib, name)
+        if name not in ("rp_destroy", "rp_last_error", "rp_version"):
+            fn.restype = C.c_int
+    _lib = lib
+    return lib
+
+
+class RpError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__(f"rp_status {status}: {message}")
+        self.status = status
+        self.message = message
+
+
+class PreconditionError(RpError):
+    """The reference's PreconditionException (src/utils/Exceptions.h:19-66)."""
+
+
+def dptr(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def make_desc(hard=RP_HARD_NONE, soft=RP_SOFT_NONE, radius=0.0, length=0.0, epsilon=0.0, sigma=0.0, centres=None,
+              centre_radius=None, centre_half_axis=None):
+    d = InteractionDesc()
+    d.hard_kind, d.soft_kind = hard, soft
+    d.radius, d.length, d.epsilon, d.sigma = radius, length, epsilon, sigma
+    centres = [] if centres is None else centres
+    d.n_centres = len(centres)
+    for i, c in enumerate(centres):
+        for k in range(3):
+            d.centres[i][k] = float(c[k])
+        d.centre_radius[i] = float(centre_radius[i]) if centre_radius is not None else 0.0
+        if centre_half_axis is not None:
+            for k in range(3):
+                d.centre_half_axis[i][k] = float(centre_half_axis[i][k])
+    return d
+
+
+class Device:
+    """One rp_handle.  Methods are 1:1 with the C entry points; arrays are numpy float64."""
+
+    def __init__(self, device=0, seed=1234):
+        self.lib = load()
+        self.h = C.c_void_p()
+        cfg = Config(device, 0, seed, None)
+        st = self.lib.rp_create(C.byref(cfg), C.byref(self.h))
+        if st != RP_OK:
+            raise RpError(st, self.lib.rp_last_error(None).decode())
+        self.n = 0
+
+    def close(self):
+        if self.h:
+            self.lib.rp_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, st):
+        if st != RP_OK:
+            msg = self.lib.rp_last_error(self.h).decode()
+            raise (PreconditionError if st == RP_ERR_PRECONDITION else RpError)(st, msg)
+
+    def set_interaction(self, desc):
+        self._check(self.lib.rp_set_interaction(self.h, C.byref(desc)))
+
+    def upload(self, box, shapes):
+        box = np.ascontiguousarray(box, dtype=np.float64).reshape(9)
+        shapes = np.ascontiguousarray(shapes, dtype=np.float64).reshape(-1, 12)
+        self._check(self.lib.rp_upload(self.h, dptr(box), dptr(shapes), shapes.shape[0]))
+        self.n = shapes.shape[0]
+
+    def download(self, out=None):
+        box = np.empty(9)
+        shapes = out if out is not None else np.empty((self.n, 12))
+        self._check(self.lib.rp_download(self.h, dptr(box), dptr(shapes), self.n))
+        return box.reshape(3, 3), shapes
+
+    def rebuild_grid(self):
+        self._check(self.lib.rp_rebuild_grid(self.h))
+
+    def grid_info(self):
+        gi = GridInfo()
+        self._check(self.lib.rp_grid_info_get(self.h, C.byref(gi)))
+        return gi
+
+    def cell_numbers(self):
+        gi = self.grid_info()
+        out = np.empty(gi.num_centres, dtype=np.uint64)
+        self._check(self.lib.rp_cell_numbers(self.h, out.ctypes.data_as(C.POINTER(C.c_uint64))))
+        return out
+
+    def count_total_overlaps(self, early_exit=False):
+        v = C.c_uint64()
+        self._check(self.lib.rp_count_total_overlaps(self.h, int(early_exit), C.byref(v)))
+        return v.value
+
+    def total_energy(self):
+        v = C.c_double()
+        self._check(self.lib.rp_total_energy(self.h, C.byref(v)))
+        return v.value
+
+    def try_move(self, particle, kind, translation=(0, 0, 0), rotation=None):
+        m = Move()
+        m.particle, m.kind = particle, kind
+        for k in range(3):
+            m.translation[k] = float(translation[k])
+        rot = np.eye(3) if rotation is None else np.asarray(rotation, dtype=np.float64)
+        for k in range(9):
+            m.rotation[k] = float(rot.reshape(9)[k])
+        v = C.c_double()
+        self._check(self.lib.rp_try_move(self.h, C.byref(m), C.byref(v)))
+        return v.value
+
+    def accept_move(self):
+        self._check(self.lib.rp_accept_move(self.h))
+
+    def try_scaling(self, new_box):
+        nb = np.ascontiguousarray(new_box, dtype=np.float64).reshape(9)
+        v = C.c_double()
+        self._check(self.lib.rp_try_scaling(self.h, dptr(nb), C.byref(v)))
+        return v.value
+
+    def revert_scaling(self):
+        self._check(self.lib.rp_revert_scaling(self.h))
+
+    def sweep(self, kind, translation_step, rotation_step, cycle, temperature=1.0, pass_=0):
+        p = SweepParams(kind, pass_, translation_step, rotation_step, temperature, cycle)
+        c = SweepCounters()
+        self._check(self.lib.rp_sweep(self.h, C.byref(p), C.byref(c)))
+        return c
+
+    def toggle_overlap_counting(self, on):
+        self._check(self.lib.rp_toggle_overlap_counting(self.h, int(on)))
+
+    def cached_overlaps(self):
+        v = C.c_uint64()
+        self._check(self.lib.rp_cached_overlaps(self.h, C.byref(v)))
+        return v.value
+
+    def pair_test_batch(self, pairs, want_verdict=True, want_energy=False):
+        pairs = np.ascontiguousarray(pairs, dtype=PAIR_DTYPE)
+        n = pairs.shape[0]
+        verdict = np.zeros(n, dtype=np.uint8) if want_verdict else None
+        energy = np.zeros(n, dtype=np.float64) if want_energy else None
+        self._check(self.lib.rp_pair_test_batch(self.h, pairs.ctypes.data, n,
+                                                verdict.ctypes.data if want_verdict else None,
+                                                energy.ctypes.data if want_energy else None))
+        return verdict, energy
+
+    def last_kernel_ms(self):
+        a, b, c, d = C.c_double(), C.c_double(), C.c_double(), C.c_double()
+        self._check(self.lib.rp_last_kernel_ms(self.h, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
+        return {"sweep": a.value, "sweep_grid": b.value, "rebuild": c.value, "scaling": d.value}
+
+    def launch_count(self):
+        v = C.c_uint64()
+        self._check(self.lib.rp_launch_count(self.h, C.byref(v)))
+        return v.value
+
+    def synchronize(self):
+        self._check(self.lib.rp_synchronize(self.h))

@@ -1,0 +1,456 @@
+// rp_api.cu — the C ABI of librampack_b200.so (include/rampack_b200.h): handle lifetime, state upload/download and
+// thin forwarding to the kernels.  No exception crosses the boundary: every entry point returns an rp_status.
+#include "rp_internal.cuh"
+#include <limits>
+
+namespace rp {
+
+static thread_local std::string tlsError;
+
+// Flatten an rp_interaction_desc into the device parameter block.  Every threshold is computed with the expression
+// the reference evaluates per call (citations in rp_pair.cuh) so that the compared doubles are bit-identical.
+static void fillInter(const rp_interaction_desc &d, Inter &I) {
+    std::memset(&I, 0, sizeof(I));
+    I.hard = d.hard_kind;
+    I.soft = d.soft_kind;
+    RP_EXPECT(d.n_centres >= 0 && d.n_centres <= RP_MAX_CENTRES, "0 <= n_centres <= RP_MAX_CENTRES");
+    RP_EXPECT(I.hard != RP_HARD_NONE || I.soft != RP_SOFT_NONE, "interaction has neither hard nor soft part");
+    I.k = d.n_centres;
+    I.kk = d.n_centres > 0 ? d.n_centres : 1;
+    double hardRange = 0, softRange = 0;
+    bool hardConvex = false;
+    switch (d.hard_kind) {
+        case RP_HARD_NONE:
+            break;
+        case RP_HARD_SPHERE:
+            RP_EXPECT(d.radius > 0, "radius > 0");
+            RP_EXPECT(d.n_centres == 0, "sphere has no interaction centres");
+            I.sphereThr2 = (2 * d.radius) * (2 * d.radius);      // std::pow(2*r, 2)
+            hardRange = 2 * d.radius;
+            hardConvex = true;
+            break;
+        case RP_HARD_SPHEROCYLINDER:
+            RP_EXPECT(d.radius > 0 && d.length >= 0, "radius > 0 && length >= 0");
+            RP_EXPECT(d.n_centres == 0, "spherocylinder has no interaction centres");
+            I.scInner2 = 4 * d.radius * d.radius;
+            I.scOuter2 = (2 * d.radius + d.length) * (2 * d.radius + d.length);
+            I.scHalfMinus = 0.5 * -1 * d.length;
+            I.scHalfPlus = 0.5 * 1 * d.length;
+            hardRange = 2 * d.radius + d.length;
+            hardConvex = true;
+            break;
+        case RP_HARD_POLYSPHERE: {
+            RP_EXPECT(d.n_centres >= 1, "polysphere needs at least one centre");
+            double maxR = 0;
+            for (int i = 0; i < d.n_centres; i++) {
+                RP_EXPECT(d.centre_radius[i] > 0, "radius > 0");
+                if (d.centre_radius[i] > maxR) maxR = d.centre_radius[i];
+            }
+            hardRange = 2 * maxR;
+            break;
+        }
+        case RP_HARD_POLYSPHEROCYLINDER: {
+            RP_EXPECT(d.n_centres >= 1, "polyspherocylinder needs at least one centre");
+            double maxC = 0;
+            for (int i = 0; i < d.n_centres; i++) {
+                RP_EXPECT(d.centre_radius[i] > 0, "radius > 0");
+                V3 ha = v3(d.centre_half_axis[i][0], d.centre_half_axis[i][1], d.centre_half_axis[i][2]);
+                I.ccircum[i] = d.centre_radius[i] + std::sqrt(norm2(ha));
+                if (I.ccircum[i] > maxC) maxC = I.ccircum[i];
+            }
+            hardRange = 2 * maxC;
+            break;
+        }
+        default:
+            throw rp_error(RP_ERR_UNSUPPORTED, "hard interaction kind not implemented on the device");
+    }
+    switch (d.soft_kind) {
+        case RP_SOFT_NONE:
+            break;
+        case RP_SOFT_LJ:
+            RP_EXPECT(d.epsilon > 0 && d.sigma > 0, "epsilon > 0 && sigma > 0");
+            softRange = 3 * d.sigma;
+            break;
+        case RP_SOFT_WCA: {
+            RP_EXPECT(d.epsilon > 0 && d.sigma > 0, "epsilon > 0 && sigma > 0");
+            double s = d.sigma * std::pow(2., 1. / 6);
+            I.wcaCut2 = s * s;
+            softRange = s;
+            break;
+        }
+        case RP_SOFT_SIC:
+            RP_EXPECT(d.epsilon != 0 && d.sigma > 0, "epsilon != 0 && sigma > 0");
+            softRange = d.sigma;
+            break;
+        default:
+            throw rp_error(RP_ERR_UNSUPPORTED, "soft interaction kind not implemented on the device");
+    }
+    I.sigma2 = d.sigma * d.sigma;
+    I.fourEps = 4 * d.epsilon;
+    I.eps = d.epsilon;
+    for (int i = 0; i < d.n_centres; i++) {
+        for (int c = 0; c < 3; c++) {
+            I.cpos[i][c] = d.centres[i][c];
+            I.chalf[i][c] = d.centre_half_axis[i][c];
+        }
+        I.cradius[i] = d.centre_radius[i];
+    }
+    // CompoundInteraction (core/interactions/CompoundInteraction.cpp:5-66): max of the ranges; convex iff the only
+    // hard part is convex
+    I.range = std::max(hardRange, softRange);
+    I.convex = hardConvex;
+    // Interaction::getTotalRangeRadius (core/Interaction.cpp:55-70)
+    double maxRadius2 = 0;
+    for (int i = 0; i < d.n_centres; i++) {
+        double r2 = norm2(v3(d.centres[i][0], d.centres[i][1], d.centres[i][2]));
+        if (r2 > maxRadius2) maxRadius2 = r2;
+    }
+    I.totalRange = d.n_centres == 0 ? I.range : 2 * std::sqrt(maxRadius2) + I.range;
+}
+
+static Box makeBox(const double m[9]) {
+    Box b;
+    for (int i = 0; i < 9; i++) b.m.a[i] = m[i];
+    b.inv = inverse(b.m);
+    return b;
+}
+
+// AoS (N x 12, reference Shape layout) <-> SoA with stride cap
+__global__ void k_unpack_shapes(int n, size_t cap, const double *__restrict__ aos, double *__restrict__ pos,
+                                double *__restrict__ orient)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n * 12) return;
+    int p = i / 12, c = i % 12;
+    double v = aos[i];
+    if (c < 3) pos[c * cap + p] = v;
+    else orient[(c - 3) * cap + p] = v;
+}
+__global__ void k_pack_shapes(int n, size_t cap, const double *__restrict__ pos, const double *__restrict__ orient,
+                              double *__restrict__ aos)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n * 12) return;
+    int p = i / 12, c = i % 12;
+    aos[i] = (c < 3) ? pos[c * cap + p] : orient[(c - 3) * cap + p];
+}
+
+static void ensureStage(Handle *h, size_t bytes) {
+    if (bytes > h->dStageCap) {
+        if (h->dStage) cudaFree(h->dStage);
+        h->dStage = nullptr;
+        RP_CUDA(cudaMalloc(&h->dStage, bytes + 64));
+        h->dStageCap = bytes + 64;
+    }
+}
+
+static void setupForInteraction(Handle *h) {
+    // Packing::setupForInteraction (core/Packing.cpp:931-950)
+    h->interactionRange = h->inter.range;
+    if (h->n == 0) return;
+    if (h->inter.k > 0) {
+        size_t need = h->cap * h->inter.k;
+        if (need > h->centreCap || !h->crel) {
+            if (h->crel) cudaFree(h->crel);
+            if (h->cabs) cudaFree(h->cabs);
+            h->crel = h->cabs = nullptr;
+            RP_CUDA(cudaMalloc(&h->crel, 3 * need * sizeof(double)));
+            RP_CUDA(cudaMalloc(&h->cabs, 3 * need * sizeof(double)));
+            h->centreCap = need;
+        }
+        initCentres(h);
+        recalcAbsoluteCentres(h);
+    }
+    h->gridDirty = true;
+    h->hasTrial = false;
+    h->hasLastScaling = false;
+    rebuildReferenceGrid(h);
+    if (h->overlapCounting)
+        h->numOverlaps = countTotalOverlaps(h, false);
+}
+
+}  // namespace rp
+
+using namespace rp;
+
+#define RP_API_BEGIN(h) if (!(h)) { rp::tlsError = "null handle"; return RP_ERR_PRECONDITION; } \
+    try { if (cudaSetDevice((h)->device) != cudaSuccess) throw rp::rp_error(RP_ERR_CUDA, "cudaSetDevice failed");
+#define RP_API_END(h) } catch (const rp::rp_error &e) { (h)->error = e.what(); return static_cast<rp_status>(e.status); } \
+    catch (const std::exception &e) { (h)->error = e.what(); return RP_ERR_STATE; } return RP_OK;
+
+extern "C" {
+
+const char *rp_version(void) { return "rampack_b200 0.1.0 (sm_100a)"; }
+
+const char *rp_last_error(const rp_handle *h) { return h ? h->error.c_str() : rp::tlsError.c_str(); }
+
+rp_status rp_create(const rp_config *config, rp_handle **out) {
+    if (!config || !out) { rp::tlsError = "null argument"; return RP_ERR_PRECONDITION; }
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        rp::tlsError = std::string("no usable CUDA device (there is no CPU fallback): ")
+                       + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+        return RP_ERR_CUDA;
+    }
+    if (config->device < 0 || config->device >= count) { rp::tlsError = "bad device ordinal"; return RP_ERR_CUDA; }
+    auto *h = new rp_handle;
+    try {
+        h->device = config->device;
+        h->seed = config->seed;
+        RP_CUDA(cudaSetDevice(h->device));
+        if (config->cuda_stream) {
+            h->stream = static_cast<cudaStream_t>(config->cuda_stream);
+        } else {
+            RP_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+            h->ownStream = true;
+        }
+        RP_CUDA(cudaMalloc(&h->dInter, sizeof(Inter)));
+        RP_CUDA(cudaMalloc(&h->dCounters, 32 * sizeof(unsigned long long)));
+        RP_CUDA(cudaMalloc(&h->dFlags, 16 * sizeof(int)));
+        RP_CUDA(cudaMalloc(&h->dMoveOut, 8 * sizeof(double)));
+        RP_CUDA(cudaMalloc(&h->tmpState, (12 + 6 * RP_MAX_CENTRES) * sizeof(double)));
+        for (auto &ev : h->ev) RP_CUDA(cudaEventCreate(&ev));
+    } catch (const std::exception &ex) {
+        rp::tlsError = ex.what();
+        delete h;
+        return RP_ERR_CUDA;
+    }
+    *out = h;
+    return RP_OK;
+}
+
+void rp_destroy(rp_handle *h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    for (void *p : {(void *) h->dInter, (void *) h->pos, (void *) h->orient, (void *) h->crel, (void *) h->cabs,
+                    (void *) h->lastPos, (void *) h->lastCabs, (void *) h->tmpState, (void *) h->dCounters,
+                    (void *) h->dFlags, (void *) h->dCellEnergy, (void *) h->dMoveOut, h->dStage,
+                    (void *) h->sweepMoved})
+        if (p) cudaFree(p);
+    if (h->stage) cudaFreeHost(h->stage);
+    freeGrid(h->grid);
+    freeGrid(h->tempGrid);
+    freeGrid(h->sgrid);
+    for (auto &ev : h->ev) if (ev) cudaEventDestroy(ev);
+    if (h->ownStream && h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+rp_status rp_set_interaction(rp_handle *h, const rp_interaction_desc *desc) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(desc != nullptr, "desc != NULL");
+    Inter I;
+    fillInter(*desc, I);
+    RP_EXPECT(I.range > 0, "interaction.getRangeRadius() > 0");
+    h->inter = I;
+    RP_CUDA(cudaMemcpyAsync(h->dInter, &h->inter, sizeof(Inter), cudaMemcpyHostToDevice, h->stream));
+    RP_CUDA(cudaStreamSynchronize(h->stream));
+    h->hasInteraction = true;
+    setupForInteraction(h);
+    RP_API_END(h)
+}
+
+rp_status rp_upload(rp_handle *h, const double box[9], const double *shapes, uint64_t n) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(box && shapes, "box and shapes must not be NULL");
+    RP_EXPECT(n > 0, "!shapes.empty()");
+    RP_EXPECT(n < (1ull << 27), "at most 2^27 particles per handle");
+    Box b = makeBox(box);
+    RP_EXPECT(boxVolume(b) != 0, "newBox.getVolume() != 0");
+    // Packing::areShapesWithinBox (core/Packing.cpp:1067-1073)
+    for (uint64_t i = 0; i < n; i++) {
+        V3 rel = absToRel(b, v3(shapes[12 * i], shapes[12 * i + 1], shapes[12 * i + 2]));
+        RP_EXPECT(!(rel.x < 0 || rel.x >= 1 || rel.y < 0 || rel.y >= 1 || rel.z < 0 || rel.z >= 1),
+                  "areShapesWithinBox(shapes, box)");
+    }
+    if (n > h->cap || !h->pos) {
+        if (h->pos) cudaFree(h->pos);
+        if (h->orient) cudaFree(h->orient);
+        h->pos = h->orient = nullptr;
+        size_t cap = n + 16;
+        RP_CUDA(cudaMalloc(&h->pos, 3 * cap * sizeof(double)));
+        RP_CUDA(cudaMalloc(&h->orient, 9 * cap * sizeof(double)));
+        h->cap = cap;
+    }
+    h->n = n;
+    h->box = b;
+    ensureStage(h, n * 12 * sizeof(double));
+    RP_CUDA(cudaMemcpyAsync(h->dStage, shapes, n * 12 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    int total = static_cast<int>(n * 12);
+    k_unpack_shapes<<<(total + 255) / 256, 256, 0, h->stream>>>(static_cast<int>(n), h->cap,
+                                                                static_cast<const double *>(h->dStage), h->pos,
+                                                                h->orient);
+    h->launches++;
+    RP_CUDA(cudaStreamSynchronize(h->stream));
+    RP_CUDA(cudaGetLastError());
+    h->gridDirty = true;
+    h->hasTrial = false;
+    h->hasLastScaling = false;
+    if (h->hasInteraction) setupForInteraction(h);
+    RP_API_END(h)
+}
+
+rp_status rp_download(rp_handle *h, double box_out[9], double *shapes_out, uint64_t n) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(n == h->n, "n == size()");
+    if (box_out) for (int i = 0; i < 9; i++) box_out[i] = h->box.m.a[i];
+    if (shapes_out && n > 0) {
+        ensureStage(h, n * 12 * sizeof(double));
+        int total = static_cast<int>(n * 12);
+        k_pack_shapes<<<(total + 255) / 256, 256, 0, h->stream>>>(static_cast<int>(n), h->cap, h->pos, h->orient,
+                                                                  static_cast<double *>(h->dStage));
+        h->launches++;
+        RP_CUDA(cudaMemcpyAsync(shapes_out, h->dStage, n * 12 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+        RP_CUDA(cudaStreamSynchronize(h->stream));
+        RP_CUDA(cudaGetLastError());
+    }
+    RP_API_END(h)
+}
+
+rp_status rp_size(const rp_handle *h, uint64_t *n_out) {
+    if (!h || !n_out) return RP_ERR_PRECONDITION;
+    *n_out = h->n;
+    return RP_OK;
+}
+
+rp_status rp_rebuild_grid(rp_handle *h) {
+    RP_API_BEGIN(h)
+    rebuildReferenceGrid(h);
+    RP_API_END(h)
+}
+
+rp_status rp_grid_info_get(rp_handle *h, rp_grid_info *out) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(out != nullptr, "out != NULL");
+    ensureGrid(h);
+    std::memset(out, 0, sizeof(*out));
+    out->has_grid = h->hasGrid ? 1 : 0;
+    out->cell_size = h->grid.cellSize;
+    out->num_centres = h->n * h->inter.kk;
+    if (h->hasGrid) {
+        for (int i = 0; i < 3; i++) out->cell_divisions[i] = h->grid.n[i];
+        out->max_cell_population = h->grid.maxPopulation;
+    }
+    RP_API_END(h)
+}
+
+rp_status rp_cell_numbers(rp_handle *h, uint64_t *cell_no_out) {
+    RP_API_BEGIN(h)
+    ensureGrid(h);
+    RP_EXPECT(h->hasGrid, "the packing has no neighbour grid (Packing.cpp:868-881)");
+    size_t m = h->grid.numItems;
+    std::vector<int> keys(m);
+    RP_CUDA(cudaMemcpyAsync(keys.data(), h->grid.keys, m * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    RP_CUDA(cudaStreamSynchronize(h->stream));
+    // reference numbering incl. ghost layers: coordinates + 1, divisions + 2 (NeighbourGrid.cpp:13-34)
+    const int *n = h->grid.n;
+    for (size_t i = 0; i < m; i++) {
+        int c = keys[i];
+        uint64_t cx = c % n[0], cy = (c / n[0]) % n[1], cz = c / (n[0] * n[1]);
+        cell_no_out[i] = ((cz + 1) * (n[1] + 2) + (cy + 1)) * (n[0] + 2) + (cx + 1);
+    }
+    RP_API_END(h)
+}
+
+rp_status rp_count_total_overlaps(rp_handle *h, int early_exit, uint64_t *count_out) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(h->hasInteraction && h->n > 0 && count_out, "packing and interaction must be set");
+    *count_out = countTotalOverlaps(h, early_exit != 0);
+    RP_API_END(h)
+}
+
+rp_status rp_total_energy(rp_handle *h, double *energy_out) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(h->hasInteraction && h->n > 0 && energy_out, "packing and interaction must be set");
+    *energy_out = totalEnergy(h);
+    RP_API_END(h)
+}
+
+rp_status rp_try_move(rp_handle *h, const rp_move *move, double *dE_out) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(move && dE_out, "move and dE_out must not be NULL");
+    *dE_out = tryMove(h, *move);
+    RP_API_END(h)
+}
+
+rp_status rp_accept_move(rp_handle *h) {
+    RP_API_BEGIN(h)
+    acceptMove(h);
+    RP_API_END(h)
+}
+
+rp_status rp_try_scaling(rp_handle *h, const double new_box[9], double *dE_out) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(new_box && dE_out, "new_box and dE_out must not be NULL");
+    *dE_out = tryScaling(h, makeBox(new_box));
+    RP_API_END(h)
+}
+
+rp_status rp_revert_scaling(rp_handle *h) {
+    RP_API_BEGIN(h)
+    revertScaling(h);
+    RP_API_END(h)
+}
+
+rp_status rp_sweep(rp_handle *h, const rp_sweep_params *params, rp_sweep_counters *counters_out) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(params != nullptr, "params != NULL");
+    RP_EXPECT(h->hasInteraction && h->n > 0, "packing and interaction must be set");
+    sweep(h, *params, counters_out);
+    RP_API_END(h)
+}
+
+rp_status rp_toggle_overlap_counting(rp_handle *h, int count_overlaps) {
+    RP_API_BEGIN(h)
+    // Packing::toggleOverlapCounting (core/Packing.cpp:1049-1053)
+    h->overlapCounting = count_overlaps != 0;
+    if (h->overlapCounting && h->hasInteraction && h->n > 0)
+        h->numOverlaps = countTotalOverlaps(h, false);
+    RP_API_END(h)
+}
+
+rp_status rp_cached_overlaps(rp_handle *h, uint64_t *count_out) {
+    RP_API_BEGIN(h)
+    // Packing::getCachedNumberOfOverlaps (core/Packing.cpp:1055-1060)
+    if (!h->overlapCounting)
+        throw rp_error(RP_ERR_STATE,
+                       "Packing: overlap counting is toggled false; number of overlaps is not cached");
+    *count_out = h->numOverlaps;
+    RP_API_END(h)
+}
+
+rp_status rp_pair_test_batch(rp_handle *h, const rp_pair *pairs, uint64_t n, uint8_t *verdict_out,
+                             double *energy_out)
+{
+    RP_API_BEGIN(h)
+    pairTestBatch(h, pairs, n, verdict_out, energy_out);
+    RP_API_END(h)
+}
+
+rp_status rp_last_kernel_ms(rp_handle *h, double *sweep_ms, double *sweep_grid_ms, double *rebuild_ms,
+                            double *scaling_ms)
+{
+    RP_API_BEGIN(h)
+    if (sweep_ms) *sweep_ms = h->lastSweepMs;
+    if (sweep_grid_ms) *sweep_grid_ms = h->lastSweepGridMs;
+    if (rebuild_ms) *rebuild_ms = h->lastRebuildMs;
+    if (scaling_ms) *scaling_ms = h->lastScalingMs;
+    RP_API_END(h)
+}
+
+rp_status rp_launch_count(rp_handle *h, uint64_t *launches_out) {
+    RP_API_BEGIN(h)
+    *launches_out = h->launches;
+    RP_API_END(h)
+}
+
+rp_status rp_synchronize(rp_handle *h) {
+    RP_API_BEGIN(h)
+    RP_CUDA(cudaStreamSynchronize(h->stream));
+    RP_API_END(h)
+}
+
+}  // extern "C"

@@ -1,0 +1,214 @@
+// rp_internal.cuh — handle layout and device views shared by the translation units of librampack_b200.so
+#pragma once
+
+#include <cuda_runtime.h>
+#include <string>
+#include <vector>
+#include <cstdio>
+#include <cstring>
+#include <cmath>
+#include <algorithm>
+#include <stdexcept>
+
+#include "rp_pair.cuh"
+
+namespace rp {
+
+// ---------------------------------------------------------------------------------------------------------------
+// Reference-geometry neighbour grid (Packing::neighbourGrid) over the REAL cells only: the reference's ghost layers
+// are replaced by periodic wrap + the same 27 lattice translations (core/NeighbourGrid.cpp:80-100, 203-217).
+// Cells are flattened x-fastest like the reference (NeighbourGrid.cpp:45-50); items of one cell are contiguous and
+// ordered by ascending centre index; pair records are SoA in that order.
+// ---------------------------------------------------------------------------------------------------------------
+struct GridView {
+    int n[3];              // real cells per axis
+    int numCells;
+    double relCell[3];     // 1 / n[i]  (NeighbourGrid.cpp:196)
+    int numItems;
+    const int *cellStart;  // [numCells + 1]
+    const int *items;      // [numItems] centre index = particle * kk + centre
+    const double *px, *py, *pz;   // sorted centre positions (absolute, inside the box)
+    const double *ax, *ay, *az;   // sorted aux vectors (rp::pairAux)
+    V3 trans[27];          // lattice translations, index (i*3 + j)*3 + k <-> relative (i-1, j-1, k-1)
+};
+
+// 0-based REAL cell coordinate of a relative coordinate — NeighbourGrid::positionToCellNo
+// (core/NeighbourGrid.cpp:13-34; the reference adds 1 for its ghost layer)
+RP_HD int cellCoord(double rel, double relCell, int *outside) {
+    const double EPSILON = 2.220446049250313e-16 * 10;
+    if (rel < 0) {
+        if (!(rel > -EPSILON) && outside) *outside = 1;
+        rel = 0;
+    } else if (rel >= 1) {
+        if (!(rel < 1 + EPSILON) && outside) *outside = 1;
+        rel = 1 - EPSILON;
+    }
+    return static_cast<int>(rel / relCell);
+}
+
+RP_HD int cellOfPosition(const GridView &g, const Box &box, V3 pos, int *outside) {
+    V3 rel = absToRel(box, pos);
+    int cx = cellCoord(rel.x, g.relCell[0], outside);
+    int cy = cellCoord(rel.y, g.relCell[1], outside);
+    int cz = cellCoord(rel.z, g.relCell[2], outside);
+    return (cz * g.n[1] + cy) * g.n[0] + cx;
+}
+
+// Neighbour cell (dx,dy,dz in -1..1) of real cell (cx,cy,cz): periodic wrap; *tIdx = index into trans[].
+// Same aliasing as NeighbourGrid::getReflectedCellData (core/NeighbourGrid.cpp:80-100).
+RP_HD int neighbourCell(const int n[3], int cx, int cy, int cz, int dx, int dy, int dz, int *tIdx) {
+    int c[3] = {cx + dx, cy + dy, cz + dz};
+    int t[3] = {1, 1, 1};
+    for (int i = 0; i < 3; i++) {
+        if (c[i] < 0) { c[i] = n[i] - 1; t[i] = 0; }
+        else if (c[i] >= n[i]) { c[i] = 0; t[i] = 2; }
+    }
+    *tIdx = (t[0] * 3 + t[1]) * 3 + t[2];
+    return (c[2] * n[1] + c[1]) * n[0] + c[0];
+}
+
+// Device storage shared by the two grid flavours (reference-geometry grid and sweep grid)
+struct GridStore {
+    int n[3] = {0, 0, 0};
+    int numCells = 0;
+    int numItems = 0;
+    double cellSize = 0;
+    int *cellStart = nullptr;     // capacity cellCap + 1
+    int *cellFill = nullptr;      // capacity cellCap + 1 (histogram / fill counters)
+    int *keys = nullptr;          // capacity itemCap
+    int *itemsTmp = nullptr;      // capacity itemCap
+    int *items = nullptr;         // capacity itemCap
+    double *rec = nullptr;        // 6 * itemCap doubles: SoA (reference grid) or AoS 48-byte records (sweep grid)
+    size_t cellCap = 0, itemCap = 0;
+    int *blockSums = nullptr;     // scan scratch
+    size_t blockSumsCap = 0;
+    int maxPopulation = 0;
+    bool valid = false;
+    Box box;                      // box the grid was built for (translations)
+};
+
+struct SweepStats {
+    unsigned long long attempted, accepted, rejDomain, rejOverlap;
+};
+
+struct Handle {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool ownStream = false;
+    unsigned long long seed = 0;
+    std::string error;
+
+    // interaction
+    bool hasInteraction = false;
+    Inter inter;            // host copy
+    Inter *dInter = nullptr;
+
+    // particles, canonical (original particle order), SoA with stride `cap`
+    size_t n = 0, cap = 0;
+    Box box;
+    Box lastBox;
+    double *pos = nullptr;       // 3 * cap
+    double *orient = nullptr;    // 9 * cap
+    double *crel = nullptr;      // 3 * centreCap  (Packing::interactionCentres, only k > 0)
+    double *cabs = nullptr;      // 3 * centreCap  (Packing::absoluteInteractionCentres, only k > 0)
+    size_t centreCap = 0;
+    double *lastPos = nullptr;   // tryScaling backup (positions and absolute centres; orientations do not change)
+    double *lastCabs = nullptr;
+    size_t lastCap = 0, lastCentreCap = 0;
+    bool hasLastScaling = false;
+    double interactionRange = 0; // Packing::interactionRange
+
+    // reference-geometry neighbour grid (Packing::neighbourGrid / tempNeighbourGrid)
+    GridStore grid, tempGrid;
+    bool hasGrid = false, tempHasGrid = false;
+    bool gridDirty = true;
+    // sweep grid (random origin, particle mass centres, even cell counts)
+    GridStore sgrid;
+    int *sweepMoved = nullptr;    // per sorted slot: accepted in this cycle
+    size_t sweepMovedCap = 0;
+
+    // explicit trial move (Packing's temp slot): pos[3] orient[9] crel[16][3] cabs[16][3]
+    double *tmpState = nullptr;
+    bool hasTrial = false;
+    unsigned long long trialParticle = 0;
+    int trialKind = 0;
+    long long lastMoveOverlapDelta = 0;
+
+    // overlap counting (Packing::overlapCounting / numOverlaps)
+    bool overlapCounting = false;
+    unsigned long long numOverlaps = 0;
+    unsigned long long lastScalingNumOverlaps = 0;
+
+    // scratch
+    unsigned long long *dCounters = nullptr;  // 32 counters
+    int *dFlags = nullptr;                    // 16 flags
+    double *dCellEnergy = nullptr;
+    size_t cellEnergyCap = 0;
+    double *dMoveOut = nullptr;               // 8 doubles
+    void *stage = nullptr;        // pinned host staging
+    size_t stageCap = 0;
+    void *dStage = nullptr;       // device staging for AoS <-> SoA transposes
+    size_t dStageCap = 0;
+
+    // timing of the last call
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    double lastSweepMs = 0, lastSweepGridMs = 0, lastRebuildMs = 0, lastScalingMs = 0;
+    unsigned long long launches = 0;
+};
+
+struct rp_error : std::runtime_error {
+    int status;
+    rp_error(int status, const std::string &msg) : std::runtime_error(msg), status(status) {}
+};
+
+#define RP_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+    throw rp::rp_error(RP_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+#define RP_EXPECT(cond, msg) do { if (!(cond)) \
+    throw rp::rp_error(RP_ERR_PRECONDITION, std::string("Precondition (") + #cond + ") failed: " + (msg)); } while (0)
+
+template <typename T>
+inline void devEnsure(T *&p, size_t &cap, size_t need) {
+    if (need <= cap && p) return;
+    if (p) cudaFree(p);
+    p = nullptr;
+    size_t newCap = need + need / 4 + 16;
+    RP_CUDA(cudaMalloc(&p, newCap * sizeof(T)));
+    cap = newCap;
+}
+
+inline void computeTranslations(const Box &box, V3 trans[27]) {
+    // NeighbourGrid::calculateTranslations (core/NeighbourGrid.cpp:203-217)
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++)
+            for (int k = 0; k < 3; k++)
+                trans[(i * 3 + j) * 3 + k] = relToAbs(box, v3(static_cast<double>(i) - 1,
+                                                              static_cast<double>(j) - 1.,
+                                                              static_cast<double>(k) - 1.));
+}
+
+// ---- rp_grid.cu ----
+void ensureGridCapacity(GridStore &g, size_t numCells, size_t numItems);
+// histogram in g.cellFill -> g.cellStart (exclusive scan), g.cellFill zeroed, max population -> dMaxPop
+void scanCells(Handle *h, GridStore &g, int *dMaxPop);
+// keys -> items (cell order, ascending index inside a cell); needs scanCells() first
+void scatterItems(Handle *h, GridStore &g);
+GridView makeView(const GridStore &g);
+void rebuildReferenceGrid(Handle *h);
+void ensureGrid(Handle *h);
+void freeGrid(GridStore &g);
+// ---- rp_recount.cu ----
+unsigned long long countTotalOverlaps(Handle *h, bool earlyExit);
+double totalEnergy(Handle *h);
+void initCentres(Handle *h);
+void recalcAbsoluteCentres(Handle *h);
+double tryMove(Handle *h, const rp_move &m);
+void acceptMove(Handle *h);
+double tryScaling(Handle *h, const Box &newBox);
+void revertScaling(Handle *h);
+void pairTestBatch(Handle *h, const rp_pair *pairs, unsigned long long n, unsigned char *verdict, double *energy);
+// ---- rp_sweep.cu ----
+void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out);
+
+}  // namespace rp
+
+struct rp_handle : rp::Handle {};

@@ -171,6 +171,11 @@ rp_status rp_pair_test_batch(rp_handle *h, const rp_pair *pairs, uint64_t n, uin
 /* ---- timing hook for bench.py: device milliseconds spent inside the kernels of the last call ---- */
 rp_status rp_last_kernel_ms(rp_handle *h, double *sweep_ms, double *sweep_grid_ms, double *rebuild_ms,
                             double *scaling_ms);
+/* measurement helpers (bench.py's roofline): candidates per interaction centre in the reference-geometry grid —
+ * Packing::getAverageNumberOfNeighbours (src/core/Packing.cpp:1000-1033) — and how many of them lie within
+ * getRangeRadius(); FP64 vector-pipe peak of the device in GFLOP/s, fused (DFMA) and non-fused (DMUL + DADD) */
+rp_status rp_neighbour_stats(rp_handle *h, double *candidates_per_centre, double *within_range_per_centre);
+rp_status rp_measure_fp64_peak(rp_handle *h, double *dfma_gflops, double *dmul_dadd_gflops);
 /* kernels launched by this handle so far (bench.py's gpu_launches) */
 rp_status rp_launch_count(rp_handle *h, uint64_t *launches_out);
 rp_status rp_synchronize(rp_handle *h);

@@ -291,3 +291,213 @@ def ref_run_simulation(traits, box, shapes, seed, temperature, pressure, trans_s
     if st != 0:
         raise RuntimeError("reference simulation failed: " + err.value.decode())
     return res, box_out.reshape(3, 3), shapes_out
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# the plain-C restatement (oracle/rp_oracle.c -> liboracle_port.so): same Python surface as RefTraits / RefPacking
+# ---------------------------------------------------------------------------------------------------------------------
+class PortRunResult(C.Structure):
+    _fields_ = [("moves_attempted", C.c_uint64), ("moves_accepted", C.c_uint64), ("scalings_attempted", C.c_uint64),
+                ("scalings_accepted", C.c_uint64), ("move_seconds", C.c_double), ("scaling_seconds", C.c_double)]
+
+
+def port_path():
+    return os.path.join(HERE, "liboracle_port.so")
+
+
+def load_port():
+    if "port" in _libs:
+        return _libs["port"]
+    path = port_path()
+    if not os.path.exists(path):
+        subprocess.check_call(["make", "-C", HERE, "port"], stdout=subprocess.DEVNULL)
+    lib = C.CDLL(path)
+    V = C.c_void_p
+    dp = C.POINTER(C.c_double)
+    u64p = C.POINTER(C.c_uint64)
+    D = C.POINTER(InteractionDesc)
+    lib.rpo_pair_test_batch.argtypes = [D, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+    lib.rpo_pair_test_batch_pbc.argtypes = [D, dp, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+    lib.rpo_box_info.argtypes = [dp, dp, dp, dp]
+    lib.rpo_box_info.restype = None
+    lib.rpo_pbc_correction.argtypes = [dp, dp, dp]
+    lib.rpo_pbc_correction.restype = None
+    lib.rpo_cell_numbers.argtypes = [dp, C.c_double, dp, C.c_uint64, u64p, u64p]
+    lib.rpo_rotation_matrix.argtypes = [dp, C.c_double, dp]
+    lib.rpo_rotation_matrix.restype = None
+    lib.rpo_range_radius.argtypes = [D]
+    lib.rpo_range_radius.restype = C.c_double
+    lib.rpo_total_range_radius.argtypes = [D]
+    lib.rpo_total_range_radius.restype = C.c_double
+    lib.rpo_packing_create.argtypes = [D, dp, dp, C.c_uint64, C.c_char_p, C.c_size_t]
+    lib.rpo_packing_create.restype = V
+    lib.rpo_packing_destroy.argtypes = [V]
+    lib.rpo_packing_destroy.restype = None
+    lib.rpo_packing_get.argtypes = [V, dp, dp]
+    lib.rpo_packing_get.restype = None
+    lib.rpo_grid_divisions.argtypes = [V, u64p]
+    lib.rpo_average_neighbours.argtypes = [V]
+    lib.rpo_average_neighbours.restype = C.c_double
+    lib.rpo_count_total_overlaps.argtypes = [V, C.c_int]
+    lib.rpo_count_total_overlaps.restype = C.c_uint64
+    lib.rpo_total_energy.argtypes = [V]
+    lib.rpo_total_energy.restype = C.c_double
+    lib.rpo_try_move.argtypes = [V, C.POINTER(Move), dp]
+    lib.rpo_accept_move.argtypes = [V]
+    lib.rpo_accept_move.restype = None
+    lib.rpo_try_scaling.argtypes = [V, dp, dp]
+    lib.rpo_revert_scaling.argtypes = [V]
+    lib.rpo_revert_scaling.restype = None
+    lib.rpo_toggle_overlap_counting.argtypes = [V, C.c_int]
+    lib.rpo_toggle_overlap_counting.restype = None
+    lib.rpo_cached_overlaps.argtypes = [V]
+    lib.rpo_cached_overlaps.restype = C.c_uint64
+    lib.rpo_run_cycles.argtypes = [V, C.c_uint64, C.c_uint64, C.c_double, C.c_double, C.c_double, C.c_double,
+                                   C.c_int, C.c_double, C.POINTER(PortRunResult)]
+    _libs["port"] = lib
+    return lib
+
+
+class PortTraits:
+    def __init__(self, desc):
+        self.lib = load_port()
+        self.desc = copy_desc(desc)
+
+    @property
+    def range_radius(self):
+        return self.lib.rpo_range_radius(C.byref(self.desc))
+
+    @property
+    def total_range_radius(self):
+        return self.lib.rpo_total_range_radius(C.byref(self.desc))
+
+    def pair_test_batch(self, pairs, want_verdict=True, want_energy=False, pbc_box=None):
+        pairs = np.ascontiguousarray(pairs, dtype=PAIR_DTYPE)
+        n = pairs.shape[0]
+        verdict = np.zeros(n, dtype=np.uint8) if want_verdict else None
+        energy = np.zeros(n, dtype=np.float64) if want_energy else None
+        vp = verdict.ctypes.data if want_verdict else None
+        ep = energy.ctypes.data if want_energy else None
+        if pbc_box is None:
+            self.lib.rpo_pair_test_batch(C.byref(self.desc), pairs.ctypes.data, n, vp, ep)
+        else:
+            box = np.ascontiguousarray(pbc_box, dtype=np.float64).reshape(9)
+            self.lib.rpo_pair_test_batch_pbc(C.byref(self.desc), _dp(box), pairs.ctypes.data, n, vp, ep)
+        return verdict, energy
+
+
+class PortPacking:
+    def __init__(self, traits, box, shapes, move_threads=1, scaling_threads=1):
+        self.lib = traits.lib
+        self.traits = traits
+        box = np.ascontiguousarray(box, dtype=np.float64).reshape(9)
+        shapes = np.ascontiguousarray(shapes, dtype=np.float64).reshape(-1, 12)
+        self.n = shapes.shape[0]
+        err = C.create_string_buffer(256)
+        self.ptr = self.lib.rpo_packing_create(C.byref(traits.desc), _dp(box), _dp(shapes), self.n, err, 256)
+        if not self.ptr:
+            raise ValueError(err.value.decode())
+
+    def __del__(self):
+        if getattr(self, "ptr", None):
+            self.lib.rpo_packing_destroy(self.ptr)
+            self.ptr = None
+
+    def get(self):
+        box = np.empty(9)
+        shapes = np.empty((self.n, 12))
+        self.lib.rpo_packing_get(self.ptr, _dp(box), _dp(shapes))
+        return box.reshape(3, 3), shapes
+
+    def grid_divisions(self):
+        out = (C.c_uint64 * 3)()
+        return tuple(out) if self.lib.rpo_grid_divisions(self.ptr, out) else None
+
+    def average_neighbours(self):
+        return self.lib.rpo_average_neighbours(self.ptr)
+
+    def count_total_overlaps(self, early_exit=False):
+        return self.lib.rpo_count_total_overlaps(self.ptr, int(early_exit))
+
+    def total_energy(self):
+        return self.lib.rpo_total_energy(self.ptr)
+
+    def try_move(self, particle, kind, translation=(0, 0, 0), rotation=None):
+        m = Move()
+        m.particle, m.kind = particle, kind
+        for k in range(3):
+            m.translation[k] = float(translation[k])
+        rot = np.eye(3) if rotation is None else np.asarray(rotation, dtype=np.float64)
+        for k in range(9):
+            m.rotation[k] = float(rot.reshape(9)[k])
+        v = C.c_double()
+        if self.lib.rpo_try_move(self.ptr, C.byref(m), C.byref(v)) != 0:
+            raise ValueError("particleIdx < size()")
+        return v.value
+
+    def accept_move(self):
+        self.lib.rpo_accept_move(self.ptr)
+
+    def try_scaling(self, new_box):
+        nb = np.ascontiguousarray(new_box, dtype=np.float64).reshape(9)
+        v = C.c_double()
+        if self.lib.rpo_try_scaling(self.ptr, _dp(nb), C.byref(v)) != 0:
+            raise ValueError("newBox.getVolume() != 0")
+        return v.value
+
+    def revert_scaling(self):
+        self.lib.rpo_revert_scaling(self.ptr)
+
+    def toggle_overlap_counting(self, on):
+        self.lib.rpo_toggle_overlap_counting(self.ptr, int(on))
+
+    def cached_overlaps(self):
+        return self.lib.rpo_cached_overlaps(self.ptr)
+
+    def run_cycles(self, seed, cycles, trans_step, rot_step, temperature=1.0, pressure=1.0, box_moves=False,
+                   box_step=0.01):
+        res = PortRunResult()
+        self.lib.rpo_run_cycles(self.ptr, seed, cycles, trans_step, rot_step, temperature, pressure, int(box_moves),
+                                box_step, C.byref(res))
+        return res
+
+
+def port_cell_numbers(box, cell_size, positions):
+    lib = load_port()
+    box = np.ascontiguousarray(box, dtype=np.float64).reshape(9)
+    positions = np.ascontiguousarray(positions, dtype=np.float64).reshape(-1, 3)
+    out = np.empty(positions.shape[0], dtype=np.uint64)
+    div = (C.c_uint64 * 3)()
+    if lib.rpo_cell_numbers(_dp(box), cell_size, _dp(positions), positions.shape[0],
+                            out.ctypes.data_as(C.POINTER(C.c_uint64)), div) != 0:
+        raise ValueError("NeighbourGrid construction or positionToCellNo failed")
+    return out, tuple(div)
+
+
+def port_box_info(box):
+    lib = load_port()
+    box = np.ascontiguousarray(box, dtype=np.float64).reshape(9)
+    heights, vol, inv = np.empty(3), C.c_double(), np.empty(9)
+    lib.rpo_box_info(_dp(box), _dp(heights), C.byref(vol), _dp(inv))
+    return heights, vol.value, inv.reshape(3, 3)
+
+
+def port_pbc_correction(box, pos):
+    lib = load_port()
+    box = np.ascontiguousarray(box, dtype=np.float64).reshape(9)
+    pos = np.ascontiguousarray(pos, dtype=np.float64).reshape(3)
+    out = np.empty(3)
+    lib.rpo_pbc_correction(_dp(box), _dp(pos), _dp(out))
+    return out
+
+
+def port_rotation_matrix(axis, angle):
+    lib = load_port()
+    axis = np.ascontiguousarray(axis, dtype=np.float64).reshape(3)
+    out = np.empty(9)
+    lib.rpo_rotation_matrix(_dp(axis), angle, _dp(out))
+    return out.reshape(3, 3)
+
+
+def have_ref(native=False):
+    return os.path.exists(ref_path(native))

@@ -63,7 +63,7 @@ SYMBOLS = ["rp_create", "rp_destroy", "rp_last_error", "rp_version", "rp_set_int
            "rp_download", "rp_size", "rp_rebuild_grid", "rp_grid_info_get", "rp_cell_numbers",
            "rp_count_total_overlaps", "rp_total_energy", "rp_try_move", "rp_accept_move", "rp_try_scaling",
            "rp_revert_scaling", "rp_sweep", "rp_toggle_overlap_counting", "rp_cached_overlaps",
-           "rp_pair_test_batch", "rp_last_kernel_ms", "rp_launch_count", "rp_synchronize"]
+           "rp_pair_test_batch", "rp_neighbour_stats", "rp_measure_fp64_peak", "rp_last_kernel_ms", "rp_launch_count", "rp_synchronize"]
 
 _lib = None
 
@@ -107,6 +107,8 @@ def load():
     lib.rp_cached_overlaps.argtypes = [H, C.POINTER(C.c_uint64)]
     lib.rp_pair_test_batch.argtypes = [H, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
     lib.rp_last_kernel_ms.argtypes = [H, dp, dp, dp, dp]
+    lib.rp_neighbour_stats.argtypes = [H, dp, dp]
+    lib.rp_measure_fp64_peak.argtypes = [H, dp, dp]
     lib.rp_launch_count.argtypes = [H, C.POINTER(C.c_uint64)]
     lib.rp_synchronize.argtypes = [H]
     for name in SYMBOLS:
@@ -152,10 +154,10 @@ def make_desc(hard=RP_HARD_NONE, soft=RP_SOFT_NONE, radius=0.0, length=0.0, epsi
 class Device:
     """One rp_handle.  Methods are 1:1 with the C entry points; arrays are numpy float64."""
 
-    def __init__(self, device=0, seed=1234):
+    def __init__(self, device=0, seed=1234, cuda_stream=None):
         self.lib = load()
         self.h = C.c_void_p()
-        cfg = Config(device, 0, seed, None)
+        cfg = Config(device, 0, seed, cuda_stream)
         st = self.lib.rp_create(C.byref(cfg), C.byref(self.h))
         if st != RP_OK:
             raise RpError(st, self.lib.rp_last_error(None).decode())
@@ -268,6 +270,16 @@ class Device:
         a, b, c, d = C.c_double(), C.c_double(), C.c_double(), C.c_double()
         self._check(self.lib.rp_last_kernel_ms(self.h, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
         return {"sweep": a.value, "sweep_grid": b.value, "rebuild": c.value, "scaling": d.value}
+
+    def neighbour_stats(self):
+        a, b = C.c_double(), C.c_double()
+        self._check(self.lib.rp_neighbour_stats(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def measure_fp64_peak(self):
+        a, b = C.c_double(), C.c_double()
+        self._check(self.lib.rp_measure_fp64_peak(self.h, C.byref(a), C.byref(b)))
+        return {"dfma_gflops": a.value, "dmul_dadd_gflops": b.value}
 
     def launch_count(self):
         v = C.c_uint64()

@@ -441,6 +441,21 @@ rp_status rp_last_kernel_ms(rp_handle *h, double *sweep_ms, double *sweep_grid_m
     RP_API_END(h)
 }
 
+rp_status rp_neighbour_stats(rp_handle *h, double *candidates_per_centre, double *within_range_per_centre) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(h->hasInteraction && h->n > 0 && candidates_per_centre && within_range_per_centre,
+              "packing and interaction must be set");
+    neighbourStats(h, candidates_per_centre, within_range_per_centre);
+    RP_API_END(h)
+}
+
+rp_status rp_measure_fp64_peak(rp_handle *h, double *dfma_gflops, double *dmul_dadd_gflops) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(dfma_gflops && dmul_dadd_gflops, "output pointers must not be NULL");
+    fp64Peak(h, dfma_gflops, dmul_dadd_gflops);
+    RP_API_END(h)
+}
+
 rp_status rp_launch_count(rp_handle *h, uint64_t *launches_out) {
     RP_API_BEGIN(h)
     *launches_out = h->launches;

@@ -206,6 +206,9 @@ void acceptMove(Handle *h);
 double tryScaling(Handle *h, const Box &newBox);
 void revertScaling(Handle *h);
 void pairTestBatch(Handle *h, const rp_pair *pairs, unsigned long long n, unsigned char *verdict, double *energy);
+// ---- rp_stats.cu ----
+void neighbourStats(Handle *h, double *kCand, double *kFull);
+void fp64Peak(Handle *h, double *dfmaGflops, double *dmulDaddGflops);
 // ---- rp_sweep.cu ----
 void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out);
 

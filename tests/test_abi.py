@@ -1,0 +1,60 @@
+"""CPU tests of the drop-in boundary: librampack_b200.so builds, loads and exports exactly what include/*.h declares;
+no compute entry point is called (there is no GPU here) except to check that they fail loudly without a device."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+import rampack_b200 as rp
+from rampack_b200 import capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    text = open(os.path.join(ROOT, "include", "rampack_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(rp_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = C.CDLL(capi.library_path()) if os.path.exists(capi.library_path()) else capi.load()
+    declared = header_symbols()
+    assert len(declared) >= 24
+    for name in declared:
+        assert hasattr(lib, name), f"{name} is declared in include/rampack_b200.h but not exported"
+    assert sorted(capi.SYMBOLS) == declared, "rampack_b200/capi.py SYMBOLS and the header disagree"
+
+
+def test_struct_layouts_match_header():
+    # sizes implied by include/rampack_b200.h (all members naturally aligned)
+    assert C.sizeof(capi.InteractionDesc) == 8 + 4 * 8 + 8 + 16 * 3 * 8 + 16 * 8 + 16 * 3 * 8
+    assert C.sizeof(capi.Config) == 24
+    assert C.sizeof(capi.Move) == 16 + 12 * 8
+    assert C.sizeof(capi.SweepParams) == 8 + 4 * 8
+    assert C.sizeof(capi.SweepCounters) == 6 * 8
+    assert capi.PAIR_DTYPE.itemsize == 29 * 8
+    assert C.sizeof(capi.GridInfo) == 4 * 4 + 8 + 8 + 8
+
+
+def test_version_and_no_cpu_fallback():
+    lib = capi.load()
+    assert b"sm_100a" in lib.rp_version()
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a device is present; the no-device path cannot be exercised")
+    with pytest.raises(rp.RpError) as e:
+        rp.Device(device=0)
+    assert e.value.status == capi.RP_ERR_CUDA
+    assert "no CPU fallback" in e.value.message
+
+
+def test_product_path_does_not_touch_the_oracle():
+    """rampack_b200/ must not import, link or load anything under oracle/ (oracle = checker only)."""
+    pkg = os.path.join(ROOT, "rampack_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".hpp")):
+                text = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert "oracle" not in text.replace("test oracle", ""), f"{f} mentions oracle/"

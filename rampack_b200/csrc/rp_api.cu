@@ -228,7 +228,7 @@ void rp_destroy(rp_handle *h) {
     for (void *p : {(void *) h->dInter, (void *) h->pos, (void *) h->orient, (void *) h->crel, (void *) h->cabs,
                     (void *) h->lastPos, (void *) h->lastCabs, (void *) h->tmpState, (void *) h->dCounters,
                     (void *) h->dFlags, (void *) h->dCellEnergy, (void *) h->dMoveOut, h->dStage,
-                    (void *) h->sweepMoved})
+                    (void *) h->sweepMoved, (void *) h->trialRec, (void *) h->trialOrient, h->trialMeta})
         if (p) cudaFree(p);
     if (h->stage) cudaFreeHost(h->stage);
     freeGrid(h->grid);

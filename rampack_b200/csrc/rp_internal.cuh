@@ -124,8 +124,12 @@ struct Handle {
     bool gridDirty = true;
     // sweep grid (random origin, particle mass centres, even cell counts)
     GridStore sgrid;
-    int *sweepMoved = nullptr;    // per sorted slot: accepted in this cycle
+    int *sweepMoved = nullptr;    // (unused)
     size_t sweepMovedCap = 0;
+    // trials of one rp_sweep call, per sorted slot: record (6 doubles), new orientation (9 doubles), meta (uint2)
+    double *trialRec = nullptr, *trialOrient = nullptr;
+    void *trialMeta = nullptr;
+    size_t trialCap = 0;
 
     // explicit trial move (Packing's temp slot): pos[3] orient[9] crel[16][3] cabs[16][3]
     double *tmpState = nullptr;

@@ -1,0 +1,179 @@
+// rp_sweep_kernel.cuh — the checkerboard sub-sweep kernels (north_star kernel (b)); included by rp_sweep.cu only.
+//
+// k_sweep_trials  one thread per particle, once per rp_sweep call: draws the trial move of every particle from its
+//                 Philox stream (MoveSampler distributions), applies the active-domain rule and stores the trial
+//                 record {new position, new half axis}, the new orientation and {reject flag, order key}.
+// k_sweep         one CTA per ACTIVE cell of the current colour (8 launches per rp_sweep call):
+//   stage   the 27 cells around the active cell (9 x-runs, contiguous in the cell-sorted order) and the trial
+//           records of the own cell are pulled into shared memory with 1-D TMA bulk copies (cp.async.bulk +
+//           mbarrier); a second pass adds the lattice translations (pos2 + translation, as the reference's
+//           HardcodedTranslation) and makes an FP32 copy of the positions in cell-local coordinates;
+//   phase A conservative FP32 cull of ALL (trial, candidate) pairs — candidates are the staged OLD states plus the
+//           NEW states of the other trials of the cell; a lane owns a candidate and builds a bitmask over trials;
+//           survivors are appended to one CTA-wide queue;
+//   phase B the queue is processed by all threads in lock step: exact FP64 pair test (reference operation order,
+//           -fmad=false); results: "hits a frozen particle" flags and two bit matrices ownMask[i] (trial i vs OLD
+//           state of own j) and newMask[i] (trial i vs NEW state of own j);
+//   phase C the trials of the cell are resolved sequentially in a random order from the bit matrices alone: trial i
+//           is accepted iff it hits no frozen particle, no unmoved own particle (ownMask & ~moved) and no already
+//           moved own particle (newMask & moved) — exactly a sequential Monte Carlo pass through the cell with the
+//           reference's accept rule (Simulation.cpp:483 with dE in {0, +inf});
+//   write   accepted states go back to the sorted records and to the canonical SoA arrays.
+//
+// The FP32 cull never decides a verdict: a pair it drops is farther apart than the pair function's range by more
+// than the proven FP32 error bound (cullThr2, computed on the host), so the FP64 test would return "disjoint".
+#pragma once
+
+#include "rp_internal.cuh"
+#include "rp_philox.cuh"
+
+namespace rp {
+
+struct SweepGrid {
+    int n[3];
+    double relCell[3];     // 1 / n[i]
+    double shift[3];       // random relative origin s
+    V3 imageShift[8];      // M * f for f = (fx, fy, fz) in {0,1}^3, index fx + 2 fy + 4 fz
+    V3 trans[27];
+};
+
+constexpr int SW_MAXOWN = 64;      // trials resolved together (bit matrices are 64 bits wide)
+constexpr int SW_QCAP = 2048;      // CTA-wide queue of (trial, candidate) pairs awaiting the exact test
+
+struct SweepArgs {
+    int kind;                   // rp_move_kind
+    double transStep, rotStep;
+    unsigned long long seed;
+    unsigned int cycle, pass;
+    int colour[3];              // parity of the active cells per axis
+    int nActive[3];             // active cells per axis
+    int capOld;                 // capacity of the staged old states (max 27-neighbourhood population)
+    int capOwn;                 // capacity of the trial region (max cell population)
+    float cullThr2;             // FP32 cull threshold: range^2 plus the FP32 error bound
+    size_t cap;
+};
+
+// device buffers of the trials of one rp_sweep call, indexed by the sorted slot
+struct TrialBuffers {
+    double *rec;                // 6 doubles per slot: new position (image frame), new half axis
+    double *orient;             // 9 doubles per slot: new orientation (only written for rotating samplers)
+    uint2 *meta;                // x: 0 alive / 2 left the cell, y: random key of the processing order
+};
+
+// ---- 1-D TMA bulk copy + mbarrier (PTX ISA: cp.async.bulk, mbarrier) ----
+__device__ __forceinline__ unsigned int smemAddr(const void *p) {
+    return static_cast<unsigned int>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbarInit(unsigned long long *bar, unsigned int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smemAddr(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbarExpectTx(unsigned long long *bar, unsigned int bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smemAddr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulkCopyG2S(void *dst, const void *src, unsigned int bytes, unsigned long long *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smemAddr(dst)), "l"(src), "r"(bytes), "r"(smemAddr(bar)) : "memory");
+}
+__device__ __forceinline__ void mbarWait(unsigned long long *bar, unsigned int phase) {
+    unsigned int done = 0;
+    while (!done) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(smemAddr(bar)), "r"(phase) : "memory");
+    }
+}
+
+// per-trial data of the exact test: position, half axis and (spherocylinders) the cap centres of the trial
+struct TrialRec {
+    double px, py, pz, hx, hy, hz;
+    double s1x, s1y, s1z, s2x, s2y, s2z;     // cap centres pos - h, pos + h (SpherocylinderTraits.cpp:24-26)
+};
+
+// Exact pair test of trial `t` against a staged candidate record (position already translated).
+// Spherocylinder: SpherocylinderTraits::overlapBetween (SpherocylinderTraits.cpp:28-46); the cap centres
+// pos + axis * (0.5 * -+1 * l) are formed as pos -+ h with h = axis * (0.5 * l): bit-identical because
+// axis * (-x) == -(axis * x) and a + (-b) == a - b in IEEE arithmetic.
+template <int HARD>
+__device__ __forceinline__ bool exactOverlap(const Inter &I, const TrialRec &t, const double *__restrict__ c) {
+    V3 p1 = v3(t.px, t.py, t.pz), p2 = v3(c[0], c[1], c[2]);
+    double d2 = norm2(p2 - p1);
+    if (HARD == RP_HARD_SPHERE) return d2 < I.sphereThr2;
+    if (d2 < I.scInner2) return true;
+    if (d2 >= I.scOuter2) return false;
+    V3 h2 = v3(c[3], c[4], c[5]);
+    double s = segmentDistance2(v3(t.s1x, t.s1y, t.s1z), v3(t.s2x, t.s2y, t.s2z), p2 - h2, p2 + h2);
+    return s < I.scInner2;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// trial moves of all particles: MoveSampler::sampleMove distributions (core/move_samplers/*.cpp), Shape::translate /
+// rotate (core/Shape.cpp:9-16), ActiveDomain::isInside with the checkerboard cell as the domain (Packing.cpp:95-96)
+// ---------------------------------------------------------------------------------------------------------------
+template <int HARD>
+__global__ void __launch_bounds__(128) k_sweep_trials(int n, SweepArgs A, SweepGrid sg, Box box, double halfLength,
+                                                      const int *__restrict__ items, const int *__restrict__ keys,
+                                                      const double *__restrict__ rec,
+                                                      const double *__restrict__ orient, TrialBuffers T)
+{
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n) return;
+    const int particleId = items[slot];
+    const int cell = keys[particleId] & 0x0FFFFFFF;
+    const int cc[3] = {cell % sg.n[0], (cell / sg.n[0]) % sg.n[1], cell / (sg.n[0] * sg.n[1])};
+    const double *r = rec + 6 * static_cast<size_t>(slot);
+    V3 p = v3(r[0], r[1], r[2]);
+    V3 h = v3(r[3], r[4], r[5]);
+    const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION);
+    const bool translated = (A.kind == RP_MOVE_TRANSLATION || A.kind == RP_MOVE_ROTOTRANSLATION);
+    Rng rng;
+    rng.init(A.seed, static_cast<unsigned int>(particleId), A.cycle, A.pass);
+    unsigned int rej = 0;
+    if (translated) {
+        // TranslationSampler / RototranslationSampler: 3 x U(-step, step)  (RototranslationSampler.cpp:31-33)
+        double tx = rng.uniform(-A.transStep, A.transStep);
+        double ty = rng.uniform(-A.transStep, A.transStep);
+        double tz = rng.uniform(-A.transStep, A.transStep);
+        p = p + v3(tx, ty, tz);
+        // the new mass centre must stay in its cell (image frame of the shifted origin)
+        V3 rel = absToRel(box, p);
+        double q[3] = {rel.x - sg.shift[0], rel.y - sg.shift[1], rel.z - sg.shift[2]};
+        for (int d = 0; d < 3; d++) {
+            if (q[d] < 0 || q[d] >= 1) rej = 2;
+            else if (static_cast<int>(q[d] / sg.relCell[d]) != cc[d]) rej = 2;
+        }
+    }
+    if (rotated) {
+        // axis uniform in the unit ball by rejection, angle U(-a, a) (RototranslationSampler.cpp:35-43);
+        // Rodrigues: identity + K*sina + ((1 - cosa)*K)*K (geometry/Matrix.tpp:437-449)
+        V3 axis;
+        double n2;
+        do {
+            axis = v3(rng.uniform(-1, 1), rng.uniform(-1, 1), rng.uniform(-1, 1));
+            n2 = norm2(axis);
+        } while (n2 > 1 || n2 == 0);
+        double nrm = sqrt(n2);
+        axis = v3(axis.x / nrm, axis.y / nrm, axis.z / nrm);
+        double angle = rng.uniform(-A.rotStep, A.rotStep);
+        double sina = sin(angle), cosa = cos(angle);
+        M33 K = {{0, -axis.z, axis.y, axis.z, 0, -axis.x, -axis.y, axis.x, 0}};
+        M33 sK;
+        for (int q = 0; q < 9; q++) sK.a[q] = (1 - cosa) * K.a[q];
+        M33 KK = mul(sK, K);
+        M33 R;
+        for (int q = 0; q < 9; q++) R.a[q] = (((q % 4 == 0) ? 1.0 : 0.0) + K.a[q] * sina) + KK.a[q];
+        M33 O;
+        for (int q = 0; q < 9; q++) O.a[q] = orient[q * A.cap + particleId];
+        M33 newOrient = mul(R, O);     // Shape::rotate (core/Shape.cpp:14-16)
+        if (HARD == RP_HARD_SPHEROCYLINDER) h = column(newOrient, 2) * halfLength;
+        double *o = T.orient + 9 * static_cast<size_t>(slot);
+        for (int q = 0; q < 9; q++) o[q] = newOrient.a[q];
+    }
+    double *t = T.rec + 6 * static_cast<size_t>(slot);
+    t[0] = p.x; t[1] = p.y; t[2] = p.z; t[3] = h.x; t[4] = h.y; t[5] = h.z;
+    rng.ctr.w = 0x40000000u;     // separate sub-stream for the processing order
+    T.meta[slot] = make_uint2(rej, philox4x32(rng.ctr, rng.k0, rng.k1).x);
+}
+
+}  // namespace rp
+
+#include "rp_sweep_kernel2.cuh"

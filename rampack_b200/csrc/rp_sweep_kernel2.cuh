@@ -1,0 +1,301 @@
+// rp_sweep_kernel2.cuh — k_sweep, the per-colour sub-sweep kernel (see rp_sweep_kernel.cuh for the overview)
+#pragma once
+
+namespace rp {
+
+template <int HARD, int THREADS>
+__global__ void __launch_bounds__(THREADS, 512 / THREADS)
+k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, const int *__restrict__ cellStart,
+        const int *__restrict__ items, double *__restrict__ rec, TrialBuffers T, double *__restrict__ pos,
+        double *__restrict__ orient, unsigned long long *__restrict__ counters, int *__restrict__ flags)
+{
+    constexpr int WARPS = THREADS / 32;
+    extern __shared__ __align__(16) unsigned char smemRaw[];
+    __shared__ Inter I;
+    __shared__ TrialRec trial[SW_MAXOWN];
+    __shared__ float4 trialF[SW_MAXOWN];
+    __shared__ unsigned long long ownMask[SW_MAXOWN], newMask[SW_MAXOWN], seqOwn[SW_MAXOWN], seqNew[SW_MAXOWN];
+    __shared__ unsigned int orderKey[SW_MAXOWN];
+    __shared__ int seqInfo[SW_MAXOWN];
+    __shared__ int rejected[SW_MAXOWN];     // 0 = alive, 1 = overlap with a frozen particle, 2 = left the cell
+    __shared__ unsigned long long sAccepted, sRejMask, sBar;
+    __shared__ int cellBegin[28], cellSrc[27], cellT[27];
+    __shared__ int sStats[3];
+    __shared__ int qCount;
+
+    // dynamic shared memory: FP64 records (old states, then the trial = new states of the own cell), the FP32
+    // cell-local positions (SoA), the CTA queue
+    const int capCand = A.capOld + A.capOwn;
+    double *cand = reinterpret_cast<double *>(smemRaw);
+    float *cfx = reinterpret_cast<float *>(cand + 6 * static_cast<size_t>(capCand));
+    float *cfy = cfx + capCand, *cfz = cfy + capCand;
+    unsigned int *queue = reinterpret_cast<unsigned int *>(cfz + capCand);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < static_cast<int>(sizeof(Inter) / sizeof(int)); i += THREADS)
+        reinterpret_cast<int *>(&I)[i] = reinterpret_cast<const int *>(interPtr)[i];
+
+    // active cell of this CTA
+    const int b = blockIdx.x;
+    const int a0 = b % A.nActive[0], a1 = (b / A.nActive[0]) % A.nActive[1], a2 = b / (A.nActive[0] * A.nActive[1]);
+    const int cx = 2 * a0 + A.colour[0], cy = 2 * a1 + A.colour[1], cz = 2 * a2 + A.colour[2];
+    const int ownCell = (cz * sg.n[1] + cy) * sg.n[0] + cx;
+
+    // neighbour code c = (dz+1)*9 + (dy+1)*3 + (dx+1): the three cells of an x-run are adjacent in the staging area
+    // exactly as they are in the cell-sorted global order (cells are flattened x-fastest)
+    if (tid < 27) {
+        int tIdx;
+        int c2 = neighbourCell(sg.n, cx, cy, cz, tid % 3 - 1, (tid / 3) % 3 - 1, tid / 9 - 1, &tIdx);
+        cellSrc[tid] = cellStart[c2];
+        cellBegin[tid] = cellStart[c2 + 1] - cellStart[c2];     // count, turned into an offset below
+        cellT[tid] = tIdx;
+    }
+    if (tid == 0) {
+        sStats[0] = 0; sStats[1] = 0; sStats[2] = 0;
+        mbarInit(&sBar, 1);
+    }
+    __syncthreads();
+    const int ownStartAll = cellStart[ownCell];
+    if (tid == 0) {
+        int off = 0;
+        for (int c = 0; c < 27; c++) { int cnt = cellBegin[c]; cellBegin[c] = off; off += cnt; }
+        cellBegin[27] = off;
+        const int numOwnT = cellBegin[14] - cellBegin[13];
+        if (numOwnT > 0 && off <= A.capOld && numOwnT <= A.capOwn) {
+            // 1-D TMA bulk copies: merged runs of cells that are contiguous in the sorted order + the own trials
+            mbarExpectTx(&sBar, static_cast<unsigned int>((off + numOwnT) * 48));
+            int runSrc = -1, runDst = 0, runCnt = 0;
+            for (int c = 0; c < 27; c++) {
+                const int cnt = cellBegin[c + 1] - cellBegin[c];
+                if (cnt == 0) continue;
+                if (runCnt > 0 && cellSrc[c] == runSrc + runCnt) { runCnt += cnt; continue; }
+                if (runCnt > 0)
+                    bulkCopyG2S(cand + 6 * static_cast<size_t>(runDst), rec + 6 * static_cast<size_t>(runSrc),
+                                static_cast<unsigned int>(runCnt * 48), &sBar);
+                runSrc = cellSrc[c]; runDst = cellBegin[c]; runCnt = cnt;
+            }
+            if (runCnt > 0)
+                bulkCopyG2S(cand + 6 * static_cast<size_t>(runDst), rec + 6 * static_cast<size_t>(runSrc),
+                            static_cast<unsigned int>(runCnt * 48), &sBar);
+            bulkCopyG2S(cand + 6 * static_cast<size_t>(off), T.rec + 6 * static_cast<size_t>(ownStartAll),
+                        static_cast<unsigned int>(numOwnT * 48), &sBar);
+        }
+    }
+    __syncthreads();
+    const int numOld = cellBegin[27], ownBeginAll = cellBegin[13], numOwnAll = cellBegin[14] - cellBegin[13];
+    if (numOwnAll == 0) return;
+    if (numOld > A.capOld || numOwnAll > A.capOwn) {
+        if (tid == 0) atomicOr(&flags[3], 1);
+        return;
+    }
+
+    // origin of the FP32 local frame: centre of the active cell (image frame)
+    const V3 origin = relToAbs(box, v3((cx + 0.5) * sg.relCell[0] + sg.shift[0], (cy + 0.5) * sg.relCell[1] + sg.shift[1],
+                                       (cz + 0.5) * sg.relCell[2] + sg.shift[2]));
+    mbarWait(&sBar, 0);
+
+    // ---- second staging pass (shared memory only): pos2 + lattice translation, FP32 local copy ----
+    for (int c = warp; c < 27; c += WARPS) {
+        const int begin = cellBegin[c], cnt = cellBegin[c + 1] - begin;
+        const V3 t = sg.trans[cellT[c]];
+        for (int j = begin + lane; j < begin + cnt; j += 32) {
+            double *r = cand + 6 * static_cast<size_t>(j);
+            double x = r[0] + t.x, y = r[1] + t.y, z = r[2] + t.z;
+            r[0] = x; r[1] = y; r[2] = z;
+            cfx[j] = static_cast<float>(x - origin.x);
+            cfy[j] = static_cast<float>(y - origin.y);
+            cfz[j] = static_cast<float>(z - origin.z);
+        }
+    }
+    for (int j = numOld + tid; j < numOld + numOwnAll; j += THREADS) {
+        const double *r = cand + 6 * static_cast<size_t>(j);
+        cfx[j] = static_cast<float>(r[0] - origin.x);
+        cfy[j] = static_cast<float>(r[1] - origin.y);
+        cfz[j] = static_cast<float>(r[2] - origin.z);
+    }
+
+    const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION);
+    const bool translated = (A.kind == RP_MOVE_TRANSLATION || A.kind == RP_MOVE_ROTOTRANSLATION);
+
+    // A cell with more than SW_MAXOWN particles is processed in batches of SW_MAXOWN trials; the particles of the
+    // other batches are frozen candidates meanwhile (their accepted states are patched into shared memory).
+    for (int batch0 = 0; batch0 < numOwnAll; batch0 += SW_MAXOWN) {
+        const int numOwn = min(SW_MAXOWN, numOwnAll - batch0);
+        const int ownBegin = ownBeginAll + batch0, ownStart = ownStartAll + batch0;
+        const int newBegin = numOld + batch0;          // new states of this batch's trials inside cand[]
+        const int numCand = numOld + numOwn;
+
+        if (tid == 0) { sAccepted = 0ull; sRejMask = 0ull; qCount = 0; }
+        __syncthreads();       // staging passes done (first batch) / previous batch fully written back
+        if (tid < numOwn) {
+            const uint2 meta = T.meta[ownStart + tid];
+            const double *r = cand + 6 * static_cast<size_t>(newBegin + tid);
+            TrialRec &t = trial[tid];
+            V3 p = v3(r[0], r[1], r[2]), h = v3(r[3], r[4], r[5]);
+            t.px = p.x; t.py = p.y; t.pz = p.z; t.hx = h.x; t.hy = h.y; t.hz = h.z;
+            V3 s1 = p - h, s2 = p + h;
+            t.s1x = s1.x; t.s1y = s1.y; t.s1z = s1.z; t.s2x = s2.x; t.s2y = s2.y; t.s2z = s2.z;
+            trialF[tid] = make_float4(cfx[newBegin + tid], cfy[newBegin + tid], cfz[newBegin + tid], 0.f);
+            rejected[tid] = static_cast<int>(meta.x);
+            orderKey[tid] = meta.y;
+            ownMask[tid] = 0ull;
+            newMask[tid] = 0ull;
+            if (meta.x) atomicOr(&sRejMask, 1ull << tid);
+        }
+        __syncthreads();
+
+        volatile int *vrej = rejected;
+        auto exactTest = [&](unsigned int e) {
+            const int ti = e >> 16, cj = e & 0xffff;
+            if (vrej[ti]) return;
+            if (exactOverlap<HARD>(I, trial[ti], cand + 6 * static_cast<size_t>(cj))) {
+                if (cj >= numOld) atomicOr(&newMask[ti], 1ull << (cj - newBegin));
+                else {
+                    const int o = cj - ownBegin;
+                    if (o >= 0 && o < numOwn) atomicOr(&ownMask[ti], 1ull << o);
+                    else vrej[ti] = 1;
+                }
+            }
+        };
+
+        // ---- phase A: FP32 cull, survivors -> CTA queue ----
+        {
+            const float thrF = A.cullThr2;
+            const unsigned long long dead = sRejMask;
+            for (int base = warp * 32; base < numCand; base += WARPS * 32) {
+                const int jj = base + lane;
+                const bool valid = jj < numCand;
+                const int j = jj < numOld ? jj : jj + batch0;
+                // a far-away dummy for the invalid slots keeps the loop branch-free
+                float cxf = 1e18f, cyf = 0.f, czf = 0.f;
+                if (valid) { cxf = cfx[j]; cyf = cfy[j]; czf = cfz[j]; }
+                unsigned int mlo = 0, mhi = 0;
+                {
+                    const int nlo = min(numOwn, 32);
+                    unsigned int bit = 1;
+                    #pragma unroll 4
+                    for (int i = 0; i < nlo; i++) {
+                        const float4 tf = trialF[i];
+                        float dx = cxf - tf.x, dy = cyf - tf.y, dz = czf - tf.z;
+                        float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                        if (d2 < thrF) mlo |= bit;
+                        bit <<= 1;
+                    }
+                    bit = 1;
+                    #pragma unroll 4
+                    for (int i = 32; i < numOwn; i++) {
+                        const float4 tf = trialF[i];
+                        float dx = cxf - tf.x, dy = cyf - tf.y, dz = czf - tf.z;
+                        float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                        if (d2 < thrF) mhi |= bit;
+                        bit <<= 1;
+                    }
+                }
+                unsigned long long m = (static_cast<unsigned long long>(mhi) << 32) | mlo;
+                // never test a particle against itself (old or new state); drop trials that left their cell
+                const int o = j - ownBegin, nw = j - newBegin;
+                if (o >= 0 && o < numOwn) m &= ~(1ull << o);
+                if (nw >= 0 && nw < numOwn) m &= ~(1ull << nw);
+                m &= ~dead;
+
+                const int cnt = __popcll(m);
+                int incl = cnt;
+                #pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    int v = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (lane >= d) incl += v;
+                }
+                const int total = __shfl_sync(0xffffffffu, incl, 31);
+                if (total == 0) continue;
+                int off = 0;
+                if (lane == 0) off = atomicAdd(&qCount, total);
+                off = __shfl_sync(0xffffffffu, off, 0) + incl - cnt;
+                while (m) {
+                    const int i = __ffsll(static_cast<long long>(m)) - 1;
+                    m &= m - 1;
+                    const unsigned int e = (static_cast<unsigned int>(i) << 16) | static_cast<unsigned int>(j);
+                    if (off < SW_QCAP) queue[off] = e;
+                    else exactTest(e);       // queue overflow (very dense cells): test in place
+                    off++;
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- phase B: exact FP64 tests, all threads in lock step over the queue ----
+        {
+            const int qn = min(qCount, SW_QCAP);
+            for (int e = tid; e < qn; e += THREADS) exactTest(queue[e]);
+        }
+        // ---- phase C: sequential resolution inside the cell, random order, from the bit matrices ----
+        int rank = 0;
+        if (tid < numOwn) {
+            const unsigned int k = orderKey[tid];
+            for (int j = 0; j < numOwn; j++) {
+                const unsigned int kj = orderKey[j];
+                rank += (kj < k) || (kj == k && j < tid);
+            }
+        }
+        __syncthreads();
+        if (tid < numOwn) {
+            seqOwn[rank] = ownMask[tid];
+            seqNew[rank] = newMask[tid];
+            seqInfo[rank] = (rejected[tid] << 8) | tid;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            unsigned long long moved = 0ull;
+            int nAcc = 0, nRejDomain = 0, nRejOverlap = 0;
+            #pragma unroll 4
+            for (int step = 0; step < numOwn; step++) {
+                const int info = seqInfo[step];
+                const unsigned long long blockers = (seqOwn[step] & ~moved) | (seqNew[step] & moved);
+                const int r = info >> 8;
+                if (r == 2) nRejDomain++;
+                else if (r == 1 || blockers != 0ull) nRejOverlap++;
+                else {
+                    // hard interactions only: Metropolis u <= exp(-0/T) always accepts (Simulation.cpp:483)
+                    moved |= 1ull << (info & 0xff);
+                    nAcc++;
+                }
+            }
+            sAccepted = moved;
+            sStats[0] += nAcc; sStats[1] += nRejDomain; sStats[2] += nRejOverlap;
+        }
+        __syncthreads();
+
+        // ---- write-back of the accepted moves: sorted record (image frame) and canonical arrays (wrapped) ----
+        if (tid < numOwn && ((sAccepted >> tid) & 1ull)) {
+            const TrialRec &t = trial[tid];
+            const int particleId = items[ownStart + tid];
+            double *r = rec + 6 * static_cast<size_t>(ownStart + tid);
+            r[0] = t.px; r[1] = t.py; r[2] = t.pz; r[3] = t.hx; r[4] = t.hy; r[5] = t.hz;
+            if (batch0 + SW_MAXOWN < numOwnAll) {
+                // later batches see this particle as a frozen candidate in its new state (own cell: no translation)
+                double *cs = cand + 6 * static_cast<size_t>(ownBegin + tid);
+                cs[0] = t.px; cs[1] = t.py; cs[2] = t.pz; cs[3] = t.hx; cs[4] = t.hy; cs[5] = t.hz;
+                cfx[ownBegin + tid] = trialF[tid].x; cfy[ownBegin + tid] = trialF[tid].y;
+                cfz[ownBegin + tid] = trialF[tid].z;
+            }
+            if (translated) {
+                // Shape::translate (core/Shape.cpp:9-12): position += bc.getCorrection(position)
+                V3 np = v3(t.px, t.py, t.pz);
+                V3 p = np + pbcCorrection(box, np);
+                pos[particleId] = p.x; pos[A.cap + particleId] = p.y; pos[2 * A.cap + particleId] = p.z;
+            }
+            if (rotated) {
+                const double *o = T.orient + 9 * static_cast<size_t>(ownStart + tid);
+                for (int q = 0; q < 9; q++) orient[q * A.cap + particleId] = o[q];
+            }
+        }
+    }   // batches
+
+    if (tid == 0) {
+        atomicAdd(&counters[0], static_cast<unsigned long long>(numOwnAll));
+        atomicAdd(&counters[1], static_cast<unsigned long long>(sStats[0]));
+        atomicAdd(&counters[2], static_cast<unsigned long long>(sStats[1]));
+        atomicAdd(&counters[3], static_cast<unsigned long long>(sStats[2]));
+    }
+}
+
+}  // namespace rp

@@ -263,3 +263,31 @@ def test_sweep_is_deterministic(device):
             device.sweep(rp.RP_MOVE_ROTOTRANSLATION, 0.2, 0.1, cycle)
         results.append(device.download()[1].copy())
     assert np.array_equal(results[0], results[1])
+
+
+def test_sweep_fp32_cull_never_changes_a_verdict(device, monkeypatch):
+    """The conservative FP32 cull of the sweep kernel must be invisible: with the cull disabled (every pair takes the
+    exact FP64 test) the trajectories are bit-identical."""
+    tric = np.array([[16 * 1.2, 3.0, 1.0], [0, 16 * 1.2, -2.0], [0, 0, 5 * 6.5]])
+    for box, shapes in (H.sc_lattice((16, 16, 5)), (tric, None)):
+        if shapes is None:
+            _, lat = H.sc_lattice((16, 16, 5))
+            rel = lat[:, :3] / np.array([16 * 1.2, 16 * 1.2, 5 * 6.5])
+            shapes = lat.copy()
+            shapes[:, :3] = rel @ box.T
+        results = []
+        for no_cull in (False, True):
+            if no_cull:
+                monkeypatch.setenv("RP_SWEEP_NO_CULL", "1")
+            else:
+                monkeypatch.delenv("RP_SWEEP_NO_CULL", raising=False)
+            device.set_interaction(H.desc_sc())
+            device.upload(box, shapes)
+            acc = 0
+            for cycle in range(6):
+                acc += device.sweep(rp.RP_MOVE_ROTOTRANSLATION, 0.25, 0.15, cycle).accepted
+            results.append((acc, device.download()[1].copy()))
+        monkeypatch.delenv("RP_SWEEP_NO_CULL", raising=False)
+        assert results[0][0] == results[1][0] > 0
+        assert np.array_equal(results[0][1], results[1][1])
+        assert device.count_total_overlaps(False) == 0

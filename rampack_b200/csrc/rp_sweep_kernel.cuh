@@ -49,7 +49,8 @@ struct SweepArgs {
     int nActive[3];             // active cells per axis
     int capOld;                 // capacity of the staged old states (max 27-neighbourhood population)
     int capOwn;                 // capacity of the trial region (max cell population)
-    float cullThr2;             // FP32 cull threshold: range^2 plus the FP32 error bound
+    float cullThr2;             // FP32 cull threshold (squared distance) including the FP32 error bound
+    float cullHalf;             // spherocylinders: half length of the axis segment
     size_t cap;
 };
 

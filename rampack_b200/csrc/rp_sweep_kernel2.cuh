@@ -13,7 +13,7 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
     extern __shared__ __align__(16) unsigned char smemRaw[];
     __shared__ Inter I;
     __shared__ TrialRec trial[SW_MAXOWN];
-    __shared__ float4 trialF[SW_MAXOWN];
+    __shared__ float4 trialF[SW_MAXOWN], trialU[SW_MAXOWN];
     __shared__ unsigned long long ownMask[SW_MAXOWN], newMask[SW_MAXOWN], seqOwn[SW_MAXOWN], seqNew[SW_MAXOWN];
     __shared__ unsigned int orderKey[SW_MAXOWN];
     __shared__ int seqInfo[SW_MAXOWN];
@@ -136,6 +136,9 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
             V3 s1 = p - h, s2 = p + h;
             t.s1x = s1.x; t.s1y = s1.y; t.s1z = s1.z; t.s2x = s2.x; t.s2y = s2.y; t.s2z = s2.z;
             trialF[tid] = make_float4(cfx[newBegin + tid], cfy[newBegin + tid], cfz[newBegin + tid], 0.f);
+            if (HARD == RP_HARD_SPHEROCYLINDER)      // FP32 unit axis of the trial for the capsule cull
+                trialU[tid] = make_float4(static_cast<float>(h.x / I.scHalfPlus), static_cast<float>(h.y / I.scHalfPlus),
+                                          static_cast<float>(h.z / I.scHalfPlus), 0.f);
             rejected[tid] = static_cast<int>(meta.x);
             orderKey[tid] = meta.y;
             ownMask[tid] = 0ull;
@@ -158,74 +161,87 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
             }
         };
 
-        // ---- phase A: FP32 cull, survivors -> CTA queue ----
+        // ---- phases A + B in rounds over super-chunks of candidates ----
+        // A: conservative FP32 cull (spheres: centre distance; spherocylinders: distance of the candidate's centre
+        //    from the trial's axis segment, a necessary condition for the segments to come closer than 2r), survivors
+        //    are appended to the CTA queue;  B: exact FP64 tests, all threads in lock step over the queue.  Between
+        //    rounds only full multiples of THREADS are consumed, so every lane stays busy.
         {
-            const float thrF = A.cullThr2;
+            const float thrF = A.cullThr2, halfF = A.cullHalf;
             const unsigned long long dead = sRejMask;
-            for (int base = warp * 32; base < numCand; base += WARPS * 32) {
-                const int jj = base + lane;
-                const bool valid = jj < numCand;
-                const int j = jj < numOld ? jj : jj + batch0;
-                // a far-away dummy for the invalid slots keeps the loop branch-free
-                float cxf = 1e18f, cyf = 0.f, czf = 0.f;
-                if (valid) { cxf = cfx[j]; cyf = cfy[j]; czf = cfz[j]; }
-                unsigned int mlo = 0, mhi = 0;
-                {
-                    const int nlo = min(numOwn, 32);
-                    unsigned int bit = 1;
-                    #pragma unroll 4
-                    for (int i = 0; i < nlo; i++) {
-                        const float4 tf = trialF[i];
-                        float dx = cxf - tf.x, dy = cyf - tf.y, dz = czf - tf.z;
-                        float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-                        if (d2 < thrF) mlo |= bit;
-                        bit <<= 1;
+            constexpr int SUPER = THREADS * 4;
+            for (int sbase = 0; sbase < numCand; sbase += SUPER) {
+                const int send = min(numCand, sbase + SUPER);
+                for (int base = sbase + warp * 32; base < send; base += WARPS * 32) {
+                    const int jj = base + lane;
+                    const bool valid = jj < send;
+                    const int j = jj < numOld ? jj : jj + batch0;
+                    // a far-away dummy for the invalid slots keeps the loop branch-free
+                    float cxf = 1e18f, cyf = 0.f, czf = 0.f;
+                    if (valid) { cxf = cfx[j]; cyf = cfy[j]; czf = cfz[j]; }
+                    unsigned int mlo = 0, mhi = 0;
+                    #pragma unroll
+                    for (int half = 0; half < 2; half++) {
+                        const int i0 = half * 32, i1 = min(numOwn, i0 + 32);
+                        unsigned int bit = 1, mm = 0;
+                        #pragma unroll 4
+                        for (int i = i0; i < i1; i++) {
+                            const float4 tf = trialF[i];
+                            float dx = cxf - tf.x, dy = cyf - tf.y, dz = czf - tf.z;
+                            float d2;
+                            if (HARD == RP_HARD_SPHEROCYLINDER) {
+                                const float4 tu = trialU[i];
+                                float s = fmaf(dz, tu.z, fmaf(dy, tu.y, dx * tu.x));
+                                s = fminf(fmaxf(s, -halfF), halfF);
+                                float rx = fmaf(-s, tu.x, dx), ry = fmaf(-s, tu.y, dy), rz = fmaf(-s, tu.z, dz);
+                                d2 = fmaf(rz, rz, fmaf(ry, ry, rx * rx));
+                            } else {
+                                d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                            }
+                            if (d2 < thrF) mm |= bit;
+                            bit <<= 1;
+                        }
+                        if (half == 0) mlo = mm; else mhi = mm;
                     }
-                    bit = 1;
-                    #pragma unroll 4
-                    for (int i = 32; i < numOwn; i++) {
-                        const float4 tf = trialF[i];
-                        float dx = cxf - tf.x, dy = cyf - tf.y, dz = czf - tf.z;
-                        float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-                        if (d2 < thrF) mhi |= bit;
-                        bit <<= 1;
-                    }
-                }
-                unsigned long long m = (static_cast<unsigned long long>(mhi) << 32) | mlo;
-                // never test a particle against itself (old or new state); drop trials that left their cell
-                const int o = j - ownBegin, nw = j - newBegin;
-                if (o >= 0 && o < numOwn) m &= ~(1ull << o);
-                if (nw >= 0 && nw < numOwn) m &= ~(1ull << nw);
-                m &= ~dead;
+                    unsigned long long m = (static_cast<unsigned long long>(mhi) << 32) | mlo;
+                    // never test a particle against itself (old or new state); drop trials that left their cell
+                    const int o = j - ownBegin, nw = j - newBegin;
+                    if (o >= 0 && o < numOwn) m &= ~(1ull << o);
+                    if (nw >= 0 && nw < numOwn) m &= ~(1ull << nw);
+                    m &= ~dead;
 
-                const int cnt = __popcll(m);
-                int incl = cnt;
-                #pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    int v = __shfl_up_sync(0xffffffffu, incl, d);
-                    if (lane >= d) incl += v;
+                    const int cnt = __popcll(m);
+                    int incl = cnt;
+                    #pragma unroll
+                    for (int d = 1; d < 32; d <<= 1) {
+                        int v = __shfl_up_sync(0xffffffffu, incl, d);
+                        if (lane >= d) incl += v;
+                    }
+                    const int total = __shfl_sync(0xffffffffu, incl, 31);
+                    if (total == 0) continue;
+                    int off = 0;
+                    if (lane == 0) off = atomicAdd(&qCount, total);
+                    off = __shfl_sync(0xffffffffu, off, 0) + incl - cnt;
+                    while (m) {
+                        const int i = __ffsll(static_cast<long long>(m)) - 1;
+                        m &= m - 1;
+                        const unsigned int e = (static_cast<unsigned int>(i) << 16) | static_cast<unsigned int>(j);
+                        if (off < SW_QCAP) queue[off] = e;
+                        else exactTest(e);       // queue overflow (very dense cells): test in place
+                        off++;
+                    }
                 }
-                const int total = __shfl_sync(0xffffffffu, incl, 31);
-                if (total == 0) continue;
-                int off = 0;
-                if (lane == 0) off = atomicAdd(&qCount, total);
-                off = __shfl_sync(0xffffffffu, off, 0) + incl - cnt;
-                while (m) {
-                    const int i = __ffsll(static_cast<long long>(m)) - 1;
-                    m &= m - 1;
-                    const unsigned int e = (static_cast<unsigned int>(i) << 16) | static_cast<unsigned int>(j);
-                    if (off < SW_QCAP) queue[off] = e;
-                    else exactTest(e);       // queue overflow (very dense cells): test in place
-                    off++;
+                __syncthreads();
+                const int qn = min(qCount, SW_QCAP);
+                const bool last = send == numCand;
+                const int take = last ? qn : qn - qn % THREADS;
+                for (int e = qn - take + tid; e < qn; e += THREADS) exactTest(queue[e]);
+                if (!last) {
+                    __syncthreads();
+                    if (tid == 0) qCount = qn - take;
+                    __syncthreads();
                 }
             }
-        }
-        __syncthreads();
-
-        // ---- phase B: exact FP64 tests, all threads in lock step over the queue ----
-        {
-            const int qn = min(qCount, SW_QCAP);
-            for (int e = tid; e < qn; e += THREADS) exactTest(queue[e]);
         }
         // ---- phase C: sequential resolution inside the cell, random order, from the bit matrices ----
         int rank = 0;

@@ -224,7 +224,7 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
     const int capOld = maxNeigh, capOwn = g.maxPopulation;
     const int capCand = capOld + capOwn;
     size_t smem = static_cast<size_t>(capCand) * (6 * sizeof(double) + 3 * sizeof(float))
-                  + SW_QCAP * sizeof(unsigned int);
+                  + (SW_THREADS / 32) * SW_WQCAP * sizeof(unsigned int);
     if (smem > 200 * 1024)
         throw rp_error(RP_ERR_CAPACITY, "rp_sweep: a cell neighbourhood does not fit into shared memory");
 

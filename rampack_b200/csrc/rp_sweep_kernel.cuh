@@ -38,7 +38,8 @@ struct SweepGrid {
 };
 
 constexpr int SW_MAXOWN = 64;      // trials resolved together (bit matrices are 64 bits wide)
-constexpr int SW_QCAP = 2048;      // CTA-wide queue of (trial, candidate) pairs awaiting the exact test
+constexpr int SW_PUSH = 4;         // queue entries a lane may push per round
+constexpr int SW_WQCAP = 32 * SW_PUSH + 32;     // per-warp queue of (trial, candidate) pairs awaiting the exact test
 
 struct SweepArgs {
     int kind;                   // rp_move_kind

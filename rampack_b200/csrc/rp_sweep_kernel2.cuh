@@ -56,28 +56,29 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
     }
     __syncthreads();
     const int ownStartAll = cellStart[ownCell];
-    if (tid == 0) {
-        int off = 0;
-        for (int c = 0; c < 27; c++) { int cnt = cellBegin[c]; cellBegin[c] = off; off += cnt; }
-        cellBegin[27] = off;
-        const int numOwnT = cellBegin[14] - cellBegin[13];
-        if (numOwnT > 0 && off <= A.capOld && numOwnT <= A.capOwn) {
-            // 1-D TMA bulk copies: merged runs of cells that are contiguous in the sorted order + the own trials
-            mbarExpectTx(&sBar, static_cast<unsigned int>((off + numOwnT) * 48));
-            int runSrc = -1, runDst = 0, runCnt = 0;
-            for (int c = 0; c < 27; c++) {
-                const int cnt = cellBegin[c + 1] - cellBegin[c];
-                if (cnt == 0) continue;
-                if (runCnt > 0 && cellSrc[c] == runSrc + runCnt) { runCnt += cnt; continue; }
-                if (runCnt > 0)
-                    bulkCopyG2S(cand + 6 * static_cast<size_t>(runDst), rec + 6 * static_cast<size_t>(runSrc),
-                                static_cast<unsigned int>(runCnt * 48), &sBar);
-                runSrc = cellSrc[c]; runDst = cellBegin[c]; runCnt = cnt;
-            }
-            if (runCnt > 0)
-                bulkCopyG2S(cand + 6 * static_cast<size_t>(runDst), rec + 6 * static_cast<size_t>(runSrc),
-                            static_cast<unsigned int>(runCnt * 48), &sBar);
-            bulkCopyG2S(cand + 6 * static_cast<size_t>(off), T.rec + 6 * static_cast<size_t>(ownStartAll),
+    if (warp == 0) {
+        // exclusive scan of the 27 cell populations -> staging offsets; every lane then issues the 1-D TMA bulk copy
+        // of its own cell (lane 27: the trial records of the own cell)
+        const int cnt = lane < 27 ? cellBegin[lane] : 0;
+        int incl = cnt;
+        #pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int v = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += v;
+        }
+        const int total = __shfl_sync(0xffffffffu, incl, 26);
+        const int numOwnT = __shfl_sync(0xffffffffu, cnt, 13);
+        const bool ok = numOwnT > 0 && total <= A.capOld && numOwnT <= A.capOwn;
+        if (lane == 0 && ok) mbarExpectTx(&sBar, static_cast<unsigned int>((total + numOwnT) * 48));
+        __syncwarp();
+        if (lane < 27) {
+            cellBegin[lane] = incl - cnt;
+            if (lane == 26) cellBegin[27] = incl;
+            if (ok && cnt > 0)
+                bulkCopyG2S(cand + 6 * static_cast<size_t>(incl - cnt), rec + 6 * static_cast<size_t>(cellSrc[lane]),
+                            static_cast<unsigned int>(cnt * 48), &sBar);
+        } else if (lane == 27 && ok) {
+            bulkCopyG2S(cand + 6 * static_cast<size_t>(total), T.rec + 6 * static_cast<size_t>(ownStartAll),
                         static_cast<unsigned int>(numOwnT * 48), &sBar);
         }
     }
@@ -161,56 +162,62 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
             }
         };
 
-        // ---- phases A + B in rounds over super-chunks of candidates ----
-        // A: conservative FP32 cull (spheres: centre distance; spherocylinders: distance of the candidate's centre
-        //    from the trial's axis segment, a necessary condition for the segments to come closer than 2r), survivors
-        //    are appended to the CTA queue;  B: exact FP64 tests, all threads in lock step over the queue.  Between
-        //    rounds only full multiples of THREADS are consumed, so every lane stays busy.
+        // ---- phases A + B, warp-autonomous (no CTA barrier in between) ----
+        // Warps grab chunks of 32 candidates from a shared counter.  A: conservative FP32 cull of the chunk against
+        // all trials (spheres: centre distance; spherocylinders: distance of the candidate's centre from the trial's
+        // axis segment — a necessary condition for the two segments to come closer than 2r); survivors go to the
+        // warp's queue.  B: whenever 32 entries are queued they take the exact FP64 test with every lane busy.
         {
             const float thrF = A.cullThr2, halfF = A.cullHalf;
             const unsigned long long dead = sRejMask;
-            constexpr int SUPER = THREADS * 4;
-            for (int sbase = 0; sbase < numCand; sbase += SUPER) {
-                const int send = min(numCand, sbase + SUPER);
-                for (int base = sbase + warp * 32; base < send; base += WARPS * 32) {
-                    const int jj = base + lane;
-                    const bool valid = jj < send;
-                    const int j = jj < numOld ? jj : jj + batch0;
-                    // a far-away dummy for the invalid slots keeps the loop branch-free
-                    float cxf = 1e18f, cyf = 0.f, czf = 0.f;
-                    if (valid) { cxf = cfx[j]; cyf = cfy[j]; czf = cfz[j]; }
-                    unsigned int mlo = 0, mhi = 0;
-                    #pragma unroll
-                    for (int half = 0; half < 2; half++) {
-                        const int i0 = half * 32, i1 = min(numOwn, i0 + 32);
-                        unsigned int bit = 1, mm = 0;
-                        #pragma unroll 4
-                        for (int i = i0; i < i1; i++) {
-                            const float4 tf = trialF[i];
-                            float dx = cxf - tf.x, dy = cyf - tf.y, dz = czf - tf.z;
-                            float d2;
-                            if (HARD == RP_HARD_SPHEROCYLINDER) {
-                                const float4 tu = trialU[i];
-                                float s = fmaf(dz, tu.z, fmaf(dy, tu.y, dx * tu.x));
-                                s = fminf(fmaxf(s, -halfF), halfF);
-                                float rx = fmaf(-s, tu.x, dx), ry = fmaf(-s, tu.y, dy), rz = fmaf(-s, tu.z, dz);
-                                d2 = fmaf(rz, rz, fmaf(ry, ry, rx * rx));
-                            } else {
-                                d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-                            }
-                            if (d2 < thrF) mm |= bit;
-                            bit <<= 1;
+            unsigned int *q = queue + warp * SW_WQCAP;
+            int qn = 0;
+            const int numChunks = (numCand + 31) >> 5;
+            for (;;) {
+                int chunk = 0;
+                if (lane == 0) chunk = atomicAdd(&qCount, 1);
+                chunk = __shfl_sync(0xffffffffu, chunk, 0);
+                if (chunk >= numChunks) break;
+                const int jj = (chunk << 5) + lane;
+                const bool valid = jj < numCand;
+                const int j = jj < numOld ? jj : jj + batch0;
+                // a far-away dummy for the invalid slots keeps the loop branch-free
+                float cxf = 1e18f, cyf = 0.f, czf = 0.f;
+                if (valid) { cxf = cfx[j]; cyf = cfy[j]; czf = cfz[j]; }
+                unsigned int mlo = 0, mhi = 0;
+                #pragma unroll
+                for (int half = 0; half < 2; half++) {
+                    const int i0 = half * 32, i1 = min(numOwn, i0 + 32);
+                    unsigned int bit = 1, mm = 0;
+                    #pragma unroll 4
+                    for (int i = i0; i < i1; i++) {
+                        const float4 tf = trialF[i];
+                        float dx = cxf - tf.x, dy = cyf - tf.y, dz = czf - tf.z;
+                        float d2;
+                        if (HARD == RP_HARD_SPHEROCYLINDER) {
+                            const float4 tu = trialU[i];
+                            float s = fmaf(dz, tu.z, fmaf(dy, tu.y, dx * tu.x));
+                            s = fminf(fmaxf(s, -halfF), halfF);
+                            float rx = fmaf(-s, tu.x, dx), ry = fmaf(-s, tu.y, dy), rz = fmaf(-s, tu.z, dz);
+                            d2 = fmaf(rz, rz, fmaf(ry, ry, rx * rx));
+                        } else {
+                            d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
                         }
-                        if (half == 0) mlo = mm; else mhi = mm;
+                        if (d2 < thrF) mm |= bit;
+                        bit <<= 1;
                     }
-                    unsigned long long m = (static_cast<unsigned long long>(mhi) << 32) | mlo;
-                    // never test a particle against itself (old or new state); drop trials that left their cell
-                    const int o = j - ownBegin, nw = j - newBegin;
-                    if (o >= 0 && o < numOwn) m &= ~(1ull << o);
-                    if (nw >= 0 && nw < numOwn) m &= ~(1ull << nw);
-                    m &= ~dead;
+                    if (half == 0) mlo = mm; else mhi = mm;
+                }
+                unsigned long long m = (static_cast<unsigned long long>(mhi) << 32) | mlo;
+                // never test a particle against itself (old or new state); drop trials that left their cell
+                const int o = j - ownBegin, nw = j - newBegin;
+                if (o >= 0 && o < numOwn) m &= ~(1ull << o);
+                if (nw >= 0 && nw < numOwn) m &= ~(1ull << nw);
+                m &= ~dead;
 
-                    const int cnt = __popcll(m);
+                // push at most SW_PUSH entries per lane and round; run the exact test on every full batch of 32
+                while (__any_sync(0xffffffffu, m != 0ull)) {
+                    const int cnt = min(__popcll(m), SW_PUSH);
                     int incl = cnt;
                     #pragma unroll
                     for (int d = 1; d < 32; d <<= 1) {
@@ -218,31 +225,24 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
                         if (lane >= d) incl += v;
                     }
                     const int total = __shfl_sync(0xffffffffu, incl, 31);
-                    if (total == 0) continue;
-                    int off = 0;
-                    if (lane == 0) off = atomicAdd(&qCount, total);
-                    off = __shfl_sync(0xffffffffu, off, 0) + incl - cnt;
-                    while (m) {
+                    int at = qn + incl - cnt;
+                    for (int k = 0; k < cnt; k++) {
                         const int i = __ffsll(static_cast<long long>(m)) - 1;
                         m &= m - 1;
-                        const unsigned int e = (static_cast<unsigned int>(i) << 16) | static_cast<unsigned int>(j);
-                        if (off < SW_QCAP) queue[off] = e;
-                        else exactTest(e);       // queue overflow (very dense cells): test in place
-                        off++;
+                        q[at + k] = (static_cast<unsigned int>(i) << 16) | static_cast<unsigned int>(j);
                     }
-                }
-                __syncthreads();
-                const int qn = min(qCount, SW_QCAP);
-                const bool last = send == numCand;
-                const int take = last ? qn : qn - qn % THREADS;
-                for (int e = qn - take + tid; e < qn; e += THREADS) exactTest(queue[e]);
-                if (!last) {
-                    __syncthreads();
-                    if (tid == 0) qCount = qn - take;
-                    __syncthreads();
+                    qn += total;
+                    __syncwarp();
+                    while (qn >= 32) {
+                        qn -= 32;
+                        exactTest(q[qn + lane]);
+                    }
+                    __syncwarp();
                 }
             }
+            if (lane < qn) exactTest(q[lane]);
         }
+
         // ---- phase C: sequential resolution inside the cell, random order, from the bit matrices ----
         int rank = 0;
         if (tid < numOwn) {

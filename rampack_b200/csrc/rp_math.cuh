@@ -146,8 +146,11 @@ struct BcPeriodic {
     RP_HD double distance2(V3 p1, V3 p2) const { return pbcDistance2(*box, p1, p2); }
 };
 
-// geometry/SegmentDistanceCalculator.h:22-85 — softSurfer / Dan Sunday segment-segment distance squared,
-// identical branch structure and EPSILON
+// geometry/SegmentDistanceCalculator.h:22-85 — softSurfer / Dan Sunday segment-segment distance squared.
+// Same arithmetic and the same EPSILON as the reference; its if/else ladder only SELECTS among already computed
+// values (sN, sD, tN, tD), so it is written here with selects: identical results bit for bit, but straight-line code
+// the GPU can software-pipeline (two independent pair tests interleave in the sweep kernel).  The two divisions are
+// evaluated unconditionally and discarded by the same |x| < EPSILON tests the reference applies first.
 RP_HD double segmentDistance2(V3 s11, V3 s12, V3 s21, V3 s22) {
     const double EPS = 0.0000000001;
     V3 u = s12 - s11;
@@ -155,49 +158,28 @@ RP_HD double segmentDistance2(V3 s11, V3 s12, V3 s21, V3 s22) {
     V3 w = s11 - s21;
     double a = dot(u, u), b = dot(u, v), c = dot(v, v), d = dot(u, w), e = dot(v, w);
     double D = a * c - b * b;
-    double sc, sN, sD = D;
-    double tc, tN, tD = D;
-    if (D < EPS) {
-        sN = 0.0;
-        sD = 1.0;
-        tN = e;
-        tD = c;
-    } else {
-        sN = (b * e - c * d);
-        tN = (a * e - b * d);
-        if (sN < 0.0) {
-            sN = 0.0;
-            tN = e;
-            tD = c;
-        } else if (sN > sD) {
-            sN = sD;
-            tN = e + b;
-            tD = c;
-        }
+    // first stage (reference lines 36-57)
+    const bool small = D < EPS;
+    const double sN0 = (b * e - c * d), tN0 = (a * e - b * d);
+    const bool lt = !small && sN0 < 0.0;
+    const bool gt = !small && !lt && sN0 > D;
+    double sN = (small || lt) ? 0.0 : (gt ? D : sN0);
+    double sD = small ? 1.0 : D;
+    double tN = (small || lt) ? e : (gt ? e + b : tN0);
+    double tD = (small || lt || gt) ? c : D;
+    // second stage (reference lines 59-79)
+    const bool tneg = tN < 0.0;
+    const bool tbig = !tneg && tN > tD;
+    const double y = tneg ? -d : (-d + b);
+    const bool ylt = y < 0.0;
+    const bool ygt = !ylt && y > a;
+    if (tneg || tbig) {
+        sN = ylt ? 0.0 : (ygt ? sD : y);
+        sD = (ylt || ygt) ? sD : a;
     }
-    if (tN < 0.0) {
-        tN = 0.0;
-        if (-d < 0.0)
-            sN = 0.0;
-        else if (-d > a)
-            sN = sD;
-        else {
-            sN = -d;
-            sD = a;
-        }
-    } else if (tN > tD) {
-        tN = tD;
-        if ((-d + b) < 0.0)
-            sN = 0;
-        else if ((-d + b) > a)
-            sN = sD;
-        else {
-            sN = (-d + b);
-            sD = a;
-        }
-    }
-    sc = (fabs(sN) < EPS ? 0.0 : sN / sD);
-    tc = (fabs(tN) < EPS ? 0.0 : tN / tD);
+    tN = tneg ? 0.0 : (tbig ? tD : tN);
+    double sc = (fabs(sN) < EPS ? 0.0 : sN / sD);
+    double tc = (fabs(tN) < EPS ? 0.0 : tN / tD);
     V3 dP = w + (sc * u) - (tc * v);
     return norm2(dP);
 }

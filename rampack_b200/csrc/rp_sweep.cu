@@ -112,7 +112,7 @@ __global__ void k_sweep_records(int numCells, size_t cap, const int *__restrict_
 // ---------------------------------------------------------------------------------------------------------------
 // host driver: one call = one pass of N trial moves (every particle once) with one sampler
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int SW_THREADS = 128;
+constexpr int SW_THREADS = 256;
 
 template <int HARD>
 static void launchSweep(Handle *h, const SweepArgs &A0, const SweepGrid &sg, const int colourOrder[8], size_t smem,
@@ -223,7 +223,7 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
     // staging capacities: records are 48 bytes, so any count keeps the 16-byte alignment of the bulk copies
     const int capOld = maxNeigh, capOwn = g.maxPopulation;
     const int capCand = capOld + capOwn;
-    size_t smem = static_cast<size_t>(capCand) * (6 * sizeof(double) + 3 * sizeof(float))
+    size_t smem = static_cast<size_t>(capCand) * 6 * sizeof(double)
                   + (SW_THREADS / 32) * SW_WQCAP * sizeof(unsigned int);
     if (smem > 200 * 1024)
         throw rp_error(RP_ERR_CAPACITY, "rp_sweep: a cell neighbourhood does not fit into shared memory");

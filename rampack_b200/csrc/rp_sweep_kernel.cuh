@@ -39,7 +39,7 @@ struct SweepGrid {
 
 constexpr int SW_MAXOWN = 64;      // trials resolved together (bit matrices are 64 bits wide)
 constexpr int SW_PUSH = 4;         // queue entries a lane may push per round
-constexpr int SW_WQCAP = 32 * SW_PUSH + 32;     // per-warp queue of (trial, candidate) pairs awaiting the exact test
+constexpr int SW_WQCAP = 32 * SW_PUSH + 64;     // per-warp queue of (trial, candidate) pairs awaiting the exact test
 
 struct SweepArgs {
     int kind;                   // rp_move_kind
@@ -100,11 +100,11 @@ __device__ __forceinline__ bool exactOverlap(const Inter &I, const TrialRec &t, 
     V3 p1 = v3(t.px, t.py, t.pz), p2 = v3(c[0], c[1], c[2]);
     double d2 = norm2(p2 - p1);
     if (HARD == RP_HARD_SPHERE) return d2 < I.sphereThr2;
-    if (d2 < I.scInner2) return true;
-    if (d2 >= I.scOuter2) return false;
+    // straight-line form of: d2 < 4r^2 -> true; d2 >= (2r + l)^2 -> false; else segment distance^2 < 4r^2.
+    // (after the FP32 cull practically every pair needs the segment test, so nothing is saved by branching)
     V3 h2 = v3(c[3], c[4], c[5]);
     double s = segmentDistance2(v3(t.s1x, t.s1y, t.s1z), v3(t.s2x, t.s2y, t.s2z), p2 - h2, p2 + h2);
-    return s < I.scInner2;
+    return (d2 < I.scInner2) || (!(d2 >= I.scOuter2) && s < I.scInner2);
 }
 
 // ---------------------------------------------------------------------------------------------------------------

@@ -4,7 +4,7 @@
 namespace rp {
 
 template <int HARD, int THREADS>
-__global__ void __launch_bounds__(THREADS, 512 / THREADS)
+__global__ void __launch_bounds__(THREADS, THREADS == 256 ? 3 : 4)
 k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, const int *__restrict__ cellStart,
         const int *__restrict__ items, double *__restrict__ rec, TrialBuffers T, double *__restrict__ pos,
         double *__restrict__ orient, unsigned long long *__restrict__ counters, int *__restrict__ flags)
@@ -23,13 +23,10 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
     __shared__ int sStats[3];
     __shared__ int qCount;
 
-    // dynamic shared memory: FP64 records (old states, then the trial = new states of the own cell), the FP32
-    // cell-local positions (SoA), the CTA queue
+    // dynamic shared memory: FP64 records (old states, then the trial = new states of the own cell), the warp queues
     const int capCand = A.capOld + A.capOwn;
     double *cand = reinterpret_cast<double *>(smemRaw);
-    float *cfx = reinterpret_cast<float *>(cand + 6 * static_cast<size_t>(capCand));
-    float *cfy = cfx + capCand, *cfz = cfy + capCand;
-    unsigned int *queue = reinterpret_cast<unsigned int *>(cfz + capCand);
+    unsigned int *queue = reinterpret_cast<unsigned int *>(cand + 6 * static_cast<size_t>(capCand));
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int i = tid; i < static_cast<int>(sizeof(Inter) / sizeof(int)); i += THREADS)
@@ -93,26 +90,18 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
     // origin of the FP32 local frame: centre of the active cell (image frame)
     const V3 origin = relToAbs(box, v3((cx + 0.5) * sg.relCell[0] + sg.shift[0], (cy + 0.5) * sg.relCell[1] + sg.shift[1],
                                        (cz + 0.5) * sg.relCell[2] + sg.shift[2]));
-    mbarWait(&sBar, 0);
+    if (warp == 0) mbarWait(&sBar, 0);       // the other warps park at the CTA barrier instead of spinning
+    __syncthreads();
 
-    // ---- second staging pass (shared memory only): pos2 + lattice translation, FP32 local copy ----
+    // ---- second staging pass (shared memory only): pos2 + lattice translation (HardcodedTranslation) ----
     for (int c = warp; c < 27; c += WARPS) {
+        if (cellT[c] == 13) continue;        // translation (0, 0, 0): pos2 + 0 == pos2
         const int begin = cellBegin[c], cnt = cellBegin[c + 1] - begin;
         const V3 t = sg.trans[cellT[c]];
         for (int j = begin + lane; j < begin + cnt; j += 32) {
             double *r = cand + 6 * static_cast<size_t>(j);
-            double x = r[0] + t.x, y = r[1] + t.y, z = r[2] + t.z;
-            r[0] = x; r[1] = y; r[2] = z;
-            cfx[j] = static_cast<float>(x - origin.x);
-            cfy[j] = static_cast<float>(y - origin.y);
-            cfz[j] = static_cast<float>(z - origin.z);
+            r[0] += t.x; r[1] += t.y; r[2] += t.z;
         }
-    }
-    for (int j = numOld + tid; j < numOld + numOwnAll; j += THREADS) {
-        const double *r = cand + 6 * static_cast<size_t>(j);
-        cfx[j] = static_cast<float>(r[0] - origin.x);
-        cfy[j] = static_cast<float>(r[1] - origin.y);
-        cfz[j] = static_cast<float>(r[2] - origin.z);
     }
 
     const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION);
@@ -136,7 +125,8 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
             t.px = p.x; t.py = p.y; t.pz = p.z; t.hx = h.x; t.hy = h.y; t.hz = h.z;
             V3 s1 = p - h, s2 = p + h;
             t.s1x = s1.x; t.s1y = s1.y; t.s1z = s1.z; t.s2x = s2.x; t.s2y = s2.y; t.s2z = s2.z;
-            trialF[tid] = make_float4(cfx[newBegin + tid], cfy[newBegin + tid], cfz[newBegin + tid], 0.f);
+            trialF[tid] = make_float4(static_cast<float>(p.x - origin.x), static_cast<float>(p.y - origin.y),
+                                      static_cast<float>(p.z - origin.z), 0.f);
             if (HARD == RP_HARD_SPHEROCYLINDER)      // FP32 unit axis of the trial for the capsule cull
                 trialU[tid] = make_float4(static_cast<float>(h.x / I.scHalfPlus), static_cast<float>(h.y / I.scHalfPlus),
                                           static_cast<float>(h.z / I.scHalfPlus), 0.f);
@@ -149,17 +139,25 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
         __syncthreads();
 
         volatile int *vrej = rejected;
-        auto exactTest = [&](unsigned int e) {
-            const int ti = e >> 16, cj = e & 0xffff;
-            if (vrej[ti]) return;
-            if (exactOverlap<HARD>(I, trial[ti], cand + 6 * static_cast<size_t>(cj))) {
-                if (cj >= numOld) atomicOr(&newMask[ti], 1ull << (cj - newBegin));
-                else {
-                    const int o = cj - ownBegin;
-                    if (o >= 0 && o < numOwn) atomicOr(&ownMask[ti], 1ull << o);
-                    else vrej[ti] = 1;
-                }
+        auto record = [&](int ti, int cj) {
+            if (cj >= numOld) atomicOr(&newMask[ti], 1ull << (cj - newBegin));
+            else {
+                const int o = cj - ownBegin;
+                if (o >= 0 && o < numOwn) atomicOr(&ownMask[ti], 1ull << o);
+                else vrej[ti] = 1;
             }
+        };
+        // two independent exact tests per lane: their FP64 dependency chains interleave (the pair arithmetic is
+        // straight-line code), which is what keeps the FP64 pipe fed at 3-4 warps per scheduler
+        auto exactTest2 = [&](unsigned int e0, unsigned int e1, bool v0, bool v1) {
+            const int t0 = e0 >> 16, c0 = e0 & 0xffff, t1 = e1 >> 16, c1 = e1 & 0xffff;
+            v0 = v0 && !vrej[t0];
+            v1 = v1 && !vrej[t1];
+            if (!(v0 || v1)) return;
+            const bool r0 = exactOverlap<HARD>(I, trial[t0], cand + 6 * static_cast<size_t>(c0));
+            const bool r1 = exactOverlap<HARD>(I, trial[t1], cand + 6 * static_cast<size_t>(c1));
+            if (v0 && r0) record(t0, c0);
+            if (v1 && r1) record(t1, c1);
         };
 
         // ---- phases A + B, warp-autonomous (no CTA barrier in between) ----
@@ -183,7 +181,12 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
                 const int j = jj < numOld ? jj : jj + batch0;
                 // a far-away dummy for the invalid slots keeps the loop branch-free
                 float cxf = 1e18f, cyf = 0.f, czf = 0.f;
-                if (valid) { cxf = cfx[j]; cyf = cfy[j]; czf = cfz[j]; }
+                if (valid) {         // FP32 copy of the position in cell-local coordinates
+                    const double *r = cand + 6 * static_cast<size_t>(j);
+                    cxf = static_cast<float>(r[0] - origin.x);
+                    cyf = static_cast<float>(r[1] - origin.y);
+                    czf = static_cast<float>(r[2] - origin.z);
+                }
                 unsigned int mlo = 0, mhi = 0;
                 #pragma unroll
                 for (int half = 0; half < 2; half++) {
@@ -215,7 +218,7 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
                 if (nw >= 0 && nw < numOwn) m &= ~(1ull << nw);
                 m &= ~dead;
 
-                // push at most SW_PUSH entries per lane and round; run the exact test on every full batch of 32
+                // push at most SW_PUSH entries per lane and round; run the exact tests on every full batch of 64
                 while (__any_sync(0xffffffffu, m != 0ull)) {
                     const int cnt = min(__popcll(m), SW_PUSH);
                     int incl = cnt;
@@ -233,14 +236,17 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
                     }
                     qn += total;
                     __syncwarp();
-                    while (qn >= 32) {
-                        qn -= 32;
-                        exactTest(q[qn + lane]);
+                    while (qn >= 64) {
+                        qn -= 64;
+                        exactTest2(q[qn + lane], q[qn + 32 + lane], true, true);
                     }
                     __syncwarp();
                 }
             }
-            if (lane < qn) exactTest(q[lane]);
+            if (qn > 0) {
+                const bool v0 = lane < qn, v1 = lane + 32 < qn;
+                exactTest2(v0 ? q[lane] : 0u, v1 ? q[lane + 32] : 0u, v0, v1);
+            }
         }
 
         // ---- phase C: sequential resolution inside the cell, random order, from the bit matrices ----
@@ -290,8 +296,6 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
                 // later batches see this particle as a frozen candidate in its new state (own cell: no translation)
                 double *cs = cand + 6 * static_cast<size_t>(ownBegin + tid);
                 cs[0] = t.px; cs[1] = t.py; cs[2] = t.pz; cs[3] = t.hx; cs[4] = t.hy; cs[5] = t.hz;
-                cfx[ownBegin + tid] = trialF[tid].x; cfy[ownBegin + tid] = trialF[tid].y;
-                cfz[ownBegin + tid] = trialF[tid].z;
             }
             if (translated) {
                 // Shape::translate (core/Shape.cpp:9-12): position += bc.getCorrection(position)

@@ -112,7 +112,7 @@ __global__ void k_sweep_records(int numCells, size_t cap, const int *__restrict_
 // ---------------------------------------------------------------------------------------------------------------
 // host driver: one call = one pass of N trial moves (every particle once) with one sampler
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int SW_THREADS = 256;
+constexpr int SW_THREADS = 128;
 
 template <int HARD>
 static void launchSweep(Handle *h, const SweepArgs &A0, const SweepGrid &sg, const int colourOrder[8], size_t smem,
@@ -134,7 +134,7 @@ static void launchSweep(Handle *h, const SweepArgs &A0, const SweepGrid &sg, con
         int col = colourOrder[c];
         A.colour[0] = col & 1; A.colour[1] = (col >> 1) & 1; A.colour[2] = (col >> 2) & 1;
         int blocks = A.nActive[0] * A.nActive[1] * A.nActive[2];
-        k_sweep<HARD, SW_THREADS><<<blocks, SW_THREADS, smem, h->stream>>>(A, sg, h->box, h->dInter, g.cellStart,
+        k_sweep<HARD, SW_THREADS><<<blocks, SW_THREADS, smem, h->stream>>>(A, sg, h->box, g.cellStart,
                                                                           g.items, g.rec, T, h->pos, h->orient,
                                                                           h->dCounters, h->dFlags);
         h->launches++;
@@ -258,6 +258,10 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
         if (std::getenv("RP_SWEEP_NO_CULL")) A.cullThr2 = 3.0e38f;
     }
     A.cap = h->cap;
+    A.inter.sphereThr2 = I.sphereThr2;
+    A.inter.scInner2 = I.scInner2;
+    A.inter.scOuter2 = I.scOuter2;
+    A.inter.scHalf = I.scHalfPlus;
     if (h->n > h->trialCap || !h->trialRec) {
         for (void *q : {(void *) h->trialRec, (void *) h->trialOrient, h->trialMeta}) if (q) cudaFree(q);
         h->trialRec = h->trialOrient = nullptr;

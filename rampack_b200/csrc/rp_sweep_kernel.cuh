@@ -41,6 +41,13 @@ constexpr int SW_MAXOWN = 64;      // trials resolved together (bit matrices are
 constexpr int SW_PUSH = 4;         // queue entries a lane may push per round
 constexpr int SW_WQCAP = 32 * SW_PUSH + 64;     // per-warp queue of (trial, candidate) pairs awaiting the exact test
 
+// the few interaction constants the sweep kernels need (rp::Inter thresholds, computed on the host with the
+// reference's expressions), passed by value
+struct SweepInter {
+    double sphereThr2;                    // SphereTraits.cpp:56-65
+    double scInner2, scOuter2, scHalf;    // SpherocylinderTraits.cpp:28-46: 4r^2, (2r + l)^2, 0.5 * l
+};
+
 struct SweepArgs {
     int kind;                   // rp_move_kind
     double transStep, rotStep;
@@ -52,6 +59,7 @@ struct SweepArgs {
     int capOwn;                 // capacity of the trial region (max cell population)
     float cullThr2;             // FP32 cull threshold (squared distance) including the FP32 error bound
     float cullHalf;             // spherocylinders: half length of the axis segment
+    SweepInter inter;
     size_t cap;
 };
 
@@ -85,25 +93,22 @@ __device__ __forceinline__ void mbarWait(unsigned long long *bar, unsigned int p
     }
 }
 
-// per-trial data of the exact test: position, half axis and (spherocylinders) the cap centres of the trial
-struct TrialRec {
-    double px, py, pz, hx, hy, hz;
-    double s1x, s1y, s1z, s2x, s2y, s2z;     // cap centres pos - h, pos + h (SpherocylinderTraits.cpp:24-26)
-};
-
-// Exact pair test of trial `t` against a staged candidate record (position already translated).
+// Exact pair test of a trial record `t` = {new position, new half axis} against a staged candidate record `c`
+// (position already translated).
 // Spherocylinder: SpherocylinderTraits::overlapBetween (SpherocylinderTraits.cpp:28-46); the cap centres
 // pos + axis * (0.5 * -+1 * l) are formed as pos -+ h with h = axis * (0.5 * l): bit-identical because
 // axis * (-x) == -(axis * x) and a + (-b) == a - b in IEEE arithmetic.
 template <int HARD>
-__device__ __forceinline__ bool exactOverlap(const Inter &I, const TrialRec &t, const double *__restrict__ c) {
-    V3 p1 = v3(t.px, t.py, t.pz), p2 = v3(c[0], c[1], c[2]);
+__device__ __forceinline__ bool exactOverlap(const SweepInter &I, const double *__restrict__ t,
+                                             const double *__restrict__ c)
+{
+    V3 p1 = v3(t[0], t[1], t[2]), p2 = v3(c[0], c[1], c[2]);
     double d2 = norm2(p2 - p1);
     if (HARD == RP_HARD_SPHERE) return d2 < I.sphereThr2;
     // straight-line form of: d2 < 4r^2 -> true; d2 >= (2r + l)^2 -> false; else segment distance^2 < 4r^2.
     // (after the FP32 cull practically every pair needs the segment test, so nothing is saved by branching)
-    V3 h2 = v3(c[3], c[4], c[5]);
-    double s = segmentDistance2(v3(t.s1x, t.s1y, t.s1z), v3(t.s2x, t.s2y, t.s2z), p2 - h2, p2 + h2);
+    V3 h1 = v3(t[3], t[4], t[5]), h2 = v3(c[3], c[4], c[5]);
+    double s = segmentDistance2(p1 - h1, p1 + h1, p2 - h2, p2 + h2);
     return (d2 < I.scInner2) || (!(d2 >= I.scOuter2) && s < I.scInner2);
 }
 

@@ -5,14 +5,12 @@ namespace rp {
 
 template <int HARD, int THREADS>
 __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 3 : 4)
-k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, const int *__restrict__ cellStart,
+k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
         const int *__restrict__ items, double *__restrict__ rec, TrialBuffers T, double *__restrict__ pos,
         double *__restrict__ orient, unsigned long long *__restrict__ counters, int *__restrict__ flags)
 {
     constexpr int WARPS = THREADS / 32;
     extern __shared__ __align__(16) unsigned char smemRaw[];
-    __shared__ Inter I;
-    __shared__ TrialRec trial[SW_MAXOWN];
     __shared__ float4 trialF[SW_MAXOWN], trialU[SW_MAXOWN];
     __shared__ unsigned long long ownMask[SW_MAXOWN], newMask[SW_MAXOWN], seqOwn[SW_MAXOWN], seqNew[SW_MAXOWN];
     __shared__ unsigned int orderKey[SW_MAXOWN];
@@ -29,8 +27,7 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
     unsigned int *queue = reinterpret_cast<unsigned int *>(cand + 6 * static_cast<size_t>(capCand));
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < static_cast<int>(sizeof(Inter) / sizeof(int)); i += THREADS)
-        reinterpret_cast<int *>(&I)[i] = reinterpret_cast<const int *>(interPtr)[i];
+    const SweepInter &I = A.inter;
 
     // active cell of this CTA
     const int b = blockIdx.x;
@@ -120,16 +117,12 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
         if (tid < numOwn) {
             const uint2 meta = T.meta[ownStart + tid];
             const double *r = cand + 6 * static_cast<size_t>(newBegin + tid);
-            TrialRec &t = trial[tid];
             V3 p = v3(r[0], r[1], r[2]), h = v3(r[3], r[4], r[5]);
-            t.px = p.x; t.py = p.y; t.pz = p.z; t.hx = h.x; t.hy = h.y; t.hz = h.z;
-            V3 s1 = p - h, s2 = p + h;
-            t.s1x = s1.x; t.s1y = s1.y; t.s1z = s1.z; t.s2x = s2.x; t.s2y = s2.y; t.s2z = s2.z;
             trialF[tid] = make_float4(static_cast<float>(p.x - origin.x), static_cast<float>(p.y - origin.y),
                                       static_cast<float>(p.z - origin.z), 0.f);
             if (HARD == RP_HARD_SPHEROCYLINDER)      // FP32 unit axis of the trial for the capsule cull
-                trialU[tid] = make_float4(static_cast<float>(h.x / I.scHalfPlus), static_cast<float>(h.y / I.scHalfPlus),
-                                          static_cast<float>(h.z / I.scHalfPlus), 0.f);
+                trialU[tid] = make_float4(static_cast<float>(h.x / I.scHalf), static_cast<float>(h.y / I.scHalf),
+                                          static_cast<float>(h.z / I.scHalf), 0.f);
             rejected[tid] = static_cast<int>(meta.x);
             orderKey[tid] = meta.y;
             ownMask[tid] = 0ull;
@@ -154,8 +147,10 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
             v0 = v0 && !vrej[t0];
             v1 = v1 && !vrej[t1];
             if (!(v0 || v1)) return;
-            const bool r0 = exactOverlap<HARD>(I, trial[t0], cand + 6 * static_cast<size_t>(c0));
-            const bool r1 = exactOverlap<HARD>(I, trial[t1], cand + 6 * static_cast<size_t>(c1));
+            const bool r0 = exactOverlap<HARD>(I, cand + 6 * static_cast<size_t>(newBegin + t0),
+                                               cand + 6 * static_cast<size_t>(c0));
+            const bool r1 = exactOverlap<HARD>(I, cand + 6 * static_cast<size_t>(newBegin + t1),
+                                               cand + 6 * static_cast<size_t>(c1));
             if (v0 && r0) record(t0, c0);
             if (v1 && r1) record(t1, c1);
         };
@@ -288,18 +283,18 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, 
 
         // ---- write-back of the accepted moves: sorted record (image frame) and canonical arrays (wrapped) ----
         if (tid < numOwn && ((sAccepted >> tid) & 1ull)) {
-            const TrialRec &t = trial[tid];
+            const double *t = cand + 6 * static_cast<size_t>(newBegin + tid);
             const int particleId = items[ownStart + tid];
             double *r = rec + 6 * static_cast<size_t>(ownStart + tid);
-            r[0] = t.px; r[1] = t.py; r[2] = t.pz; r[3] = t.hx; r[4] = t.hy; r[5] = t.hz;
+            for (int q = 0; q < 6; q++) r[q] = t[q];
             if (batch0 + SW_MAXOWN < numOwnAll) {
                 // later batches see this particle as a frozen candidate in its new state (own cell: no translation)
                 double *cs = cand + 6 * static_cast<size_t>(ownBegin + tid);
-                cs[0] = t.px; cs[1] = t.py; cs[2] = t.pz; cs[3] = t.hx; cs[4] = t.hy; cs[5] = t.hz;
+                for (int q = 0; q < 6; q++) cs[q] = t[q];
             }
             if (translated) {
                 // Shape::translate (core/Shape.cpp:9-12): position += bc.getCorrection(position)
-                V3 np = v3(t.px, t.py, t.pz);
+                V3 np = v3(t[0], t[1], t[2]);
                 V3 p = np + pbcCorrection(box, np);
                 pos[particleId] = p.x; pos[A.cap + particleId] = p.y; pos[2 * A.cap + particleId] = p.z;
             }

@@ -90,6 +90,7 @@ __device__ __forceinline__ void mbarWait(unsigned long long *bar, unsigned int p
     while (!done) {
         asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
                      "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(smemAddr(bar)), "r"(phase) : "memory");
+        if (!done) __nanosleep(200);     // leave the issue slots to the other CTAs of the SM
     }
 }
 

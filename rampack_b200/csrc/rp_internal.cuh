@@ -215,6 +215,7 @@ void neighbourStats(Handle *h, double *kCand, double *kFull);
 void fp64Peak(Handle *h, double *dfmaGflops, double *dmulDaddGflops);
 // ---- rp_sweep.cu ----
 void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out);
+void cullThresholds(const Handle *h, const double relCell[3], float *thr2, float *half);
 
 }  // namespace rp
 

@@ -7,7 +7,9 @@
 //   Packing::countParticleOverlaps / calculateParticleEnergy        core/Packing.cpp:373-429, 649-688
 //   Packing::tryScaling / revertScaling                             core/Packing.cpp:172-208, 363-371
 #include "rp_internal.cuh"
+#include "rp_recount_cull.cuh"
 #include <limits>
+#include <cstdlib>
 
 namespace rp {
 
@@ -268,7 +270,27 @@ unsigned long long countTotalOverlaps(Handle *h, bool earlyExit) {
     cudaStream_t st = h->stream;
     RP_CUDA(cudaMemsetAsync(h->dCounters, 0, sizeof(unsigned long long), st));
     RP_CUDA(cudaMemsetAsync(h->dFlags + 2, 0, sizeof(int), st));
-    if (h->hasGrid) {
+    const Inter &I = h->inter;
+    const bool culled = h->hasGrid && I.k == 0 && (I.hard == RP_HARD_SPHERE || I.hard == RP_HARD_SPHEROCYLINDER)
+                        && !std::getenv("RP_RECOUNT_LEGACY");
+    if (culled) {
+        // two-stage pair test (FP32 cull -> compacted exact FP64 tests), rp_recount_cull.cuh
+        GridView g = makeView(h->grid);
+        RecountArgs A;
+        A.inter.sphereThr2 = I.sphereThr2;
+        A.inter.scInner2 = I.scInner2;
+        A.inter.scOuter2 = I.scOuter2;
+        A.inter.scHalf = I.scHalfPlus;
+        A.earlyExit = earlyExit ? 1 : 0;
+        cullThresholds(h, g.relCell, &A.cullThr2, &A.cullHalf);
+        int blocks = (g.numCells + RC_WARPS - 1) / RC_WARPS;
+        if (I.hard == RP_HARD_SPHERE)
+            k_recount_cull<RP_HARD_SPHERE><<<blocks, RC_WARPS * 32, 0, st>>>(g, h->grid.box, A, h->dCounters,
+                                                                             h->dFlags + 2);
+        else
+            k_recount_cull<RP_HARD_SPHEROCYLINDER><<<blocks, RC_WARPS * 32, 0, st>>>(g, h->grid.box, A, h->dCounters,
+                                                                                     h->dFlags + 2);
+    } else if (h->hasGrid) {
         GridView g = makeView(h->grid);
         int blocks = (g.numCells * 32 + 255) / 256;
         k_recount_grid<false><<<blocks, 256, 0, st>>>(g, h->dInter, earlyExit ? 1 : 0, h->dCounters, h->dFlags + 2,

@@ -112,6 +112,25 @@ __global__ void k_sweep_records(int numCells, size_t cap, const int *__restrict_
 // ---------------------------------------------------------------------------------------------------------------
 // host driver: one call = one pass of N trial moves (every particle once) with one sampler
 // ---------------------------------------------------------------------------------------------------------------
+// FP32 cull threshold + a bound on the FP32 error: positions are converted to cell-local coordinates of magnitude
+// <= E (1.5 cells along every box vector), so a coordinate difference carries an absolute error <= 4 E 2^-24 and sums
+// of squares / projections a relative one of a few 2^-24.
+//   spheres:          centre distance < range
+//   spherocylinders:  distance(candidate centre, trial's axis segment) < 2r + l/2 — necessary for the two axis
+//                     segments to come closer than 2r (every point of the candidate's segment lies within l/2 of
+//                     its centre); it implies centre distance < range as well
+void cullThresholds(const Handle *h, const double relCell[3], float *thr2, float *half) {
+    const Inter &I = h->inter;
+    double E = 0;
+    for (int i = 0; i < 3; i++)
+        E += 1.5 * relCell[i] * std::sqrt(norm2(relToAbs(h->box, v3(i == 0, i == 1, i == 2))));
+    double R = I.range, u = std::ldexp(1.0, -24), delta = 4 * E * u;
+    double Rc = (I.hard == RP_HARD_SPHEROCYLINDER) ? std::sqrt(I.scInner2) + I.scHalfPlus : R;
+    double margin = 8 * Rc * (8 * delta + 8 * u * R) + 1e-5 * Rc * Rc;
+    *thr2 = std::nextafterf(static_cast<float>(Rc * Rc + margin), INFINITY);
+    *half = static_cast<float>(I.scHalfPlus);
+}
+
 constexpr int SW_THREADS = 128;
 
 template <int HARD>
@@ -239,21 +258,7 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
     A.capOld = capOld;
     A.capOwn = capOwn;
     {
-        // FP32 cull threshold + a bound on the FP32 error: positions are converted to cell-local coordinates of
-        // magnitude <= E (1.5 cells along every box vector), so a coordinate difference carries an absolute error
-        // <= 4 E 2^-24 and sums of squares / projections a relative one of a few 2^-24.
-        //   spheres:          centre distance < range
-        //   spherocylinders:  distance(candidate centre, trial's axis segment) < 2r + l/2 — necessary for the two
-        //                     axis segments to come closer than 2r (every point of the candidate's segment lies
-        //                     within l/2 of its centre); it implies centre distance < range as well
-        double E = 0;
-        for (int i = 0; i < 3; i++)
-            E += 1.5 * sg.relCell[i] * std::sqrt(norm2(relToAbs(h->box, v3(i == 0, i == 1, i == 2))));
-        double R = I.range, u = std::ldexp(1.0, -24), delta = 4 * E * u;
-        double Rc = (I.hard == RP_HARD_SPHEROCYLINDER) ? std::sqrt(I.scInner2) + I.scHalfPlus : R;
-        double margin = 8 * Rc * (8 * delta + 8 * u * R) + 1e-5 * Rc * Rc;
-        A.cullThr2 = std::nextafterf(static_cast<float>(Rc * Rc + margin), INFINITY);
-        A.cullHalf = static_cast<float>(I.scHalfPlus);
+        cullThresholds(h, sg.relCell, &A.cullThr2, &A.cullHalf);
         // test hook: with the cull disabled every pair takes the exact FP64 test; the results must be bit-identical
         if (std::getenv("RP_SWEEP_NO_CULL")) A.cullThr2 = 3.0e38f;
     }

@@ -117,6 +117,7 @@ typedef struct rp_sweep_counters {
     uint64_t accepted;
     uint64_t rejected_domain;     /* rejected because the mass centre left the active region (Packing.cpp:95-96) */
     uint64_t rejected_overlap;
+    uint64_t rejected_energy;     /* rejected by the Metropolis test on a finite energy difference */
     uint64_t sub_sweeps;          /* checkerboard colours run */
     uint64_t kernel_launches;     /* device kernels launched by this call */
 } rp_sweep_counters;
@@ -160,6 +161,25 @@ rp_status rp_revert_scaling(rp_handle *h);
 
 /* ---- bulk sweep: Simulation::performMoves (Simulation.cpp:365-491) as one call per sampler per cycle ---- */
 rp_status rp_sweep(rp_handle *h, const rp_sweep_params *params, rp_sweep_counters *counters_out);
+
+/* Parity harness: what the last rp_sweep call did, one entry per particle.  Replaying the entries in the order
+ * (colour_step, cell, order_key, slot) through Packing::tryMove / acceptMove of the reference must reproduce every
+ * accept / reject decision (tests/test_gpu_sweep_replay.py). */
+typedef struct rp_trial_trace {
+    uint64_t particle;
+    int32_t colour_step;      /* 0..7: the sub-sweep that processed the particle */
+    int32_t cell;             /* sweep-grid cell (the active domain of the trial) */
+    uint32_t order_key;       /* processing order inside the cell: ascending (order_key, slot) */
+    int32_t slot;
+    int32_t status;           /* 0 rejected (overlap or Metropolis), 1 accepted, 2 rejected: left the active cell */
+    int32_t reserved;
+    double position[3];       /* trial mass centre in the image frame of the sweep grid (not wrapped) */
+    double orientation[9];    /* trial orientation */
+    double image_shift[3];    /* image-frame position of the particle = canonical position + image_shift */
+    double u;                 /* Metropolis variate (0 on the hard-only fast path, which draws none) */
+    double dE;                /* what Packing::tryMove would have returned for the trial (undefined when status == 2) */
+} rp_trial_trace;
+rp_status rp_sweep_trace(rp_handle *h, rp_trial_trace *out, uint64_t n);
 
 /* ---- counting mode + walls: Packing::toggleOverlapCounting / getCachedNumberOfOverlaps (Packing.cpp:1049-1060) ---- */
 rp_status rp_toggle_overlap_counting(rp_handle *h, int count_overlaps);

@@ -49,7 +49,7 @@ class SweepParams(C.Structure):
 
 class SweepCounters(C.Structure):
     _fields_ = [("attempted", C.c_uint64), ("accepted", C.c_uint64), ("rejected_domain", C.c_uint64),
-                ("rejected_overlap", C.c_uint64), ("sub_sweeps", C.c_uint64), ("kernel_launches", C.c_uint64)]
+                ("rejected_overlap", C.c_uint64), ("rejected_energy", C.c_uint64), ("sub_sweeps", C.c_uint64), ("kernel_launches", C.c_uint64)]
 
 
 # rp_pair as a numpy structured dtype (same layout as the C struct: all members are 8 bytes wide)
@@ -57,12 +57,17 @@ PAIR_DTYPE = np.dtype([("pos1", "<f8", 3), ("orientation1", "<f8", 9), ("idx1", 
                        ("pos2", "<f8", 3), ("orientation2", "<f8", 9), ("idx2", "<u8"),
                        ("translation", "<f8", 3)])
 assert PAIR_DTYPE.itemsize == 8 * 29
+# rp_trial_trace
+TRACE_DTYPE = np.dtype([("particle", "<u8"), ("colour_step", "<i4"), ("cell", "<i4"), ("order_key", "<u4"),
+                        ("slot", "<i4"), ("status", "<i4"), ("reserved", "<i4"), ("position", "<f8", 3),
+                        ("orientation", "<f8", 9), ("image_shift", "<f8", 3), ("u", "<f8"), ("dE", "<f8")])
+assert TRACE_DTYPE.itemsize == 8 + 6 * 4 + 8 * 17
 
 # every symbol include/rampack_b200.h declares (tests/test_abi.py checks the exports against the header)
 SYMBOLS = ["rp_create", "rp_destroy", "rp_last_error", "rp_version", "rp_set_interaction", "rp_upload",
            "rp_download", "rp_size", "rp_rebuild_grid", "rp_grid_info_get", "rp_cell_numbers",
            "rp_count_total_overlaps", "rp_total_energy", "rp_try_move", "rp_accept_move", "rp_try_scaling",
-           "rp_revert_scaling", "rp_sweep", "rp_toggle_overlap_counting", "rp_cached_overlaps",
+           "rp_revert_scaling", "rp_sweep", "rp_sweep_trace", "rp_toggle_overlap_counting", "rp_cached_overlaps",
            "rp_pair_test_batch", "rp_neighbour_stats", "rp_measure_fp64_peak", "rp_last_kernel_ms", "rp_launch_count", "rp_synchronize"]
 
 _lib = None
@@ -103,6 +108,7 @@ def load():
     lib.rp_try_scaling.argtypes = [H, dp, dp]
     lib.rp_revert_scaling.argtypes = [H]
     lib.rp_sweep.argtypes = [H, C.POINTER(SweepParams), C.POINTER(SweepCounters)]
+    lib.rp_sweep_trace.argtypes = [H, C.c_void_p, C.c_uint64]
     lib.rp_toggle_overlap_counting.argtypes = [H, C.c_int]
     lib.rp_cached_overlaps.argtypes = [H, C.POINTER(C.c_uint64)]
     lib.rp_pair_test_batch.argtypes = [H, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
@@ -247,6 +253,12 @@ class Device:
         c = SweepCounters()
         self._check(self.lib.rp_sweep(self.h, C.byref(p), C.byref(c)))
         return c
+
+    def sweep_trace(self):
+        """The trials of the last sweep() call, one TRACE_DTYPE entry per particle (parity harness)."""
+        out = np.zeros(self.n, dtype=TRACE_DTYPE)
+        self._check(self.lib.rp_sweep_trace(self.h, out.ctypes.data, out.shape[0]))
+        return out
 
     def toggle_overlap_counting(self, on):
         self._check(self.lib.rp_toggle_overlap_counting(self.h, int(on)))

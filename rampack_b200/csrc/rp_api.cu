@@ -228,7 +228,8 @@ void rp_destroy(rp_handle *h) {
     for (void *p : {(void *) h->dInter, (void *) h->pos, (void *) h->orient, (void *) h->crel, (void *) h->cabs,
                     (void *) h->lastPos, (void *) h->lastCabs, (void *) h->tmpState, (void *) h->dCounters,
                     (void *) h->dFlags, (void *) h->dCellEnergy, (void *) h->dMoveOut, h->dStage,
-                    (void *) h->sweepMoved, (void *) h->trialRec, (void *) h->trialOrient, h->trialMeta})
+                    (void *) h->sweepMoved, (void *) h->trialRec, (void *) h->trialOrient, h->trialMeta,
+                    (void *) h->genRec, (void *) h->genTrialRec, (void *) h->genTrialCrel, (void *) h->genTrialU})
         if (p) cudaFree(p);
     if (h->stage) cudaFreeHost(h->stage);
     freeGrid(h->grid);
@@ -400,6 +401,13 @@ rp_status rp_sweep(rp_handle *h, const rp_sweep_params *params, rp_sweep_counter
     RP_EXPECT(params != nullptr, "params != NULL");
     RP_EXPECT(h->hasInteraction && h->n > 0, "packing and interaction must be set");
     sweep(h, *params, counters_out);
+    RP_API_END(h)
+}
+
+rp_status rp_sweep_trace(rp_handle *h, rp_trial_trace *out, uint64_t n) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(out != nullptr && n == h->n, "out != NULL && n == size()");
+    sweepTrace(h, out, n);
     RP_API_END(h)
 }
 

@@ -130,6 +130,15 @@ struct Handle {
     double *trialRec = nullptr, *trialOrient = nullptr;
     void *trialMeta = nullptr;
     size_t trialCap = 0;
+    // what rp_sweep_trace needs to know about the last rp_sweep call
+    bool lastSweepValid = false, lastSweepGeneric = false, lastSweepRotated = false;
+    int lastColourOrder[8] = {0, 1, 2, 3, 4, 5, 6, 7};
+    int lastSweepN[3] = {0, 0, 0};
+    int lastRecw = 6;
+    V3 lastImageShift[8];
+    // generic sweep (rp_sweep_generic.cuh): whole-particle records in cell order and the trial buffers
+    double *genRec = nullptr, *genTrialRec = nullptr, *genTrialCrel = nullptr, *genTrialU = nullptr;
+    size_t genRecCap = 0, genTrialRecCap = 0, genTrialCrelCap = 0, genTrialUCap = 0;
 
     // explicit trial move (Packing's temp slot): pos[3] orient[9] crel[16][3] cabs[16][3]
     double *tmpState = nullptr;
@@ -216,6 +225,7 @@ void fp64Peak(Handle *h, double *dfmaGflops, double *dmulDaddGflops);
 // ---- rp_sweep.cu ----
 void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out);
 void cullThresholds(const Handle *h, const double relCell[3], float *thr2, float *half);
+void sweepTrace(Handle *h, rp_trial_trace *out, unsigned long long n);
 
 }  // namespace rp
 

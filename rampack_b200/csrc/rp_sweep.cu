@@ -23,7 +23,9 @@
 //     grid is an ordinary periodic grid over [s, s+1)^3 and the only lattice translations are the reference's 27.
 #include "rp_internal.cuh"
 #include "rp_sweep_kernel.cuh"
+#include "rp_sweep_generic.cuh"
 #include <cstdlib>
+#include <limits>
 
 namespace rp {
 
@@ -160,26 +162,63 @@ static void launchSweep(Handle *h, const SweepArgs &A0, const SweepGrid &sg, con
     }
 }
 
+static void ensureTrialBuffers(Handle *h) {
+    if (h->n > h->trialCap || !h->trialRec) {
+        for (void *q : {(void *) h->trialRec, (void *) h->trialOrient, h->trialMeta}) if (q) cudaFree(q);
+        h->trialRec = h->trialOrient = nullptr;
+        h->trialMeta = nullptr;
+        size_t cap = h->n + h->n / 8 + 64;
+        RP_CUDA(cudaMalloc(&h->trialRec, cap * 6 * sizeof(double)));
+        RP_CUDA(cudaMalloc(&h->trialOrient, cap * 9 * sizeof(double)));
+        RP_CUDA(cudaMalloc(&h->trialMeta, cap * sizeof(uint2)));
+        h->trialCap = cap;
+    }
+}
+
+static bool fastPathEligible(const Handle *h) {
+    const Inter &I = h->inter;
+    return I.k == 0 && I.soft == RP_SOFT_NONE && (I.hard == RP_HARD_SPHERE || I.hard == RP_HARD_SPHEROCYLINDER)
+           && !h->overlapCounting && !std::getenv("RP_SWEEP_GENERIC");
+}
+
+static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &sg, const int colourOrder[8],
+                         const int refN[3], rp_sweep_counters *out);
+
 void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
     const Inter &I = h->inter;
-    if (I.k != 0 || I.soft != RP_SOFT_NONE || !(I.hard == RP_HARD_SPHERE || I.hard == RP_HARD_SPHEROCYLINDER))
-        throw rp_error(RP_ERR_UNSUPPORTED, "rp_sweep: only hard spheres and hard spherocylinders are implemented");
+    const bool fast = fastPathEligible(h);
     RP_EXPECT(p.kind >= RP_MOVE_TRANSLATION && p.kind <= RP_MOVE_ROTOTRANSLATION, "unknown sampler kind");
     bool translated = p.kind != RP_MOVE_ROTATION, rotated = p.kind != RP_MOVE_TRANSLATION;
     if (translated) RP_EXPECT(p.translation_step > 0, "translationStepSize > 0");
     if (rotated) RP_EXPECT(p.rotation_step > 0, "rotationStepSize > 0");
+    if (I.soft != RP_SOFT_NONE) RP_EXPECT(p.temperature > 0, "temperature > 0");
 
     double heights[3];
     boxHeights(h->box, heights);
     double volume = boxVolume(h->box);
     // cell width: at least totalRange (plus a rounding margin), and wide enough to hold ~16 particles
     const double TARGET_POPULATION = 16;
-    double width = std::max(I.totalRange * (1 + 1e-9), std::cbrt(TARGET_POPULATION * volume / static_cast<double>(h->n)));
+    double minWidth = I.totalRange * (1 + 1e-9);
+    int refN[3] = {0, 0, 0};
+    if (I.soft == RP_SOFT_LJ) {
+        // un-truncated potential: the pair set is "centres in adjacent cells of the reference-geometry grid"
+        // (rp_sweep_generic.cuh); two such centres are at most 2 reference cells apart along every axis
+        ensureGrid(h);
+        if (!h->hasGrid)
+            throw rp_error(RP_ERR_UNSUPPORTED, "rp_sweep: Lennard-Jones needs a box with a neighbour grid");
+        double cellMax = 0;
+        for (int i = 0; i < 3; i++) {
+            refN[i] = h->grid.n[i];
+            cellMax = std::max(cellMax, heights[i] / refN[i]);
+        }
+        minWidth = (2 * cellMax + (I.totalRange - I.range)) * (1 + 1e-9);
+    }
+    double width = std::max(minWidth, std::cbrt(TARGET_POPULATION * volume / static_cast<double>(h->n)));
     SweepGrid sg;
     size_t numCells = 1;
     for (int i = 0; i < 3; i++) {
         int n = static_cast<int>(floor(heights[i] / width));
-        if (n < 2 && heights[i] >= 2 * I.totalRange * (1 + 1e-9)) n = 2;
+        if (n < 2 && heights[i] >= 2 * minWidth) n = 2;
         if (n < 2)
             throw rp_error(RP_ERR_UNSUPPORTED, "rp_sweep: the box must be at least 2 x totalRange high along every "
                                                "axis for the checkerboard sweep");
@@ -201,6 +240,10 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
     for (int f = 0; f < 8; f++)
         sg.imageShift[f] = relToAbs(h->box, v3(f & 1, (f >> 1) & 1, (f >> 2) & 1));
     computeTranslations(h->box, sg.trans);
+    h->lastSweepValid = false;
+    for (int c = 0; c < 8; c++) { h->lastColourOrder[c] = colourOrder[c]; h->lastImageShift[c] = sg.imageShift[c]; }
+    for (int i = 0; i < 3; i++) h->lastSweepN[i] = sg.n[i];
+    h->lastSweepRotated = rotated;
 
     GridStore &g = h->sgrid;
     ensureGridCapacity(g, numCells, h->n);
@@ -219,6 +262,11 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
     k_sweep_keys<<<(n + 255) / 256, 256, 0, st>>>(n, h->cap, h->pos, h->box, sg, g.keys, g.cellFill);
     scanCells(h, g, &h->dFlags[1]);
     k_sweep_scatter<<<(n + 255) / 256, 256, 0, st>>>(n, g.keys, g.cellStart, g.cellFill, g.itemsTmp);
+    if (!fast) {
+        h->launches += 2;
+        sweepGeneric(h, p, sg, colourOrder, refN, out);
+        return;
+    }
     int recBlocks = static_cast<int>((numCells * 32 + 255) / 256);
     if (I.hard == RP_HARD_SPHERE)
         k_sweep_records<RP_HARD_SPHERE><<<recBlocks, 256, 0, st>>>(g.numCells, h->cap, g.cellStart, g.itemsTmp,
@@ -267,16 +315,7 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
     A.inter.scInner2 = I.scInner2;
     A.inter.scOuter2 = I.scOuter2;
     A.inter.scHalf = I.scHalfPlus;
-    if (h->n > h->trialCap || !h->trialRec) {
-        for (void *q : {(void *) h->trialRec, (void *) h->trialOrient, h->trialMeta}) if (q) cudaFree(q);
-        h->trialRec = h->trialOrient = nullptr;
-        h->trialMeta = nullptr;
-        size_t cap = h->n + h->n / 8 + 64;
-        RP_CUDA(cudaMalloc(&h->trialRec, cap * 6 * sizeof(double)));
-        RP_CUDA(cudaMalloc(&h->trialOrient, cap * 9 * sizeof(double)));
-        RP_CUDA(cudaMalloc(&h->trialMeta, cap * sizeof(uint2)));
-        h->trialCap = cap;
-    }
+    ensureTrialBuffers(h);
     TrialBuffers T;
     T.rec = h->trialRec;
     T.orient = h->trialOrient;
@@ -299,13 +338,188 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
     h->hasTrial = false;
     if (flags[3])
         throw rp_error(RP_ERR_CAPACITY, "rp_sweep: shared-memory staging capacity exceeded (cells skipped)");
+    h->lastSweepValid = true;
+    h->lastSweepGeneric = false;
+    h->lastRecw = 6;
     if (out) {
         out->attempted = counters[0];
         out->accepted = counters[1];
         out->rejected_domain = counters[2];
         out->rejected_overlap = counters[3];
+        out->rejected_energy = 0;
         out->sub_sweeps = 8;
         out->kernel_launches = 8 + 7;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// generic path: records, trials and the 8 colour launches of k_gen_sweep (rp_sweep_generic.cuh); called after the
+// keys / scan / scatter of the sweep grid
+// ---------------------------------------------------------------------------------------------------------------
+static GenLayout genLayout(const Inter &I) {
+    GenLayout L;
+    L.kk = I.kk;
+    int w = 3;
+    L.offOrient = -1;        // reserved for shapes whose pair test needs the whole orientation (XenoCollide)
+    if (I.k > 0) { L.offCentre = w; w += 3 * I.k; } else L.offCentre = 0;
+    L.offAux = -1;
+    if (I.hard == RP_HARD_SPHEROCYLINDER || I.hard == RP_HARD_POLYSPHEROCYLINDER) { L.offAux = w; w += 3 * I.kk; }
+    L.offCell = -1;
+    if (I.soft == RP_SOFT_LJ) { L.offCell = w; w += I.kk; }
+    L.recw = (w + 1) & ~1;
+    return L;
+}
+
+static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &sg, const int colourOrder[8],
+                         const int refN[3], rp_sweep_counters *out)
+{
+    const Inter &I = h->inter;
+    GridStore &g = h->sgrid;
+    cudaStream_t st = h->stream;
+    const int n = static_cast<int>(h->n);
+    GenArgs A;
+    std::memset(&A, 0, sizeof(A));
+    A.kind = p.kind;
+    A.transStep = p.translation_step;
+    A.rotStep = p.rotation_step;
+    A.temperature = I.soft != RP_SOFT_NONE ? p.temperature : 1.0;
+    A.seed = h->seed;
+    A.cycle = static_cast<unsigned int>(p.cycle);
+    A.pass = static_cast<unsigned int>(p.pass);
+    for (int i = 0; i < 3; i++) { A.nActive[i] = sg.n[i] / 2; A.refN[i] = refN[i]; A.refRelCell[i] = refN[i] ? 1.0 / refN[i] : 1.0; }
+    A.counting = h->overlapCounting ? 1 : 0;
+    double tr = I.totalRange * (1 + 1e-9);
+    A.cullRange2 = I.soft == RP_SOFT_LJ ? std::numeric_limits<double>::infinity() : tr * tr;
+    A.cap = h->cap;
+    A.ccap = h->centreCap;
+    A.L = genLayout(I);
+    const size_t recw = A.L.recw;
+
+    devEnsure(h->genRec, h->genRecCap, recw * h->n);
+    devEnsure(h->genTrialRec, h->genTrialRecCap, recw * h->n);
+    devEnsure(h->genTrialCrel, h->genTrialCrelCap, 3 * static_cast<size_t>(std::max(I.k, 1)) * h->n);
+    devEnsure(h->genTrialU, h->genTrialUCap, 2 * h->n);
+    ensureTrialBuffers(h);
+    GenTrialBuffers T;
+    T.rec = h->genTrialRec;
+    T.orient = h->trialOrient;
+    T.crel = h->genTrialCrel;
+    T.u = h->genTrialU;
+    T.dE = h->genTrialU + h->n;
+    T.meta = static_cast<uint2 *>(h->trialMeta);
+
+    int recBlocks = static_cast<int>((static_cast<size_t>(g.numCells) * 32 + 255) / 256);
+    k_gen_records<<<recBlocks, 256, 0, st>>>(g.numCells, A, sg, h->box, h->dInter, g.cellStart, g.itemsTmp, g.keys,
+                                             h->pos, h->orient, h->crel, g.items, h->genRec);
+    h->launches++;
+    RP_CUDA(cudaEventRecord(h->ev[1], st));
+    int flags[4];
+    RP_CUDA(cudaMemcpyAsync(flags, h->dFlags, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    RP_CUDA(cudaStreamSynchronize(st));
+    RP_CUDA(cudaGetLastError());
+    g.maxPopulation = flags[1];
+    A.capOwn = std::max(g.maxPopulation, 1);
+    size_t smem = static_cast<size_t>(A.capOwn) * (16 * recw + 48) + 64;
+    if (smem > 200 * 1024)
+        throw rp_error(RP_ERR_CAPACITY, "rp_sweep: a cell does not fit into shared memory");
+    static size_t configured = 0;
+    if (smem > configured) {
+        RP_CUDA(cudaFuncSetAttribute(k_gen_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     static_cast<int>(std::max<size_t>(smem, 48 * 1024))));
+        configured = std::max<size_t>(smem, 48 * 1024);
+    }
+    RP_CUDA(cudaEventRecord(h->ev[2], st));
+    k_gen_trials<<<(n + 127) / 128, 128, 0, st>>>(n, A, sg, h->box, h->dInter, g.items, g.keys, h->genRec, h->orient,
+                                                  h->crel, T);
+    h->launches++;
+    for (int c = 0; c < 8; c++) {
+        GenArgs Ac = A;
+        int col = colourOrder[c];
+        Ac.colour[0] = col & 1; Ac.colour[1] = (col >> 1) & 1; Ac.colour[2] = (col >> 2) & 1;
+        int blocks = A.nActive[0] * A.nActive[1] * A.nActive[2];
+        k_gen_sweep<<<blocks, GEN_THREADS, smem, st>>>(Ac, sg, h->box, h->dInter, g.cellStart, g.items, h->genRec, T,
+                                                       h->pos, h->orient, h->crel, h->cabs, h->dCounters, h->dFlags);
+        h->launches++;
+    }
+    RP_CUDA(cudaEventRecord(h->ev[3], st));
+    unsigned long long counters[6];
+    RP_CUDA(cudaMemcpyAsync(counters, h->dCounters, sizeof(counters), cudaMemcpyDeviceToHost, st));
+    RP_CUDA(cudaMemcpyAsync(flags, h->dFlags, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    RP_CUDA(cudaStreamSynchronize(st));
+    RP_CUDA(cudaGetLastError());
+    float msGrid = 0, msSweep = 0;
+    cudaEventElapsedTime(&msGrid, h->ev[0], h->ev[1]);
+    cudaEventElapsedTime(&msSweep, h->ev[2], h->ev[3]);
+    h->lastSweepMs = msSweep;
+    h->lastSweepGridMs = msGrid;
+    h->gridDirty = true;
+    h->hasTrial = false;
+    if (flags[3])
+        throw rp_error(RP_ERR_CAPACITY, "rp_sweep: shared-memory staging capacity exceeded (cells skipped)");
+    if (h->overlapCounting)
+        h->numOverlaps = static_cast<unsigned long long>(static_cast<long long>(h->numOverlaps)
+                                                         + static_cast<long long>(counters[5]));
+    h->lastSweepValid = true;
+    h->lastSweepGeneric = true;
+    h->lastRecw = A.L.recw;
+    if (out) {
+        out->attempted = counters[0];
+        out->accepted = counters[1];
+        out->rejected_domain = counters[2];
+        out->rejected_overlap = counters[3];
+        out->rejected_energy = counters[4];
+        out->sub_sweeps = 8;
+        out->kernel_launches = 8 + 7;
+    }
+}
+
+// parity harness: the trials of the last rp_sweep call (device buffers are intact until the next call)
+void sweepTrace(Handle *h, rp_trial_trace *out, unsigned long long n) {
+    if (!h->lastSweepValid)
+        throw rp_error(RP_ERR_STATE, "rp_sweep_trace: no completed rp_sweep call to report");
+    cudaStream_t st = h->stream;
+    GridStore &g = h->sgrid;
+    const size_t recw = h->lastRecw;
+    std::vector<int> items(n), keys(n);
+    std::vector<uint2> meta(n);
+    std::vector<double> rec(n * recw), orient(n * 9), u(2 * n, 0.0), canon(9 * n);
+    RP_CUDA(cudaMemcpyAsync(items.data(), g.items, n * sizeof(int), cudaMemcpyDeviceToHost, st));
+    RP_CUDA(cudaMemcpyAsync(keys.data(), g.keys, n * sizeof(int), cudaMemcpyDeviceToHost, st));
+    RP_CUDA(cudaMemcpyAsync(meta.data(), h->trialMeta, n * sizeof(uint2), cudaMemcpyDeviceToHost, st));
+    RP_CUDA(cudaMemcpyAsync(rec.data(), h->lastSweepGeneric ? h->genTrialRec : h->trialRec,
+                            n * recw * sizeof(double), cudaMemcpyDeviceToHost, st));
+    const bool haveOrient = h->lastSweepGeneric || h->lastSweepRotated;
+    if (haveOrient)
+        RP_CUDA(cudaMemcpyAsync(orient.data(), h->trialOrient, n * 9 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    else
+        for (int q = 0; q < 9; q++)
+            RP_CUDA(cudaMemcpyAsync(canon.data() + q * n, h->orient + q * h->cap, n * sizeof(double),
+                                    cudaMemcpyDeviceToHost, st));
+    if (h->lastSweepGeneric)
+        RP_CUDA(cudaMemcpyAsync(u.data(), h->genTrialU, 2 * n * sizeof(double), cudaMemcpyDeviceToHost, st));
+    RP_CUDA(cudaStreamSynchronize(st));
+    int stepOfColour[8];
+    for (int c = 0; c < 8; c++) stepOfColour[h->lastColourOrder[c]] = c;
+    const int *sn = h->lastSweepN;
+    for (unsigned long long slot = 0; slot < n; slot++) {
+        const int id = items[slot];
+        rp_trial_trace &t = out[id];
+        const int cell = keys[id] & 0x0FFFFFFF, f = (keys[id] >> 28) & 7;
+        const int cx = cell % sn[0], cy = (cell / sn[0]) % sn[1], cz = cell / (sn[0] * sn[1]);
+        t.particle = id;
+        t.colour_step = stepOfColour[(cx & 1) | ((cy & 1) << 1) | ((cz & 1) << 2)];
+        t.cell = cell;
+        t.order_key = meta[slot].y;
+        t.slot = static_cast<int>(slot);
+        t.status = meta[slot].x == 4u ? 1 : (meta[slot].x == 2u ? 2 : 0);
+        t.reserved = 0;
+        for (int d = 0; d < 3; d++) t.position[d] = rec[slot * recw + d];
+        for (int q = 0; q < 9; q++) t.orientation[q] = haveOrient ? orient[slot * 9 + q] : canon[q * n + id];
+        const V3 s = f ? h->lastImageShift[f] : v3(0, 0, 0);
+        t.image_shift[0] = s.x; t.image_shift[1] = s.y; t.image_shift[2] = s.z;
+        t.u = u[slot];
+        t.dE = h->lastSweepGeneric ? u[n + slot]
+                                   : (t.status == 1 ? 0.0 : std::numeric_limits<double>::infinity());
     }
 }
 

@@ -287,6 +287,7 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
             const int particleId = items[ownStart + tid];
             double *r = rec + 6 * static_cast<size_t>(ownStart + tid);
             for (int q = 0; q < 6; q++) r[q] = t[q];
+            T.meta[ownStart + tid].x = 4u;      // accepted (read back by rp_sweep_trace only)
             if (batch0 + SW_MAXOWN < numOwnAll) {
                 // later batches see this particle as a frozen candidate in its new state (own cell: no translation)
                 double *cs = cand + 6 * static_cast<size_t>(ownBegin + tid);

@@ -42,7 +42,9 @@ typedef enum rp_hard_kind {
     RP_HARD_SPHERE = 1,              /* SphereTraits::HardInteraction        (src/core/shapes/SphereTraits.cpp:56-75) */
     RP_HARD_SPHEROCYLINDER = 2,      /* SpherocylinderTraits                 (src/core/shapes/SpherocylinderTraits.cpp:28-73) */
     RP_HARD_POLYSPHERE = 3,          /* PolysphereTraits::HardInteraction    (src/core/shapes/PolysphereTraits.cpp:97-136) */
-    RP_HARD_POLYSPHEROCYLINDER = 4   /* PolyspherocylinderTraits             (src/core/shapes/PolyspherocylinderTraits.cpp:109-170) */
+    RP_HARD_POLYSPHEROCYLINDER = 4,  /* PolyspherocylinderTraits             (src/core/shapes/PolyspherocylinderTraits.cpp:109-170) */
+    RP_HARD_XENOCOLLIDE = 5          /* XenoCollideTraits<...> (generic_convex, smooth_wedge, polyhedral_wedge:
+                                        src/core/shapes/XenoCollideTraits.h:147-171, geometry/xenocollide/XenoCollide.h) */
 } rp_hard_kind;
 
 /* Soft part: replaces CentralInteraction::calculateEnergyBetween (src/core/interactions/CentralInteraction.h:58-67) */
@@ -54,6 +56,48 @@ typedef enum rp_soft_kind {
 } rp_soft_kind;
 
 #define RP_MAX_CENTRES 16
+
+/*
+ * XenoCollide geometry as a flat program.  The reference builds a tree of AbstractXCGeometry objects
+ * (src/geometry/xenocollide/XCPrimitives.h, XCOperations.h, XCBodyBuilder.cpp); a `describe()` walk over that tree
+ * emits one rp_xc_node per object (children before parents) and one rp_xc_entry per child slot of XCSum / XCDiff /
+ * XCMax ({geometry, pos, rot} in the order of the object's `entries` vector; XCDiff: geom1 then geom2).
+ * params are the constructor arguments of the reference class, in its order:
+ *   POINT x y z | SEGMENT halfLength | RECTANGLE halfSideX halfSideY | CUBOID halfSides[3] | DISK radius |
+ *   SPHERE radius | ELLIPSE semiAxisX semiAxisY | ELLIPSOID semiAxes[3] | FOOTBALL halfLength radius |
+ *   SAUCER radius halfThickness | SMOOTH_WEDGE R r l (SmoothWedgeTraits::CollideGeometry) |
+ *   POLYHEDRAL_WEDGE axBottom ayBottom axTop ayTop length (PolyhedralWedgeTraits::CollideGeometry)
+ * Circumsphere / insphere radii and centres are derived by the library with the reference's expressions.
+ */
+typedef enum rp_xc_kind {
+    RP_XC_POINT = 0, RP_XC_SEGMENT = 1, RP_XC_RECTANGLE = 2, RP_XC_CUBOID = 3, RP_XC_DISK = 4, RP_XC_SPHERE = 5,
+    RP_XC_ELLIPSE = 6, RP_XC_ELLIPSOID = 7, RP_XC_FOOTBALL = 8, RP_XC_SAUCER = 9, RP_XC_SMOOTH_WEDGE = 10,
+    RP_XC_POLYHEDRAL_WEDGE = 11,
+    RP_XC_SUM = 16,   /* XCSum  (XCOperations.cpp:38-73)  */
+    RP_XC_DIFF = 17,  /* XCDiff (XCOperations.cpp:75-99)  */
+    RP_XC_MAX = 18    /* XCMax  (XCOperations.cpp:101-185), the `wrap` of XCBodyBuilder */
+} rp_xc_kind;
+#define RP_XC_MAX_NODES 32
+#define RP_XC_MAX_ENTRIES 32
+typedef struct rp_xc_node {
+    int32_t kind;          /* rp_xc_kind */
+    int32_t n_entries;     /* operations: number of child entries */
+    int32_t first_entry;   /* operations: index of the first child entry */
+    int32_t reserved;
+    double params[6];
+} rp_xc_node;
+typedef struct rp_xc_entry {
+    int32_t node;          /* child geometry: index of an EARLIER node */
+    int32_t reserved;
+    double pos[3];
+    double rot[9];         /* row-major */
+} rp_xc_entry;
+typedef struct rp_xc_program {
+    int32_t n_nodes, n_entries;
+    rp_xc_node nodes[RP_XC_MAX_NODES];
+    rp_xc_entry entries[RP_XC_MAX_ENTRIES];
+    int32_t root[RP_MAX_CENTRES];   /* getCollideGeometry(i): node of interaction centre i (root[0] when n_centres == 0) */
+} rp_xc_program;
 
 /*
  * POD description of an Interaction (the reference hides these parameters behind a vtable; a `describe()` on the
@@ -72,6 +116,7 @@ typedef struct rp_interaction_desc {
     double centres[RP_MAX_CENTRES][3];         /* body-frame centre positions */
     double centre_radius[RP_MAX_CENTRES];      /* polysphere bead radius / polyspherocylinder radius */
     double centre_half_axis[RP_MAX_CENTRES][3];/* polyspherocylinder body-frame half axis */
+    const rp_xc_program *xc;           /* RP_HARD_XENOCOLLIDE: the collide geometries (copied by rp_set_interaction) */
 } rp_interaction_desc;
 
 typedef struct rp_config {

@@ -25,6 +25,11 @@
 #include "core/shapes/PolysphereTraits.h"
 #include "core/shapes/PolyspherocylinderTraits.h"
 #include "core/shapes/CompoundShapeTraits.h"
+#include "core/shapes/XenoCollideTraits.h"
+#include "core/shapes/SmoothWedgeTraits.h"
+#include "core/shapes/PolyhedralWedgeTraits.h"
+#include "geometry/xenocollide/XCPrimitives.h"
+#include "geometry/xenocollide/XCOperations.h"
 #include "core/interactions/LennardJonesInteraction.h"
 #include "core/interactions/RepulsiveLennardJonesInteraction.h"
 #include "core/interactions/SquareInverseCoreInteraction.h"
@@ -79,6 +84,85 @@ namespace {
         for (int k = 0; k < 3; k++) out[k] = s.getPosition()[k];
         for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) out[3 + 3*r + c] = s.getOrientation()(r, c);
     }
+
+    // RP_HARD_XENOCOLLIDE: the reference's OWN geometry classes instantiated from the flat program the C ABI takes
+    // (include/rampack_b200.h, rp_xc_program).  Only public constructors / add() are used, in the order a
+    // describe() walk of the reference tree emits them, so the objects are what XCBodyBuilder would have built.
+    std::shared_ptr<AbstractXCGeometry> buildXcNode(const rp_xc_program &P, int idx,
+                                                    std::vector<std::shared_ptr<AbstractXCGeometry>> &built)
+    {
+        const rp_xc_node &N = P.nodes[idx];
+        const double *a = N.params;
+        switch (N.kind) {
+            case RP_XC_POINT:     return std::make_shared<XCPoint>(Vector<3>{a[0], a[1], a[2]});
+            case RP_XC_SEGMENT:   return std::make_shared<XCSegment>(a[0]);
+            case RP_XC_RECTANGLE: return std::make_shared<XCRectangle>(a[0], a[1]);
+            case RP_XC_CUBOID:    return std::make_shared<XCCuboid>(Vector<3>{a[0], a[1], a[2]});
+            case RP_XC_DISK:      return std::make_shared<XCDisk>(a[0]);
+            case RP_XC_SPHERE:    return std::make_shared<XCSphere>(a[0]);
+            case RP_XC_ELLIPSE:   return std::make_shared<XCEllipse>(a[0], a[1]);
+            case RP_XC_ELLIPSOID: return std::make_shared<XCEllipsoid>(Vector<3>{a[0], a[1], a[2]});
+            case RP_XC_FOOTBALL:  return std::make_shared<XCFootball>(a[0], a[1]);
+            case RP_XC_SAUCER:    return std::make_shared<XCSaucer>(a[0], a[1]);
+            case RP_XC_SMOOTH_WEDGE:
+                return std::make_shared<PolymorphicXCAdapter<SmoothWedgeTraits::CollideGeometry>>(
+                    SmoothWedgeTraits::CollideGeometry(a[0], a[1], a[2]));
+            case RP_XC_POLYHEDRAL_WEDGE:
+                return std::make_shared<PolymorphicXCAdapter<PolyhedralWedgeTraits::CollideGeometry>>(
+                    PolyhedralWedgeTraits::CollideGeometry(a[0], a[1], a[2], a[3], a[4]));
+            case RP_XC_SUM: {
+                auto g = std::make_shared<XCSum>();
+                for (int e = 0; e < N.n_entries; e++) {
+                    const rp_xc_entry &E = P.entries[N.first_entry + e];
+                    g->add(built.at(E.node), vec(E.pos), mat(E.rot));
+                }
+                return g;
+            }
+            case RP_XC_MAX: {
+                auto g = std::make_shared<XCMax>();
+                for (int e = 0; e < N.n_entries; e++) {
+                    const rp_xc_entry &E = P.entries[N.first_entry + e];
+                    g->add(built.at(E.node), vec(E.pos), mat(E.rot));
+                }
+                return g;
+            }
+            case RP_XC_DIFF: {
+                const rp_xc_entry &E1 = P.entries[N.first_entry], &E2 = P.entries[N.first_entry + 1];
+                return std::make_shared<XCDiff>(built.at(E1.node), mat(E1.rot), vec(E1.pos),
+                                                built.at(E2.node), mat(E2.rot), vec(E2.pos));
+            }
+            default:
+                throw std::runtime_error("unknown rp_xc_kind");
+        }
+    }
+
+    // Same pattern as GenericXenoCollideTraits (one geometry) and SmoothWedgeTraits / PolyhedralWedgeTraits (one
+    // geometry per interaction centre): the CRTP base supplies overlapBetween / getRangeRadius unchanged.
+    class ProgramXCTraits : public XenoCollideTraits<ProgramXCTraits> {
+        std::vector<std::shared_ptr<AbstractXCGeometry>> geometries;
+        std::vector<Vector<3>> centres;
+    public:
+        ProgramXCTraits(std::vector<std::shared_ptr<AbstractXCGeometry>> geometries, std::vector<Vector<3>> centres)
+                : XenoCollideTraits({0, 0, 1}, {1, 0, 0}, {0, 0, 0}, 1.0),
+                  geometries{std::move(geometries)}, centres{std::move(centres)}
+        { }
+        [[nodiscard]] const AbstractXCGeometry &getCollideGeometry(std::size_t i = 0) const {
+            return *this->geometries.at(i);
+        }
+        [[nodiscard]] std::vector<Vector<3>> getInteractionCentres() const override { return this->centres; }
+    };
+
+    std::shared_ptr<ShapeTraits> makeXcTraits(const rp_interaction_desc *d) {
+        if (!d->xc) throw std::runtime_error("RP_HARD_XENOCOLLIDE without a program");
+        const rp_xc_program &P = *d->xc;
+        std::vector<std::shared_ptr<AbstractXCGeometry>> built;
+        for (int i = 0; i < P.n_nodes; i++) built.push_back(buildXcNode(P, i, built));
+        std::vector<std::shared_ptr<AbstractXCGeometry>> geoms;
+        std::vector<Vector<3>> centres;
+        for (int c = 0; c < (d->n_centres > 0 ? d->n_centres : 1); c++) geoms.push_back(built.at(P.root[c]));
+        for (int c = 0; c < d->n_centres; c++) centres.push_back(vec(d->centres[c]));
+        return std::make_shared<ProgramXCTraits>(std::move(geoms), std::move(centres));
+    }
 }
 
 extern "C" {
@@ -111,6 +195,9 @@ void *rpr_traits_create(const rp_interaction_desc *d) {
                 t->traits = std::make_shared<PolyspherocylinderTraits>(std::move(geom));
                 break;
             }
+            case RP_HARD_XENOCOLLIDE:
+                t->traits = makeXcTraits(d);
+                break;
             case RP_HARD_NONE: {
                 if (!soft) { delete t; return nullptr; }
                 if (d->n_centres == 0) {

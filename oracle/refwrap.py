@@ -21,7 +21,8 @@ class InteractionDesc(C.Structure):
                 ("n_centres", C.c_int32), ("reserved", C.c_int32),
                 ("centres", (C.c_double * 3) * RP_MAX_CENTRES),
                 ("centre_radius", C.c_double * RP_MAX_CENTRES),
-                ("centre_half_axis", (C.c_double * 3) * RP_MAX_CENTRES)]
+                ("centre_half_axis", (C.c_double * 3) * RP_MAX_CENTRES),
+                ("xc", C.c_void_p)]      # const rp_xc_program * (include/rampack_b200.h)
 
 
 class Move(C.Structure):
@@ -45,8 +46,11 @@ PAIR_DTYPE = np.dtype([("pos1", "<f8", 3), ("orientation1", "<f8", 9), ("idx1", 
 
 def copy_desc(src):
     """Copies any ctypes struct with the rp_interaction_desc layout into this module's InteractionDesc."""
+    assert C.sizeof(src) == C.sizeof(InteractionDesc), "rp_interaction_desc layouts disagree"
     d = InteractionDesc()
     C.memmove(C.byref(d), C.byref(src), C.sizeof(InteractionDesc))
+    # the desc only holds a POINTER to the XenoCollide program: keep the pointee alive with the copy
+    d._xc_keepalive = getattr(src, "_xc_keepalive", None)
     return d
 
 

@@ -14,9 +14,29 @@ from . import build as _build
 RP_MAX_CENTRES = 16
 
 RP_OK, RP_ERR_PRECONDITION, RP_ERR_CUDA, RP_ERR_STATE, RP_ERR_UNSUPPORTED, RP_ERR_CAPACITY = range(6)
-RP_HARD_NONE, RP_HARD_SPHERE, RP_HARD_SPHEROCYLINDER, RP_HARD_POLYSPHERE, RP_HARD_POLYSPHEROCYLINDER = range(5)
+(RP_HARD_NONE, RP_HARD_SPHERE, RP_HARD_SPHEROCYLINDER, RP_HARD_POLYSPHERE, RP_HARD_POLYSPHEROCYLINDER,
+ RP_HARD_XENOCOLLIDE) = range(6)
+# rp_xc_kind
+(RP_XC_POINT, RP_XC_SEGMENT, RP_XC_RECTANGLE, RP_XC_CUBOID, RP_XC_DISK, RP_XC_SPHERE, RP_XC_ELLIPSE, RP_XC_ELLIPSOID,
+ RP_XC_FOOTBALL, RP_XC_SAUCER, RP_XC_SMOOTH_WEDGE, RP_XC_POLYHEDRAL_WEDGE) = range(12)
+RP_XC_SUM, RP_XC_DIFF, RP_XC_MAX = 16, 17, 18
+RP_XC_MAX_NODES = RP_XC_MAX_ENTRIES = 32
 RP_SOFT_NONE, RP_SOFT_LJ, RP_SOFT_WCA, RP_SOFT_SIC = range(4)
 RP_MOVE_TRANSLATION, RP_MOVE_ROTATION, RP_MOVE_ROTOTRANSLATION = range(3)
+
+
+class XcNode(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("n_entries", C.c_int32), ("first_entry", C.c_int32), ("reserved", C.c_int32),
+                ("params", C.c_double * 6)]
+
+
+class XcEntry(C.Structure):
+    _fields_ = [("node", C.c_int32), ("reserved", C.c_int32), ("pos", C.c_double * 3), ("rot", C.c_double * 9)]
+
+
+class XcProgram(C.Structure):
+    _fields_ = [("n_nodes", C.c_int32), ("n_entries", C.c_int32), ("nodes", XcNode * RP_XC_MAX_NODES),
+                ("entries", XcEntry * RP_XC_MAX_ENTRIES), ("root", C.c_int32 * RP_MAX_CENTRES)]
 
 
 class InteractionDesc(C.Structure):
@@ -25,7 +45,8 @@ class InteractionDesc(C.Structure):
                 ("n_centres", C.c_int32), ("reserved", C.c_int32),
                 ("centres", (C.c_double * 3) * RP_MAX_CENTRES),
                 ("centre_radius", C.c_double * RP_MAX_CENTRES),
-                ("centre_half_axis", (C.c_double * 3) * RP_MAX_CENTRES)]
+                ("centre_half_axis", (C.c_double * 3) * RP_MAX_CENTRES),
+                ("xc", C.POINTER(XcProgram))]
 
 
 class Config(C.Structure):
@@ -141,8 +162,11 @@ def dptr(a):
 
 
 def make_desc(hard=RP_HARD_NONE, soft=RP_SOFT_NONE, radius=0.0, length=0.0, epsilon=0.0, sigma=0.0, centres=None,
-              centre_radius=None, centre_half_axis=None):
+              centre_radius=None, centre_half_axis=None, xc=None):
     d = InteractionDesc()
+    if xc is not None:
+        d.xc = C.pointer(xc)
+        d._xc_keepalive = xc        # the desc only holds a pointer: keep the program alive with it
     d.hard_kind, d.soft_kind = hard, soft
     d.radius, d.length, d.epsilon, d.sigma = radius, length, epsilon, sigma
     centres = [] if centres is None else centres

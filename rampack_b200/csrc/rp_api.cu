@@ -9,7 +9,7 @@ static thread_local std::string tlsError;
 
 // Flatten an rp_interaction_desc into the device parameter block.  Every threshold is computed with the expression
 // the reference evaluates per call (citations in rp_pair.cuh) so that the compared doubles are bit-identical.
-static void fillInter(const rp_interaction_desc &d, Inter &I) {
+static void fillInter(const rp_interaction_desc &d, Inter &I, const XcProgram *xc) {
     std::memset(&I, 0, sizeof(I));
     I.hard = d.hard_kind;
     I.soft = d.soft_kind;
@@ -59,6 +59,16 @@ static void fillInter(const rp_interaction_desc &d, Inter &I) {
                 if (I.ccircum[i] > maxC) maxC = I.ccircum[i];
             }
             hardRange = 2 * maxC;
+            break;
+        }
+        case RP_HARD_XENOCOLLIDE: {
+            // XenoCollideTraits::getRangeRadius (XenoCollideTraits.h:188-202): 2 * max circumsphere radius
+            RP_EXPECT(xc != nullptr, "RP_HARD_XENOCOLLIDE needs desc.xc");
+            double maxRadius = 0;
+            for (int i = 0; i < std::max(d.n_centres, 1); i++)
+                maxRadius = std::max(maxRadius, xc->nodes[xc->root[i]].circum);
+            hardRange = 2 * maxRadius;
+            hardConvex = true;
             break;
         }
         default:
@@ -231,6 +241,8 @@ void rp_destroy(rp_handle *h) {
                     (void *) h->sweepMoved, (void *) h->trialRec, (void *) h->trialOrient, h->trialMeta,
                     (void *) h->genRec, (void *) h->genTrialRec, (void *) h->genTrialCrel, (void *) h->genTrialU})
         if (p) cudaFree(p);
+    if (h->dXc) cudaFree(h->dXc);
+    delete h->xcHost;
     if (h->stage) cudaFreeHost(h->stage);
     freeGrid(h->grid);
     freeGrid(h->tempGrid);
@@ -244,7 +256,15 @@ rp_status rp_set_interaction(rp_handle *h, const rp_interaction_desc *desc) {
     RP_API_BEGIN(h)
     RP_EXPECT(desc != nullptr, "desc != NULL");
     Inter I;
-    fillInter(*desc, I);
+    if (desc->hard_kind == RP_HARD_XENOCOLLIDE) {
+        RP_EXPECT(desc->xc != nullptr, "RP_HARD_XENOCOLLIDE needs desc.xc");
+        if (!h->xcHost) h->xcHost = new XcProgram;
+        buildXcProgram(*desc->xc, desc->n_centres, *h->xcHost);
+        if (!h->dXc) RP_CUDA(cudaMalloc(&h->dXc, sizeof(XcProgram)));
+        RP_CUDA(cudaMemcpyAsync(h->dXc, h->xcHost, sizeof(XcProgram), cudaMemcpyHostToDevice, h->stream));
+    }
+    fillInter(*desc, I, h->xcHost);
+    I.xc = h->dXc;
     RP_EXPECT(I.range > 0, "interaction.getRangeRadius() > 0");
     h->inter = I;
     RP_CUDA(cudaMemcpyAsync(h->dInter, &h->inter, sizeof(Inter), cudaMemcpyHostToDevice, h->stream));

@@ -102,6 +102,7 @@ struct Handle {
     bool hasInteraction = false;
     Inter inter;            // host copy
     Inter *dInter = nullptr;
+    XcProgram *xcHost = nullptr, *dXc = nullptr;   // RP_HARD_XENOCOLLIDE geometries (host copy, device copy)
 
     // particles, canonical (original particle order), SoA with stride `cap`
     size_t n = 0, cap = 0;
@@ -219,6 +220,8 @@ void acceptMove(Handle *h);
 double tryScaling(Handle *h, const Box &newBox);
 void revertScaling(Handle *h);
 void pairTestBatch(Handle *h, const rp_pair *pairs, unsigned long long n, unsigned char *verdict, double *energy);
+// ---- rp_xc_setup.cu ----
+void buildXcProgram(const rp_xc_program &src, int nRoots, XcProgram &dst);
 // ---- rp_stats.cu ----
 void neighbourStats(Handle *h, double *kCand, double *kFull);
 void fp64Peak(Handle *h, double *dfmaGflops, double *dmulDaddGflops);

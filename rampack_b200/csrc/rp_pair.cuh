@@ -3,6 +3,7 @@
 #pragma once
 
 #include "rp_math.cuh"
+#include "rp_xc.cuh"
 #include "../../include/rampack_b200.h"
 
 namespace rp {
@@ -31,6 +32,7 @@ struct Inter {
     double chalf[RP_MAX_CENTRES][3];     // polyspherocylinder body-frame half axis
     double ccircum[RP_MAX_CENTRES];      // radius + |halfAxis| (core/shapes/PolyspherocylinderTraits.cpp:78-84)
     bool convex;                         // Interaction::isConvex()
+    const XcProgram *xc;                 // RP_HARD_XENOCOLLIDE: device copy of the collide geometries
 };
 
 // "aux" vector carried beside each interaction centre in the sorted pair records:
@@ -92,6 +94,26 @@ RP_HD bool overlapBetween(const Inter &I, V3 pos1, V3 aux1, int c1, V3 pos2, V3 
             return false;
     }
 }
+
+// Interaction::overlapBetween for shapes whose pair test needs the whole orientation (XenoCollide); getO1 / getO2
+// return the orientation matrices and are only called when the sphere pre-filters do not decide
+// (core/shapes/XenoCollideTraits.h:147-171)
+template <typename BC, typename O1, typename O2>
+RP_HD bool overlapBetweenOriented(const Inter &I, V3 pos1, O1 &&getO1, int c1, V3 pos2, O2 &&getO2, int c2,
+                                  const BC &bc, int *supportCalls = nullptr)
+{
+    const XcProgram &P = *I.xc;
+    const int g1 = P.root[c1], g2 = P.root[c2];
+    double rCircumsphere = P.nodes[g1].circum + P.nodes[g2].circum;
+    double rInsphere = P.nodes[g1].in + P.nodes[g2].in;
+    V3 pos2bc = pos2 + bc.translation(pos1, pos2);
+    double dist2 = norm2(pos2bc - pos1);
+    if (dist2 > rCircumsphere * rCircumsphere) return false;
+    if (dist2 < rInsphere * rInsphere) return true;
+    M33 o1 = getO1(), o2 = getO2();
+    return xcIntersect(P, g1, o1, pos1, g2, o2, pos2bc, 1.0e-12, supportCalls);
+}
+RP_HD bool needsOrientation(const Inter &I) { return I.hard == RP_HARD_XENOCOLLIDE; }
 
 // CentralInteraction::calculateEnergyForDistance2 (core/interactions/*.cpp)
 RP_HD double energyForDistance2(const Inter &I, double distance2) {

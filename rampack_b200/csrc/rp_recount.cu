@@ -63,10 +63,31 @@ void recalcAbsoluteCentres(Handle *h) {
 // full recount with the neighbour grid: one warp per real cell; half-shell rule 9a+3b+c > 13 on the offsets
 // (core/NeighbourGrid.cpp:127-131) with a = x offset
 // ---------------------------------------------------------------------------------------------------------------
+// Interaction::overlapBetween for any supported hard part.  Shapes whose test needs the whole orientation matrix
+// (XenoCollide) fetch it from the canonical SoA arrays only when the sphere pre-filters do not decide; o1 != nullptr
+// overrides the first particle's orientation (the trial state of an explicit move).
+__device__ __forceinline__ M33 loadOrientSoA(const double *__restrict__ orient, size_t cap, int particle) {
+    M33 o;
+    for (int q = 0; q < 9; q++) o.a[q] = orient[q * cap + particle];
+    return o;
+}
+template <typename BC>
+__device__ __forceinline__ bool overlapAny(const Inter &I, const double *__restrict__ orient, size_t cap, V3 pos1,
+                                           V3 aux1, const M33 *o1, int particle1, int c1, V3 pos2, V3 aux2,
+                                           int particle2, int c2, const BC &bc)
+{
+    if (needsOrientation(I))
+        return overlapBetweenOriented(
+            I, pos1, [&] { return o1 ? *o1 : loadOrientSoA(orient, cap, particle1); }, c1, pos2,
+            [&] { return loadOrientSoA(orient, cap, particle2); }, c2, bc);
+    return overlapBetween(I, pos1, aux1, c1, pos2, aux2, c2, bc);
+}
+
 template <bool ENERGY>
 __global__ void __launch_bounds__(256) k_recount_grid(GridView g, const Inter *__restrict__ interPtr, int earlyExit,
                                                       unsigned long long *__restrict__ count, int *__restrict__ found,
-                                                      double *__restrict__ cellEnergy)
+                                                      double *__restrict__ cellEnergy,
+                                                      const double *__restrict__ orient, size_t cap)
 {
     __shared__ Inter I;
     for (int i = threadIdx.x; i < static_cast<int>(sizeof(Inter) / sizeof(int)); i += blockDim.x)
@@ -102,7 +123,9 @@ __global__ void __launch_bounds__(256) k_recount_grid(GridView g, const Inter *_
                 energy += energyBetween(I, pos1, pos2, none);
             } else {
                 V3 aux2 = v3(g.ax[j], g.ay[j], g.az[j]);
-                if (overlapBetween(I, pos1, aux1, centre1, pos2, aux2, centre2, none)) overlaps++;
+                if (overlapAny(I, orient, cap, pos1, aux1, nullptr, particle1, centre1, pos2, aux2, particle2,
+                               centre2, none))
+                    overlaps++;
             }
         }
         // pairs with the 13 "positive" neighbour cells
@@ -121,7 +144,9 @@ __global__ void __launch_bounds__(256) k_recount_grid(GridView g, const Inter *_
                     energy += energyBetween(I, pos1, pos2, bc);
                 } else {
                     V3 aux2 = v3(g.ax[j], g.ay[j], g.az[j]);
-                    if (overlapBetween(I, pos1, aux1, centre1, pos2, aux2, centre2, bc)) overlaps++;
+                    if (overlapAny(I, orient, cap, pos1, aux1, nullptr, particle1, centre1, pos2, aux2, particle2,
+                                   centre2, bc))
+                        overlaps++;
                 }
             }
         }
@@ -212,8 +237,9 @@ __global__ void __launch_bounds__(256) k_recount_nogrid(ParticleView P, Box box,
             if (ENERGY) {
                 energy += energyBetween(I, pos1, pos2, bc);
             } else {
-                V3 aux1 = pairAux(I, loadOrient(P, pi), 0), aux2 = pairAux(I, loadOrient(P, pj), 0);
-                if (overlapBetween(I, pos1, aux1, 0, pos2, aux2, 0, bc)) overlaps++;
+                M33 o1 = loadOrient(P, pi);
+                V3 aux1 = pairAux(I, o1, 0), aux2 = pairAux(I, loadOrient(P, pj), 0);
+                if (overlapAny(I, P.orient, P.cap, pos1, aux1, &o1, pi, 0, pos2, aux2, pj, 0, bc)) overlaps++;
             }
         } else {
             M33 o1, o2;
@@ -223,7 +249,8 @@ __global__ void __launch_bounds__(256) k_recount_nogrid(ParticleView P, Box box,
                 for (int c2 = 0; c2 < P.k; c2++) {
                     V3 pos2 = loadCabs(P, pj * P.k + c2);
                     if (ENERGY) energy += energyBetween(I, pos1, pos2, bc);
-                    else if (overlapBetween(I, pos1, pairAux(I, o1, c1), c1, pos2, pairAux(I, o2, c2), c2, bc))
+                    else if (overlapAny(I, P.orient, P.cap, pos1, pairAux(I, o1, c1), &o1, pi, c1, pos2,
+                                        pairAux(I, o2, c2), pj, c2, bc))
                         overlaps++;
                 }
             }
@@ -294,7 +321,7 @@ unsigned long long countTotalOverlaps(Handle *h, bool earlyExit) {
         GridView g = makeView(h->grid);
         int blocks = (g.numCells * 32 + 255) / 256;
         k_recount_grid<false><<<blocks, 256, 0, st>>>(g, h->dInter, earlyExit ? 1 : 0, h->dCounters, h->dFlags + 2,
-                                                     nullptr);
+                                                     nullptr, h->orient, h->cap);
     } else {
         long long nPairs = static_cast<long long>(h->n) * (h->n - 1) / 2;
         int blocks = static_cast<int>(std::min<long long>(1184, (nPairs + 255) / 256));
@@ -319,7 +346,8 @@ double totalEnergy(Handle *h) {
         GridView g = makeView(h->grid);
         ensureCellEnergy(h, g.numCells + 1);
         int blocks = (g.numCells * 32 + 255) / 256;
-        k_recount_grid<true><<<blocks, 256, 0, st>>>(g, h->dInter, 0, nullptr, nullptr, h->dCellEnergy);
+        k_recount_grid<true><<<blocks, 256, 0, st>>>(g, h->dInter, 0, nullptr, nullptr, h->dCellEnergy, h->orient,
+                                                    h->cap);
         parts = g.numCells;
     } else {
         long long nPairs = static_cast<long long>(h->n) * (h->n - 1) / 2;
@@ -378,7 +406,9 @@ __device__ void scanParticle(const TrialState &S, int orig, const ParticleView &
                     V3 pos2 = v3(g.px[j], g.py[j], g.pz[j]);
                     if (wantOverlaps) {
                         V3 aux2 = v3(g.ax[j], g.ay[j], g.az[j]);
-                        if (overlapBetween(I, pos1, aux1, c1, pos2, aux2, centre2, bc)) overlaps++;
+                        if (overlapAny(I, P.orient, P.cap, pos1, aux1, &S.orient, orig, c1, pos2, aux2, particle2,
+                                       centre2, bc))
+                            overlaps++;
                     }
                     if (wantEnergy) energy += energyBetween(I, pos1, pos2, bc);
                 }
@@ -392,7 +422,9 @@ __device__ void scanParticle(const TrialState &S, int orig, const ParticleView &
                 V3 pos2 = loadPos(P, j);
                 if (wantOverlaps) {
                     V3 aux2 = pairAux(I, loadOrient(P, j), 0);
-                    if (overlapBetween(I, S.pos, pairAux(I, S.orient, 0), 0, pos2, aux2, 0, bc)) overlaps++;
+                    if (overlapAny(I, P.orient, P.cap, S.pos, pairAux(I, S.orient, 0), &S.orient, orig, 0, pos2, aux2,
+                                   j, 0, bc))
+                        overlaps++;
                 }
                 if (wantEnergy) energy += energyBetween(I, S.pos, pos2, bc);
             } else {
@@ -401,8 +433,8 @@ __device__ void scanParticle(const TrialState &S, int orig, const ParticleView &
                 for (int c1 = 0; c1 < I.k; c1++) {
                     for (int c2 = 0; c2 < I.k; c2++) {
                         V3 pos2 = loadCabs(P, j * I.k + c2);
-                        if (wantOverlaps && overlapBetween(I, S.cabs[c1], pairAux(I, S.orient, c1), c1, pos2,
-                                                           pairAux(I, o2, c2), c2, bc))
+                        if (wantOverlaps && overlapAny(I, P.orient, P.cap, S.cabs[c1], pairAux(I, S.orient, c1),
+                                                       &S.orient, orig, c1, pos2, pairAux(I, o2, c2), j, c2, bc))
                             overlaps++;
                         if (wantEnergy) energy += energyBetween(I, S.cabs[c1], pos2, bc);
                     }
@@ -662,7 +694,9 @@ __global__ void k_pair_batch(unsigned long long n, const rp_pair *__restrict__ p
         int c1 = static_cast<int>(p.idx1), c2 = static_cast<int>(p.idx2);
         if (verdict)
             verdict[i] = (I.hard != RP_HARD_NONE)
-                         && overlapBetween(I, pos1, pairAux(I, o1, c1), c1, pos2, pairAux(I, o2, c2), c2, bc);
+                         && (needsOrientation(I)
+                             ? overlapBetweenOriented(I, pos1, [&] { return o1; }, c1, pos2, [&] { return o2; }, c2, bc)
+                             : overlapBetween(I, pos1, pairAux(I, o1, c1), c1, pos2, pairAux(I, o2, c2), c2, bc));
         if (energy)
             energy[i] = (I.soft != RP_SOFT_NONE) ? energyBetween(I, pos1, pos2, bc) : 0.0;
     }

@@ -360,7 +360,8 @@ static GenLayout genLayout(const Inter &I) {
     GenLayout L;
     L.kk = I.kk;
     int w = 3;
-    L.offOrient = -1;        // reserved for shapes whose pair test needs the whole orientation (XenoCollide)
+    L.offOrient = -1;        // shapes whose pair test needs the whole orientation (XenoCollide)
+    if (I.hard == RP_HARD_XENOCOLLIDE) { L.offOrient = w; w += 9; }
     if (I.k > 0) { L.offCentre = w; w += 3 * I.k; } else L.offCentre = 0;
     L.offAux = -1;
     if (I.hard == RP_HARD_SPHEROCYLINDER || I.hard == RP_HARD_POLYSPHEROCYLINDER) { L.offAux = w; w += 3 * I.kk; }

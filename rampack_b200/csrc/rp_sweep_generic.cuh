@@ -228,7 +228,13 @@ __device__ __forceinline__ void pairTerms(const Inter &I, const GenArgs &A, cons
             V3 pos2 = ld3(b + L.offCentre + 3 * c2);
             if (wantOv) {
                 V3 aux2 = L.offAux >= 0 ? ld3(b + L.offAux + 3 * c2) : v3(0, 0, 0);
-                if (overlapBetween(I, pos1, aux1, c1, pos2, aux2, c2, bc)) {
+                const bool hit = needsOrientation(I)
+                    ? overlapBetweenOriented(I, pos1, [&] { M33 o; for (int q = 0; q < 9; q++) o.a[q] = a[L.offOrient + q]; return o; },
+                                             c1, pos2,
+                                             [&] { M33 o; for (int q = 0; q < 9; q++) o.a[q] = b[L.offOrient + q]; return o; },
+                                             c2, bc)
+                    : overlapBetween(I, pos1, aux1, c1, pos2, aux2, c2, bc);
+                if (hit) {
                     (*ov)++;
                     if (firstOnly) return;
                 }

@@ -29,7 +29,9 @@ def test_library_exports_every_declared_symbol():
 
 def test_struct_layouts_match_header():
     # sizes implied by include/rampack_b200.h (all members naturally aligned)
-    assert C.sizeof(capi.InteractionDesc) == 8 + 4 * 8 + 8 + 16 * 3 * 8 + 16 * 8 + 16 * 3 * 8
+    assert C.sizeof(capi.InteractionDesc) == 8 + 4 * 8 + 8 + 16 * 3 * 8 + 16 * 8 + 16 * 3 * 8 + 8
+    assert C.sizeof(capi.XcNode) == 16 + 6 * 8 and C.sizeof(capi.XcEntry) == 8 + 12 * 8
+    assert C.sizeof(capi.XcProgram) == 8 + 32 * 64 + 32 * 104 + 16 * 4
     assert C.sizeof(capi.Config) == 24
     assert C.sizeof(capi.Move) == 16 + 12 * 8
     assert C.sizeof(capi.SweepParams) == 8 + 4 * 8

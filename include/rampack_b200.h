@@ -233,6 +233,24 @@ rp_status rp_cached_overlaps(rp_handle *h, uint64_t *count_out);
 /* ---- parity harness: Interaction::overlapBetween / calculateEnergyBetween on explicit pairs ---- */
 rp_status rp_pair_test_batch(rp_handle *h, const rp_pair *pairs, uint64_t n, uint8_t *verdict_out, double *energy_out);
 
+/* ---- spatial sharding over the GPUs of one node (no reference analogue: the reference is one OpenMP process;
+ * semantic model: Simulation::performMovesWithDomainDivision, src/core/Simulation.cpp:389-441).
+ * One process per GPU.  Rank 0 calls rp_comm_unique_id and the host distributes the 128 bytes (MPI, torch.distributed,
+ * a file ...); every rank then calls rp_comm_init on its handle.  Afterwards all ranks must make the SAME sequence of
+ * calls with the same arguments (rp_upload of the same state included): the state is replicated, rp_sweep runs only
+ * the cell layers of this rank's slab and exchanges accepted moves over NCCL, rp_count_total_overlaps /
+ * rp_try_scaling split the recount and all-reduce the count on the device.  An N-GPU run is bit-identical to the
+ * 1-GPU run with the same seed.  Hard spheres / spherocylinders only in this round. */
+rp_status rp_comm_unique_id(uint8_t id_out[128]);
+rp_status rp_comm_init(rp_handle *h, const uint8_t id[128], int32_t rank, int32_t n_ranks);
+rp_status rp_comm_destroy(rp_handle *h);
+/* bytes this rank sent in the per-colour halo exchanges / received in the end-of-cycle gather of the last rp_sweep */
+rp_status rp_comm_stats(rp_handle *h, uint64_t *halo_bytes, uint64_t *gather_bytes);
+/* host logic of the sharded sweep, callable without a device: rank `rank` of `n_ranks` owns the cell layers
+ * [2 * out[0], 2 * out[1]) of `n_layers_z`; after a sub-sweep of `colour` (bit 2 = z parity of the active cells) it
+ * sends the accepted moves of layer out[2] to rank out[4] and receives those of layer out[3] from rank out[5] */
+rp_status rp_shard_plan(int32_t n_layers_z, int32_t n_ranks, int32_t rank, int32_t colour, int32_t out[6]);
+
 /* ---- timing hook for bench.py: device milliseconds spent inside the kernels of the last call ---- */
 rp_status rp_last_kernel_ms(rp_handle *h, double *sweep_ms, double *sweep_grid_ms, double *rebuild_ms,
                             double *scaling_ms);

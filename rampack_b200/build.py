@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "librampack_b200.so")
-SOURCES = ["rp_api.cu", "rp_grid.cu", "rp_recount.cu", "rp_sweep.cu", "rp_stats.cu", "rp_xc_setup.cu"]
+SOURCES = ["rp_api.cu", "rp_grid.cu", "rp_recount.cu", "rp_sweep.cu", "rp_stats.cu", "rp_xc_setup.cu", "rp_shard.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
               "-Xcompiler", "-fPIC,-ffp-contract=off", "-Xptxas", "-v"]
 
@@ -47,7 +47,7 @@ def build(force=False, verbose=False):
         f.write("\n".join(log))
     if verbose:
         print("\n".join(log))
-    cmd = [nvcc, "-shared", "-o", OUT] + objs + ["-lcudart"]
+    cmd = [nvcc, "-shared", "-o", OUT] + objs + ["-lcudart", "-ldl"]
     subprocess.check_call(cmd)
     return OUT
 

@@ -89,7 +89,8 @@ SYMBOLS = ["rp_create", "rp_destroy", "rp_last_error", "rp_version", "rp_set_int
            "rp_download", "rp_size", "rp_rebuild_grid", "rp_grid_info_get", "rp_cell_numbers",
            "rp_count_total_overlaps", "rp_total_energy", "rp_try_move", "rp_accept_move", "rp_try_scaling",
            "rp_revert_scaling", "rp_sweep", "rp_sweep_trace", "rp_toggle_overlap_counting", "rp_cached_overlaps",
-           "rp_pair_test_batch", "rp_neighbour_stats", "rp_measure_fp64_peak", "rp_last_kernel_ms", "rp_launch_count", "rp_synchronize"]
+           "rp_pair_test_batch", "rp_comm_unique_id", "rp_comm_init", "rp_comm_destroy", "rp_comm_stats", "rp_shard_plan",
+           "rp_neighbour_stats", "rp_measure_fp64_peak", "rp_last_kernel_ms", "rp_launch_count", "rp_synchronize"]
 
 _lib = None
 
@@ -131,6 +132,11 @@ def load():
     lib.rp_sweep.argtypes = [H, C.POINTER(SweepParams), C.POINTER(SweepCounters)]
     lib.rp_sweep_trace.argtypes = [H, C.c_void_p, C.c_uint64]
     lib.rp_toggle_overlap_counting.argtypes = [H, C.c_int]
+    lib.rp_comm_unique_id.argtypes = [C.c_void_p]
+    lib.rp_comm_init.argtypes = [H, C.c_void_p, C.c_int32, C.c_int32]
+    lib.rp_comm_destroy.argtypes = [H]
+    lib.rp_shard_plan.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32)]
+    lib.rp_comm_stats.argtypes = [H, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     lib.rp_cached_overlaps.argtypes = [H, C.POINTER(C.c_uint64)]
     lib.rp_pair_test_batch.argtypes = [H, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
     lib.rp_last_kernel_ms.argtypes = [H, dp, dp, dp, dp]
@@ -144,6 +150,17 @@ def load():
             fn.restype = C.c_int
     _lib = lib
     return lib
+
+
+def shard_plan(n_layers_z, n_ranks, rank, colour):
+    """rp_shard_plan as a dict (host logic of the sharded sweep; needs no device)."""
+    lib = load()
+    out = (C.c_int32 * 6)()
+    st = lib.rp_shard_plan(n_layers_z, n_ranks, rank, colour, out)
+    if st != RP_OK:
+        raise RpError(st, lib.rp_last_error(None).decode())
+    keys = ("a_lo", "a_hi", "send_layer", "recv_layer", "peer_send", "peer_recv")
+    return dict(zip(keys, out))
 
 
 class RpError(RuntimeError):
@@ -283,6 +300,28 @@ class Device:
         out = np.zeros(self.n, dtype=TRACE_DTYPE)
         self._check(self.lib.rp_sweep_trace(self.h, out.ctypes.data, out.shape[0]))
         return out
+
+    @staticmethod
+    def comm_unique_id():
+        """128 bytes (ncclUniqueId) created on rank 0; distribute them to all ranks, then comm_init()."""
+        lib = load()
+        buf = (C.c_uint8 * 128)()
+        st = lib.rp_comm_unique_id(buf)
+        if st != RP_OK:
+            raise RpError(st, lib.rp_last_error(None).decode())
+        return bytes(buf)
+
+    def comm_init(self, unique_id, rank, n_ranks):
+        buf = (C.c_uint8 * 128).from_buffer_copy(unique_id)
+        self._check(self.lib.rp_comm_init(self.h, buf, rank, n_ranks))
+
+    def comm_destroy(self):
+        self._check(self.lib.rp_comm_destroy(self.h))
+
+    def comm_stats(self):
+        a, b = C.c_uint64(), C.c_uint64()
+        self._check(self.lib.rp_comm_stats(self.h, C.byref(a), C.byref(b)))
+        return {"halo_bytes": a.value, "gather_bytes": b.value}
 
     def toggle_overlap_counting(self, on):
         self._check(self.lib.rp_toggle_overlap_counting(self.h, int(on)))

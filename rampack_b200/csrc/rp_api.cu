@@ -1,6 +1,7 @@
 // rp_api.cu — the C ABI of librampack_b200.so (include/rampack_b200.h): handle lifetime, state upload/download and
 // thin forwarding to the kernels.  No exception crosses the boundary: every entry point returns an rp_status.
 #include "rp_internal.cuh"
+#include "rp_shard.cuh"
 #include <limits>
 
 namespace rp {
@@ -241,6 +242,7 @@ void rp_destroy(rp_handle *h) {
                     (void *) h->sweepMoved, (void *) h->trialRec, (void *) h->trialOrient, h->trialMeta,
                     (void *) h->genRec, (void *) h->genTrialRec, (void *) h->genTrialCrel, (void *) h->genTrialU})
         if (p) cudaFree(p);
+    shardDestroy(h);
     if (h->dXc) cudaFree(h->dXc);
     delete h->xcHost;
     if (h->stage) cudaFreeHost(h->stage);
@@ -428,6 +430,45 @@ rp_status rp_sweep_trace(rp_handle *h, rp_trial_trace *out, uint64_t n) {
     RP_API_BEGIN(h)
     RP_EXPECT(out != nullptr && n == h->n, "out != NULL && n == size()");
     sweepTrace(h, out, n);
+    RP_API_END(h)
+}
+
+rp_status rp_comm_unique_id(uint8_t id_out[128]) {
+    try {
+        if (!id_out) throw rp::rp_error(RP_ERR_PRECONDITION, "id_out != NULL");
+        shardUniqueId(id_out);
+    } catch (const rp::rp_error &e) { rp::tlsError = e.what(); return static_cast<rp_status>(e.status); }
+    return RP_OK;
+}
+
+rp_status rp_comm_init(rp_handle *h, const uint8_t id[128], int32_t rank, int32_t n_ranks) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(id != nullptr && n_ranks <= 64, "id != NULL && n_ranks <= 64");
+    shardInit(h, id, rank, n_ranks);
+    RP_API_END(h)
+}
+
+rp_status rp_comm_destroy(rp_handle *h) {
+    RP_API_BEGIN(h)
+    shardDestroy(h);
+    RP_API_END(h)
+}
+
+rp_status rp_shard_plan(int32_t n_layers_z, int32_t n_ranks, int32_t rank, int32_t colour, int32_t out[6]) {
+    if (!out || n_ranks < 1 || rank < 0 || rank >= n_ranks || n_layers_z < 2 * n_ranks || (n_layers_z & 1)) {
+        rp::tlsError = "rp_shard_plan: need an even n_layers_z >= 2 * n_ranks and 0 <= rank < n_ranks";
+        return RP_ERR_PRECONDITION;
+    }
+    HaloPlan p = shardHaloPlan(n_layers_z, n_ranks, rank, colour);
+    out[0] = p.aLo; out[1] = p.aHi; out[2] = p.sendLayer; out[3] = p.recvLayer; out[4] = p.peerSend;
+    out[5] = p.peerRecv;
+    return RP_OK;
+}
+
+rp_status rp_comm_stats(rp_handle *h, uint64_t *halo_bytes, uint64_t *gather_bytes) {
+    RP_API_BEGIN(h)
+    if (halo_bytes) *halo_bytes = h->shard ? h->shard->lastHaloBytes : 0;
+    if (gather_bytes) *gather_bytes = h->shard ? h->shard->lastGatherBytes : 0;
     RP_API_END(h)
 }
 

@@ -164,6 +164,9 @@ struct Handle {
     void *dStage = nullptr;       // device staging for AoS <-> SoA transposes
     size_t dStageCap = 0;
 
+    // spatial sharding over the GPUs of one node (rp_shard.cuh); nullptr = single GPU
+    struct Shard *shard = nullptr;
+
     // timing of the last call
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     double lastSweepMs = 0, lastSweepGridMs = 0, lastRebuildMs = 0, lastScalingMs = 0;

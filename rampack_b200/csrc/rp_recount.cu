@@ -8,6 +8,7 @@
 //   Packing::tryScaling / revertScaling                             core/Packing.cpp:172-208, 363-371
 #include "rp_internal.cuh"
 #include "rp_recount_cull.cuh"
+#include "rp_shard.cuh"
 #include <limits>
 #include <cstdlib>
 
@@ -310,7 +311,16 @@ unsigned long long countTotalOverlaps(Handle *h, bool earlyExit) {
         A.inter.scHalf = I.scHalfPlus;
         A.earlyExit = earlyExit ? 1 : 0;
         cullThresholds(h, g.relCell, &A.cullThr2, &A.cullHalf);
-        int blocks = (g.numCells + RC_WARPS - 1) / RC_WARPS;
+        A.cellBegin = 0;
+        A.cellEnd = g.numCells;
+        if (shardActive(h)) {
+            // every pair is enumerated from exactly one cell (half-shell rule), so a split of the cells is a split
+            // of the pairs; the per-rank counts are summed on the device (ncclAllReduce below)
+            const long long P = h->shard->nranks, r = h->shard->rank;
+            A.cellBegin = static_cast<int>(r * g.numCells / P);
+            A.cellEnd = static_cast<int>((r + 1) * g.numCells / P);
+        }
+        int blocks = std::max(1, (A.cellEnd - A.cellBegin + RC_WARPS - 1) / RC_WARPS);
         if (I.hard == RP_HARD_SPHERE)
             k_recount_cull<RP_HARD_SPHERE><<<blocks, RC_WARPS * 32, 0, st>>>(g, h->grid.box, A, h->dCounters,
                                                                              h->dFlags + 2);
@@ -329,6 +339,7 @@ unsigned long long countTotalOverlaps(Handle *h, bool earlyExit) {
             k_recount_nogrid<false><<<blocks, 256, 0, st>>>(particleView(h), h->box, h->dInter, h->dCounters, nullptr);
     }
     h->launches++;
+    if (culled && shardActive(h)) shardAllReduceU64(h, h->dCounters, 1);
     unsigned long long result = 0;
     RP_CUDA(cudaMemcpyAsync(&result, h->dCounters, sizeof(result), cudaMemcpyDeviceToHost, st));
     RP_CUDA(cudaStreamSynchronize(st));

@@ -18,6 +18,7 @@ struct RecountArgs {
     SweepInter inter;
     float cullThr2, cullHalf;
     int earlyExit;
+    int cellBegin, cellEnd;     // cells this launch covers (sharded runs: this rank's share)
 };
 
 template <int HARD>
@@ -30,8 +31,8 @@ k_recount_cull(GridView g, Box box, RecountArgs A, unsigned long long *__restric
     __shared__ int sNbBegin[RC_WARPS][16], sNbStart[RC_WARPS][16], sNbT[RC_WARPS][16];
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int cell = blockIdx.x * RC_WARPS + warp;
-    if (cell >= g.numCells) return;
+    const int cell = A.cellBegin + blockIdx.x * RC_WARPS + warp;
+    if (cell >= A.cellEnd) return;
     if (A.earlyExit && *reinterpret_cast<volatile int *>(found)) return;
     const SweepInter &I = A.inter;
     float4 *ownF = sOwnF[warp], *ownU = sOwnU[warp];

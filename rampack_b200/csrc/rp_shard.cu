@@ -1,0 +1,258 @@
+// rp_shard.cu — see rp_shard.cuh.  NCCL is bound at run time (dlopen) so that librampack_b200.so has no link-time
+// dependency on it: a single-GPU user never loads NCCL, and inside a PyTorch process the already loaded
+// libnccl.so.2 is reused (RTLD_NOLOAD first) instead of a second copy.
+#include "rp_shard.cuh"
+#include "rp_sweep_kernel.cuh"
+#include <dlfcn.h>
+#include <nccl.h>
+
+namespace rp {
+
+namespace {
+struct NcclApi {
+    void *lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
+                              cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Broadcast)(const void *, void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+NcclApi nccl;
+
+template <typename F>
+void bind(F &fn, const char *name) {
+    fn = reinterpret_cast<F>(dlsym(nccl.lib, name));
+    if (!fn) throw rp_error(RP_ERR_STATE, std::string("NCCL symbol missing: ") + name);
+}
+
+void loadNccl() {
+    if (nccl.lib) return;
+    void *lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+    if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) throw rp_error(RP_ERR_STATE, std::string("cannot load NCCL (libnccl.so.2): ") + dlerror());
+    nccl.lib = lib;
+    bind(nccl.GetUniqueId, "ncclGetUniqueId");
+    bind(nccl.CommInitRank, "ncclCommInitRank");
+    bind(nccl.CommDestroy, "ncclCommDestroy");
+    bind(nccl.Send, "ncclSend");
+    bind(nccl.Recv, "ncclRecv");
+    bind(nccl.GroupStart, "ncclGroupStart");
+    bind(nccl.GroupEnd, "ncclGroupEnd");
+    bind(nccl.AllReduce, "ncclAllReduce");
+    bind(nccl.AllGather, "ncclAllGather");
+    bind(nccl.Broadcast, "ncclBroadcast");
+    bind(nccl.GetErrorString, "ncclGetErrorString");
+}
+
+#define RP_NCCL(call) do { ncclResult_t r_ = (call); if (r_ != ncclSuccess) \
+    throw rp::rp_error(RP_ERR_CUDA, std::string(#call) + ": " + nccl.GetErrorString(r_)); } while (0)
+
+ncclComm_t commOf(const Handle *h) { return static_cast<ncclComm_t>(h->shard->comm); }
+}  // namespace
+
+bool shardActive(const Handle *h) { return h->shard && h->shard->nranks > 1; }
+
+void shardUniqueId(unsigned char id[128]) {
+    loadNccl();
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    ncclUniqueId u;
+    RP_NCCL(nccl.GetUniqueId(&u));
+    std::memcpy(id, &u, 128);
+}
+
+void shardInit(Handle *h, const unsigned char id[128], int rank, int nranks) {
+    RP_EXPECT(nranks >= 1 && rank >= 0 && rank < nranks, "0 <= rank < nranks");
+    shardDestroy(h);
+    h->shard = new Shard;
+    h->shard->rank = rank;
+    h->shard->nranks = nranks;
+    if (nranks == 1) return;
+    loadNccl();
+    ncclUniqueId u;
+    std::memcpy(&u, id, 128);
+    ncclComm_t comm;
+    RP_NCCL(nccl.CommInitRank(&comm, nranks, u, rank));
+    h->shard->comm = comm;
+    RP_CUDA(cudaMalloc(&h->shard->dCounts, 64 * sizeof(unsigned long long)));
+}
+
+void shardDestroy(Handle *h) {
+    if (!h->shard) return;
+    Shard *s = h->shard;
+    if (s->comm) nccl.CommDestroy(static_cast<ncclComm_t>(s->comm));
+    for (void *p : {(void *) s->sendBuf, (void *) s->recvBuf, (void *) s->gatherBuf, (void *) s->dLayerStart,
+                    (void *) s->dCounts})
+        if (p) cudaFree(p);
+    delete s;
+    h->shard = nullptr;
+}
+
+void shardSlab(int nActiveZ, int nranks, int r, int *aLo, int *aHi) {
+    *aLo = static_cast<int>(static_cast<long long>(r) * nActiveZ / nranks);
+    *aHi = static_cast<int>(static_cast<long long>(r + 1) * nActiveZ / nranks);
+}
+
+HaloPlan shardHaloPlan(int nz, int P, int r, int colour) {
+    HaloPlan p;
+    shardSlab(nz / 2, P, r, &p.aLo, &p.aHi);
+    const int pz = (colour >> 2) & 1;
+    // even-z colours changed my bottom layer, which rank r-1 reads next; odd-z colours my top layer (rank r+1)
+    p.sendLayer = pz == 0 ? 2 * p.aLo : 2 * p.aHi - 1;
+    p.peerSend = pz == 0 ? (r + P - 1) % P : (r + 1) % P;
+    p.peerRecv = pz == 0 ? (r + 1) % P : (r + P - 1) % P;
+    p.recvLayer = pz == 0 ? (2 * p.aHi) % nz : (2 * p.aLo - 1 + nz) % nz;
+    return p;
+}
+
+__global__ void k_layer_starts(int nz, int layerCells, const int *__restrict__ cellStart, int *__restrict__ out) {
+    int z = blockIdx.x * blockDim.x + threadIdx.x;
+    if (z <= nz) out[z] = cellStart[z * layerCells];
+}
+
+void shardQueueLayerStarts(Handle *h, int nx, int ny, int nz) {
+    Shard *s = h->shard;
+    devEnsure(s->dLayerStart, s->layerCap, static_cast<size_t>(nz) + 1);
+    k_layer_starts<<<(nz + 1 + 127) / 128, 128, 0, h->stream>>>(nz, nx * ny, h->sgrid.cellStart, s->dLayerStart);
+    h->launches++;
+    s->layerStart.resize(nz + 1);
+    RP_CUDA(cudaMemcpyAsync(s->layerStart.data(), s->dLayerStart, (nz + 1) * sizeof(int), cudaMemcpyDeviceToHost,
+                            h->stream));
+}
+
+// accepted moves (meta.x == 4) of the slots [s0, s1); xyColour >= 0 keeps only cells of that x/y parity
+__global__ void k_pack_moves(int s0, int s1, int xyColour, int nx, int ny, const int *__restrict__ items,
+                             const int *__restrict__ keys, const uint2 *__restrict__ meta,
+                             const double *__restrict__ rec, const double *__restrict__ trialOrient, int rotated,
+                             MoveMsg *__restrict__ out)
+{
+    int slot = s0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= s1) return;
+    if (meta[slot].x != 4u) return;
+    if (xyColour >= 0) {
+        int cell = keys[items[slot]] & 0x0FFFFFFF;
+        int cx = cell % nx, cy = (cell / nx) % ny;
+        if (((cx & 1) | ((cy & 1) << 1)) != xyColour) return;
+    }
+    unsigned long long at = atomicAdd(reinterpret_cast<unsigned long long *>(&out[0].slot), 1ull);
+    MoveMsg &m = out[1 + at];
+    m.slot = slot;
+    for (int q = 0; q < 6; q++) m.rec[q] = rec[6 * static_cast<size_t>(slot) + q];
+    if (rotated) for (int q = 0; q < 9; q++) m.orient[q] = trialOrient[9 * static_cast<size_t>(slot) + q];
+}
+
+// the receiving side of the sweep kernel's write-back (same arithmetic: Shape::translate, core/Shape.cpp:9-12)
+__global__ void k_apply_moves(const MoveMsg *__restrict__ in, int translated, int rotated, Box box, size_t cap,
+                              const int *__restrict__ items, double *__restrict__ rec, double *__restrict__ pos,
+                              double *__restrict__ orient, uint2 *__restrict__ meta)
+{
+    long long count = in[0].slot;
+    long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const MoveMsg &m = in[1 + i];
+    const int slot = static_cast<int>(m.slot), id = items[slot];
+    for (int q = 0; q < 6; q++) rec[6 * static_cast<size_t>(slot) + q] = m.rec[q];
+    if (translated) {
+        V3 np = v3(m.rec[0], m.rec[1], m.rec[2]);
+        V3 p = np + pbcCorrection(box, np);
+        pos[id] = p.x; pos[cap + id] = p.y; pos[2 * cap + id] = p.z;
+    }
+    if (rotated) for (int q = 0; q < 9; q++) orient[q * cap + id] = m.orient[q];
+    meta[slot].x = 4u;
+}
+
+static void ensureMsgBuf(MoveMsg *&buf, size_t &cap, size_t need) {
+    if (need <= cap && buf) return;
+    if (buf) cudaFree(buf);
+    buf = nullptr;
+    size_t newCap = need + need / 4 + 64;
+    RP_CUDA(cudaMalloc(&buf, (newCap + 1) * sizeof(MoveMsg)));
+    cap = newCap;
+}
+
+static void pack(Handle *h, int s0, int s1, int xyColour, int nx, int ny, bool rotated, MoveMsg *out) {
+    RP_CUDA(cudaMemsetAsync(out, 0, sizeof(MoveMsg), h->stream));
+    if (s1 > s0) {
+        k_pack_moves<<<(s1 - s0 + 255) / 256, 256, 0, h->stream>>>(s0, s1, xyColour, nx, ny, h->sgrid.items,
+                                                                  h->sgrid.keys, static_cast<uint2 *>(h->trialMeta),
+                                                                  h->sgrid.rec, h->trialOrient, rotated ? 1 : 0, out);
+        h->launches++;
+    }
+}
+
+static void apply(Handle *h, const MoveMsg *in, size_t capacity, bool translated, bool rotated) {
+    if (capacity == 0) return;
+    k_apply_moves<<<static_cast<int>((capacity + 255) / 256), 256, 0, h->stream>>>(
+        in, translated ? 1 : 0, rotated ? 1 : 0, h->box, h->cap, h->sgrid.items, h->sgrid.rec, h->pos, h->orient,
+        static_cast<uint2 *>(h->trialMeta));
+    h->launches++;
+}
+
+void shardHaloExchange(Handle *h, int colour, int nx, int ny, int nz, bool translated, bool rotated) {
+    Shard *s = h->shard;
+    const int P = s->nranks, r = s->rank;
+    const HaloPlan plan = shardHaloPlan(nz, P, r, colour);
+    const int sendLayer = plan.sendLayer, recvLayer = plan.recvLayer, peerSend = plan.peerSend,
+              peerRecv = plan.peerRecv;
+    const std::vector<int> &L = s->layerStart;
+    const size_t sendCapNow = static_cast<size_t>(L[sendLayer + 1] - L[sendLayer]);
+    const size_t recvCapNow = static_cast<size_t>(L[recvLayer + 1] - L[recvLayer]);
+    ensureMsgBuf(s->sendBuf, s->sendCap, sendCapNow);
+    ensureMsgBuf(s->recvBuf, s->recvCap, recvCapNow);
+    pack(h, L[sendLayer], L[sendLayer + 1], colour & 3, nx, ny, rotated, s->sendBuf);
+    const size_t dblPerMsg = sizeof(MoveMsg) / sizeof(double);
+    RP_NCCL(nccl.GroupStart());
+    RP_NCCL(nccl.Send(s->sendBuf, (sendCapNow + 1) * dblPerMsg, ncclDouble, peerSend, commOf(h), h->stream));
+    RP_NCCL(nccl.Recv(s->recvBuf, (recvCapNow + 1) * dblPerMsg, ncclDouble, peerRecv, commOf(h), h->stream));
+    RP_NCCL(nccl.GroupEnd());
+    apply(h, s->recvBuf, recvCapNow, translated, rotated);
+    s->lastHaloBytes += (sendCapNow + 1) * sizeof(MoveMsg);
+}
+
+void shardGatherCycle(Handle *h, int nz, bool translated, bool rotated) {
+    Shard *s = h->shard;
+    const int P = s->nranks, r = s->rank;
+    const std::vector<int> &L = s->layerStart;
+    std::vector<int> lo(P), hi(P);
+    size_t total = 0;
+    std::vector<size_t> offset(P);
+    for (int q = 0; q < P; q++) {
+        int aLo, aHi;
+        shardSlab(nz / 2, P, q, &aLo, &aHi);
+        lo[q] = L[2 * aLo];
+        hi[q] = L[2 * aHi];
+        offset[q] = total;
+        total += static_cast<size_t>(hi[q] - lo[q]) + 1;      // + header
+    }
+    ensureMsgBuf(s->gatherBuf, s->gatherCap, total);
+    MoveMsg *mine = s->gatherBuf + offset[r];
+    pack(h, lo[r], hi[r], -1, 0, 0, rotated, mine);
+    // message counts of all ranks -> host (exact broadcast sizes)
+    RP_NCCL(nccl.AllGather(&mine[0].slot, s->dCounts, 1, ncclUint64, commOf(h), h->stream));
+    unsigned long long counts[64];
+    RP_CUDA(cudaMemcpyAsync(counts, s->dCounts, P * sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
+    RP_CUDA(cudaStreamSynchronize(h->stream));
+    const size_t dblPerMsg = sizeof(MoveMsg) / sizeof(double);
+    RP_NCCL(nccl.GroupStart());
+    for (int q = 0; q < P; q++) {
+        MoveMsg *buf = s->gatherBuf + offset[q];
+        RP_NCCL(nccl.Broadcast(buf, buf, (counts[q] + 1) * dblPerMsg, ncclDouble, q, commOf(h), h->stream));
+        if (q != r) s->lastGatherBytes += (counts[q] + 1) * sizeof(MoveMsg);
+    }
+    RP_NCCL(nccl.GroupEnd());
+    for (int q = 0; q < P; q++)
+        if (q != r) apply(h, s->gatherBuf + offset[q], counts[q], translated, rotated);
+}
+
+void shardAllReduceU64(Handle *h, unsigned long long *dValues, int count) {
+    RP_NCCL(nccl.AllReduce(dValues, dValues, count, ncclUint64, ncclSum, commOf(h), h->stream));
+}
+
+}  // namespace rp

@@ -1,0 +1,56 @@
+// rp_shard.cuh — spatial sharding of the sweep over the GPUs of one node (north_star: "per-sweep halo exchange over
+// NCCL/NVLink and a device-side all-reduce for the volume-move overlap count").  The reference has no analogue (one
+// process, OpenMP); its semantic model is the domain decomposition of Simulation::performMovesWithDomainDivision
+// (core/Simulation.cpp:389-441): domains that are far enough apart move concurrently.
+//
+// Round-1 design: the STATE is replicated (every rank holds all particles and builds the same sweep grid from the same
+// Philox key — bit-identical on every rank), the COMPUTE is sharded: the cell layers along z are cut into one slab per
+// rank (an even number of layers, so both parities are present), rank r runs the active cells of its slab only.
+//   * after every colour: the accepted moves of the ONE boundary layer a neighbour will read next are sent to that
+//     neighbour (even-z colours: bottom layer -> rank r-1, odd-z colours: top layer -> rank r+1; ncclSend/ncclRecv,
+//     fixed-capacity buffers, no host synchronisation);
+//   * after the eighth colour: every rank broadcasts the accepted moves of its slab (exact sizes, one count exchange)
+//     so that the replicated state is identical again before the next grid build / box move / download.
+// Result: an N-GPU run is bit-identical to the 1-GPU run with the same seed (tests/test_gpu_shard.py).
+#pragma once
+
+#include "rp_internal.cuh"
+
+namespace rp {
+
+struct MoveMsg {                 // 128 bytes; element 0 of every buffer is the header: slot = number of messages
+    long long slot;
+    double rec[6];               // new sorted record {P'(3), half axis(3)}
+    double orient[9];            // new orientation (rotating samplers only)
+};
+
+struct Shard {
+    void *comm = nullptr;        // ncclComm_t
+    int rank = 0, nranks = 1;
+    MoveMsg *sendBuf = nullptr, *recvBuf = nullptr, *gatherBuf = nullptr;
+    size_t sendCap = 0, recvCap = 0, gatherCap = 0;     // in messages (without header)
+    int *dLayerStart = nullptr;  // slot at which cell layer z begins, z = 0..nz
+    size_t layerCap = 0;
+    std::vector<int> layerStart; // host copy
+    unsigned long long *dCounts = nullptr;    // nranks message counts (all-gathered)
+    // timing of the last sharded sweep (ms, CUDA events on the handle's stream)
+    double lastHaloMs = 0, lastGatherMs = 0;
+    unsigned long long lastHaloBytes = 0, lastGatherBytes = 0;
+};
+
+bool shardActive(const Handle *h);
+void shardUniqueId(unsigned char id[128]);
+void shardInit(Handle *h, const unsigned char id[128], int rank, int nranks);
+void shardDestroy(Handle *h);
+// slab of rank r in active-cell layers: [aLo, aHi) of nActiveZ
+void shardSlab(int nActiveZ, int nranks, int r, int *aLo, int *aHi);
+// downloads the layer boundaries of the current sweep grid (call after the grid build, before the host sync)
+// who sends which cell layer to whom after a sub-sweep of `colour` (bit 2 = z parity); nz = cell layers along z
+struct HaloPlan { int aLo, aHi, sendLayer, recvLayer, peerSend, peerRecv; };
+HaloPlan shardHaloPlan(int nz, int nranks, int r, int colour);
+void shardQueueLayerStarts(Handle *h, int nx, int ny, int nz);
+void shardHaloExchange(Handle *h, int colour, int nx, int ny, int nz, bool translated, bool rotated);
+void shardGatherCycle(Handle *h, int nz, bool translated, bool rotated);
+void shardAllReduceU64(Handle *h, unsigned long long *dValues, int count);
+
+}  // namespace rp

@@ -24,6 +24,7 @@
 #include "rp_internal.cuh"
 #include "rp_sweep_kernel.cuh"
 #include "rp_sweep_generic.cuh"
+#include "rp_shard.cuh"
 #include <cstdlib>
 #include <limits>
 
@@ -147,18 +148,34 @@ static void launchSweep(Handle *h, const SweepArgs &A0, const SweepGrid &sg, con
     }
     GridStore &g = h->sgrid;
     int n = static_cast<int>(h->n);
-    k_sweep_trials<HARD><<<(n + 127) / 128, 128, 0, h->stream>>>(n, A0, sg, h->box, h->inter.scHalfPlus, g.items,
-                                                                  g.keys, g.rec, h->orient, T);
+    const bool sharded = shardActive(h);
+    const bool translated = A0.kind != RP_MOVE_ROTATION, rotated = A0.kind != RP_MOVE_TRANSLATION;
+    int activeLayers = A0.nActive[2];
+    if (sharded) {
+        int aLo, aHi;
+        shardSlab(A0.nActive[2], h->shard->nranks, h->shard->rank, &aLo, &aHi);
+        activeLayers = aHi - aLo;
+        h->shard->lastHaloBytes = h->shard->lastGatherBytes = 0;
+    }
+    int nTrials = A0.slotEnd - A0.slotBegin;
+    if (nTrials > 0)
+        k_sweep_trials<HARD><<<(nTrials + 127) / 128, 128, 0, h->stream>>>(n, A0, sg, h->box, h->inter.scHalfPlus,
+                                                                        g.items, g.keys, g.rec, h->orient, T);
     h->launches++;
     for (int c = 0; c < 8; c++) {
         SweepArgs A = A0;
         int col = colourOrder[c];
         A.colour[0] = col & 1; A.colour[1] = (col >> 1) & 1; A.colour[2] = (col >> 2) & 1;
-        int blocks = A.nActive[0] * A.nActive[1] * A.nActive[2];
+        int blocks = A.nActive[0] * A.nActive[1] * activeLayers;
         k_sweep<HARD, SW_THREADS><<<blocks, SW_THREADS, smem, h->stream>>>(A, sg, h->box, g.cellStart,
                                                                           g.items, g.rec, T, h->pos, h->orient,
                                                                           h->dCounters, h->dFlags);
         h->launches++;
+        if (sharded) shardHaloExchange(h, col, sg.n[0], sg.n[1], sg.n[2], translated, rotated);
+    }
+    if (sharded) {
+        shardGatherCycle(h, sg.n[2], translated, rotated);
+        shardAllReduceU64(h, h->dCounters, 4);
     }
 }
 
@@ -263,10 +280,16 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
     scanCells(h, g, &h->dFlags[1]);
     k_sweep_scatter<<<(n + 255) / 256, 256, 0, st>>>(n, g.keys, g.cellStart, g.cellFill, g.itemsTmp);
     if (!fast) {
+        if (shardActive(h))
+            throw rp_error(RP_ERR_UNSUPPORTED, "rp_sweep: the sharded sweep covers hard spheres / spherocylinders "
+                                               "only (other interactions: run replicas)");
         h->launches += 2;
         sweepGeneric(h, p, sg, colourOrder, refN, out);
         return;
     }
+    if (shardActive(h) && sg.n[2] / 2 < h->shard->nranks)
+        throw rp_error(RP_ERR_UNSUPPORTED, "rp_sweep: fewer active cell layers along z than ranks; use fewer GPUs "
+                                           "or orient the longest box vector along z");
     int recBlocks = static_cast<int>((numCells * 32 + 255) / 256);
     if (I.hard == RP_HARD_SPHERE)
         k_sweep_records<RP_HARD_SPHERE><<<recBlocks, 256, 0, st>>>(g.numCells, h->cap, g.cellStart, g.itemsTmp,
@@ -278,6 +301,7 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
                                                                             sg, I.scHalfPlus, g.items, g.rec,
                                                                             &h->dFlags[2]);
     h->launches += 3;
+    if (shardActive(h)) shardQueueLayerStarts(h, sg.n[0], sg.n[1], sg.n[2]);
     RP_CUDA(cudaEventRecord(h->ev[1], st));
     int flags[4];
     RP_CUDA(cudaMemcpyAsync(flags, h->dFlags, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -311,6 +335,16 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
         if (std::getenv("RP_SWEEP_NO_CULL")) A.cullThr2 = 3.0e38f;
     }
     A.cap = h->cap;
+    A.aOff2 = 0;
+    A.slotBegin = 0;
+    A.slotEnd = n;
+    if (shardActive(h)) {
+        int aLo, aHi;
+        shardSlab(sg.n[2] / 2, h->shard->nranks, h->shard->rank, &aLo, &aHi);
+        A.aOff2 = aLo;
+        A.slotBegin = h->shard->layerStart[2 * aLo];
+        A.slotEnd = h->shard->layerStart[2 * aHi];
+    }
     A.inter.sphereThr2 = I.sphereThr2;
     A.inter.scInner2 = I.scInner2;
     A.inter.scOuter2 = I.scOuter2;

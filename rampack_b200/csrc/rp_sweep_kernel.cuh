@@ -61,6 +61,8 @@ struct SweepArgs {
     float cullHalf;             // spherocylinders: half length of the axis segment
     SweepInter inter;
     size_t cap;
+    int aOff2;                  // sharded runs: first active-cell layer (z) of this rank's slab, else 0
+    int slotBegin, slotEnd;     // sorted slots whose trials this rank generates (all of them on one GPU)
 };
 
 // device buffers of the trials of one rp_sweep call, indexed by the sorted slot
@@ -123,8 +125,8 @@ __global__ void __launch_bounds__(128) k_sweep_trials(int n, SweepArgs A, SweepG
                                                       const double *__restrict__ rec,
                                                       const double *__restrict__ orient, TrialBuffers T)
 {
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot >= n) return;
+    const int slot = A.slotBegin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= A.slotEnd || slot >= n) return;
     const int particleId = items[slot];
     const int cell = keys[particleId] & 0x0FFFFFFF;
     const int cc[3] = {cell % sg.n[0], (cell / sg.n[0]) % sg.n[1], cell / (sg.n[0] * sg.n[1])};

@@ -31,7 +31,8 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
 
     // active cell of this CTA
     const int b = blockIdx.x;
-    const int a0 = b % A.nActive[0], a1 = (b / A.nActive[0]) % A.nActive[1], a2 = b / (A.nActive[0] * A.nActive[1]);
+    const int a0 = b % A.nActive[0], a1 = (b / A.nActive[0]) % A.nActive[1],
+              a2 = b / (A.nActive[0] * A.nActive[1]) + A.aOff2;
     const int cx = 2 * a0 + A.colour[0], cy = 2 * a1 + A.colour[1], cz = 2 * a2 + A.colour[2];
     const int ownCell = (cz * sg.n[1] + cy) * sg.n[0] + cx;
 

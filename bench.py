@@ -7,7 +7,12 @@ A "step" is one NpT cycle over the whole packing: one bulk trial-move pass (N ro
 one box-move proposal (Simulation::tryScaling semantics, rp_try_scaling / rp_revert_scaling).
   value  = attempted particle moves / device time of K steps, state resident in HBM        (CUDA events, max over ranks)
   e2e    = the same through the C ABI with HOST buffers: rp_upload (pinned host -> device) + cycle + rp_download
-N > 1 ranks run independent replicas (the pressure points of a scan, north_star), one per GPU, no data-path collective.
+N > 1 ranks (--parallelism):
+  sharded  (default) ONE packing of the named workload, the sweep spatially sharded over the ranks (z-slabs of cell
+           layers, per-colour boundary-layer exchange + end-of-cycle exchange of accepted moves over NCCL, box-move
+           recount split with a device all-reduce) — bit-identical to the 1-GPU run; "scaling": "strong"
+  replicas independent packings (the pressure points of a scan, north_star), one per GPU, no data-path collective;
+           "scaling": "weak"
 --impl reference times the reference's own OpenMP CPU implementation (oracle/_ref, unmodified sources) on the host.
 """
 import argparse
@@ -202,6 +207,8 @@ def main():
     ap.add_argument("--therm", type=int, default=20, help="untimed equilibration cycles before the warm-up")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-cycles", type=int, default=1)
+    ap.add_argument("--parallelism", default="sharded", choices=["sharded", "replicas"],
+                    help="what N > 1 ranks do (ignored at N = 1)")
     args = ap.parse_args()
     if args.impl == "reference":
         return main_reference(args)
@@ -239,8 +246,16 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
+    sharded = world > 1 and args.parallelism == "sharded"
+    rseed = SEED if sharded else SEED + rank          # sharded ranks are one simulation: same Philox key everywhere
     stream = torch.cuda.Stream()
-    dev = rp.Device(device=local, seed=SEED + rank, cuda_stream=stream.cuda_stream)
+    dev = rp.Device(device=local, seed=rseed, cuda_stream=stream.cuda_stream)
+    if sharded:
+        ident = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            ident.copy_(torch.frombuffer(bytearray(rp.Device.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(ident, 0)
+        dev.comm_init(bytes(ident.cpu().numpy().tobytes()), rank, world)
     desc = rp.make_desc(hard=rp.RP_HARD_SPHEROCYLINDER, radius=W.SC_RADIUS, length=W.SC_LENGTH)
     box, shapes = W.sc_config(args.workload)
     n = shapes.shape[0]
@@ -248,7 +263,8 @@ def main():
     dev.upload(box, shapes)
     # each replica is one pressure point of a scan (north_star): rank r runs p = 1.2 + 0.1 r
     sim = Simulation(dev, box, [(rp.RP_MOVE_ROTOTRANSLATION, TRANS_STEP, ROT_STEP)], TEMPERATURE,
-                     PRESSURE + 0.1 * rank, TriclinicDeltaScaler(box_step_for(n)), seed=SEED + rank)
+                     PRESSURE if sharded else PRESSURE + 0.1 * rank, TriclinicDeltaScaler(box_step_for(n)),
+                     seed=rseed)
     for _ in range(args.therm):
         sim.perform_cycle()
     therm_box, therm_shapes = dev.download()
@@ -279,7 +295,8 @@ def main():
     evaluated = sim.scalings_evaluated - k0[3]
     attempted = sim.moves.attempted - k0[4]
     accepted = sim.moves.accepted - k0[5]
-    total_attempted = sum_over_ranks(float(attempted))
+    # sharded: every rank reports the counters of the ONE packing; replicas: one packing per rank
+    total_attempted = float(attempted) if sharded else sum_over_ranks(float(attempted))
     value = total_attempted / (ms * 1e-3)
 
     # ---- end to end through the C ABI with host buffers (pinned): upload + cycle + download every step ----
@@ -296,7 +313,8 @@ def main():
         dev.download(out=host)
     barrier()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
-    e2e_value = sum_over_ranks(float(n * e2e_steps)) / (e2e_ms * 1e-3)
+    e2e_value = (float(n * e2e_steps) if sharded else sum_over_ranks(float(n * e2e_steps))) / (e2e_ms * 1e-3)
+    comm = dev.comm_stats() if sharded else None
 
     # ---- roofline of the dominant kernel (k_sweep, 8 launches per step) ----
     k_cand, k_full = dev.neighbour_stats()
@@ -304,7 +322,7 @@ def main():
     peak = dev.measure_fp64_peak()
     launches_sweep = 8 * args.steps
     avg_launch_ms = sweep_ms / launches_sweep
-    units_per_launch = attempted / launches_sweep
+    units_per_launch = attempted / launches_sweep / (world if sharded else 1)    # per GPU
     achieved_tflops = units_per_launch * w_move / (avg_launch_ms * 1e-3) * 1e-12
     peaks = {}
     try:
@@ -344,12 +362,17 @@ def main():
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": "strong" if sharded else "weak",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": f"{args.workload}: hard spherocylinders l=5 r=0.5, N={n} per GPU, sc lattice "
+                "config": {"workload": f"{args.workload}: hard spherocylinders l=5 r=0.5, N={n} "
+                                       f"{'in ONE packing sharded over all GPUs' if sharded else 'per GPU'}, sc lattice "
                                        f"eta=0.475 + {args.therm} equilibration cycles, NpT T=1 p=1.2, "
                                        f"rototranslation(0.05, 0.05), delta_triclinic({box_step_for(n):g})",
-                           "parallelism": "replicas (pressure-scan points), one per GPU" if world > 1 else "1 GPU",
+                           "parallelism": ("1 GPU" if world == 1 else
+                                           f"spatially sharded sweep: {world} z-slabs of cell layers, NCCL per-colour "
+                                           "boundary exchange + end-of-cycle move exchange, state replicated"
+                                           if sharded else "replicas (pressure-scan points), one per GPU"),
                            "l2_policy": f"state {n * 96 / 1e6:.0f} MB + sorted records {n * 48 / 1e6:.0f} MB per "
                                         "step; every step rebuilds the sweep grid from all particles "
                                         "(inputs not flushed: working set is re-read each step by design)"},
@@ -364,6 +387,7 @@ def main():
                                  "accepted": int(sim.scalings.accepted - k0[6]),
                                  "evaluated_per_s": (evaluated / (scaling_ms * 1e-3)) if scaling_ms > 0 else None,
                                  "ms_per_evaluated": (scaling_ms / evaluated) if evaluated else None},
+                "comm_bytes_last_sweep": comm,
                 "breakdown_ms_per_step": {"sweep_kernels": sweep_ms / args.steps, "sweep_grid": grid_ms / args.steps,
                                           "box_move": scaling_ms / args.steps}}
         print(json.dumps(line))

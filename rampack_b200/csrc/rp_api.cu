@@ -127,11 +127,21 @@ static Box makeBox(const double m[9]) {
 }
 
 // AoS (N x 12, reference Shape layout) <-> SoA with stride cap
+// Packing::areShapesWithinBox (core/Packing.cpp:1067-1073) on the staged upload: flag[0] |= 1 when a relative
+// coordinate lies outside [0, 1)
+__global__ void k_check_within_box(int n, Box box, const double *__restrict__ aos, int *__restrict__ flag) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    V3 rel = absToRel(box, v3(aos[12 * static_cast<size_t>(p)], aos[12 * static_cast<size_t>(p) + 1],
+                              aos[12 * static_cast<size_t>(p) + 2]));
+    if (rel.x < 0 || rel.x >= 1 || rel.y < 0 || rel.y >= 1 || rel.z < 0 || rel.z >= 1) atomicOr(flag, 1);
+}
+// (the unpack is skipped when the check failed: a rejected upload leaves the previous state untouched)
 __global__ void k_unpack_shapes(int n, size_t cap, const double *__restrict__ aos, double *__restrict__ pos,
-                                double *__restrict__ orient)
+                                double *__restrict__ orient, const int *__restrict__ flag)
 {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n * 12) return;
+    if (i >= n * 12 || *flag) return;
     int p = i / 12, c = i % 12;
     double v = aos[i];
     if (c < 3) pos[c * cap + p] = v;
@@ -283,12 +293,6 @@ rp_status rp_upload(rp_handle *h, const double box[9], const double *shapes, uin
     RP_EXPECT(n < (1ull << 27), "at most 2^27 particles per handle");
     Box b = makeBox(box);
     RP_EXPECT(boxVolume(b) != 0, "newBox.getVolume() != 0");
-    // Packing::areShapesWithinBox (core/Packing.cpp:1067-1073)
-    for (uint64_t i = 0; i < n; i++) {
-        V3 rel = absToRel(b, v3(shapes[12 * i], shapes[12 * i + 1], shapes[12 * i + 2]));
-        RP_EXPECT(!(rel.x < 0 || rel.x >= 1 || rel.y < 0 || rel.y >= 1 || rel.z < 0 || rel.z >= 1),
-                  "areShapesWithinBox(shapes, box)");
-    }
     if (n > h->cap || !h->pos) {
         if (h->pos) cudaFree(h->pos);
         if (h->orient) cudaFree(h->orient);
@@ -297,18 +301,25 @@ rp_status rp_upload(rp_handle *h, const double box[9], const double *shapes, uin
         RP_CUDA(cudaMalloc(&h->pos, 3 * cap * sizeof(double)));
         RP_CUDA(cudaMalloc(&h->orient, 9 * cap * sizeof(double)));
         h->cap = cap;
+        h->n = 0;          // the previous state went with the old buffers
     }
-    h->n = n;
-    h->box = b;
     ensureStage(h, n * 12 * sizeof(double));
     RP_CUDA(cudaMemcpyAsync(h->dStage, shapes, n * 12 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    RP_CUDA(cudaMemsetAsync(h->dFlags, 0, sizeof(int), h->stream));
+    k_check_within_box<<<static_cast<int>((n + 255) / 256), 256, 0, h->stream>>>(
+        static_cast<int>(n), b, static_cast<const double *>(h->dStage), h->dFlags);
     int total = static_cast<int>(n * 12);
     k_unpack_shapes<<<(total + 255) / 256, 256, 0, h->stream>>>(static_cast<int>(n), h->cap,
                                                                 static_cast<const double *>(h->dStage), h->pos,
-                                                                h->orient);
-    h->launches++;
+                                                                h->orient, h->dFlags);
+    h->launches += 2;
+    int outside = 0;
+    RP_CUDA(cudaMemcpyAsync(&outside, h->dFlags, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     RP_CUDA(cudaStreamSynchronize(h->stream));
     RP_CUDA(cudaGetLastError());
+    RP_EXPECT(!outside, "areShapesWithinBox(shapes, box)");
+    h->n = n;
+    h->box = b;
     h->gridDirty = true;
     h->hasTrial = false;
     h->hasLastScaling = false;

@@ -1,0 +1,116 @@
+"""Statistical-parity cases (north_star: packing fraction / density under NpT, nematic P2, smectic order and pair
+correlation must agree with the reference's CPU run within two combined standard errors).
+
+The same protocol runs on both sides: start from a lattice, `therm` NpT cycles, then `avg` cycles sampled every
+`every` cycles; the observables are computed from the sampled configurations with the numpy code below (restating
+the reference's observables, cited per function), errors by block averaging (the reference's own `+-` is the naive
+SEM without autocorrelation correction, src/utils/Quantity.cpp:55-60).
+
+  reference side: tests/golden/make_stat_golden.py (run where /root/reference is mounted) -> stat_golden.json
+  device side:    tests/test_gpu_statistics.py
+"""
+import math
+
+import numpy as np
+
+import rampack_b200 as rp
+
+
+def sphere_lattice(n_side, spacing):
+    g = (np.arange(n_side) + 0.5) * spacing
+    x, y, z = np.meshgrid(g, g, g, indexing="ij")
+    pos = np.stack([x.ravel(), y.ravel(), z.ravel()], axis=1)
+    shapes = np.zeros((pos.shape[0], 12))
+    shapes[:, :3] = pos
+    shapes[:, 3:] = np.eye(3).ravel()
+    return np.eye(3) * (n_side * spacing), shapes
+
+
+def sc_lattice(ncells, cell):
+    nx, ny, nz = ncells
+    ix, iy, iz = np.meshgrid(np.arange(nx), np.arange(ny), np.arange(nz), indexing="ij")
+    pos = np.stack([(ix.ravel() + 0.5) * cell[0], (iy.ravel() + 0.5) * cell[1], (iz.ravel() + 0.5) * cell[2]], axis=1)
+    shapes = np.zeros((pos.shape[0], 12))
+    shapes[:, :3] = pos
+    shapes[:, 3:] = np.eye(3).ravel()
+    return np.diag([nx * cell[0], ny * cell[1], nz * cell[2]]).astype(np.float64), shapes
+
+
+# name -> protocol.  Thermodynamic points follow test/validation_tests/SimulationTest.cpp (:77-101 degenerate hard
+# sphere gas, :103-148 hard spherocylinder gas) at a particle number the checkerboard sweep admits (box >= 2 cells of
+# totalRange per axis), plus the L/D = 5 spherocylinder fluid of BASELINE config 2 at a nematic pressure.
+CASES = {
+    "hs_degenerate": dict(
+        desc=lambda: rp.make_desc(hard=rp.RP_HARD_SPHERE, radius=0.5), state=lambda: sphere_lattice(8, 1.36),
+        temperature=1.0, pressure=1.0, trans_step=0.5, rot_step=0.1, nematic=False,
+        scaler=("delta_v", 8.0), therm=3000, avg=20000, every=20, eos_density=0.398574, gr=(1.0, 1.2)),
+    "sc_l3_gas": dict(
+        desc=lambda: rp.make_desc(hard=rp.RP_HARD_SPHEROCYLINDER, radius=0.5, length=3.0),
+        state=lambda: sc_lattice((9, 9, 5), (1.6, 1.6, 4.2)),
+        temperature=1.0, pressure=0.5, trans_step=0.5, rot_step=0.6, nematic=True,
+        scaler=("delta_v", 20.0), therm=5000, avg=20000, every=20, eos_density=0.09454087, gr=(1.0, 1.5)),
+    "sc_l5_dense": dict(
+        desc=lambda: rp.make_desc(hard=rp.RP_HARD_SPHEROCYLINDER, radius=0.5, length=5.0),
+        state=lambda: sc_lattice((12, 12, 4), (1.2, 1.2, 6.5)),
+        temperature=1.0, pressure=1.6, trans_step=0.12, rot_step=0.06, nematic=True,
+        scaler=("delta_triclinic", 0.004), therm=20000, avg=20000, every=20, eos_density=None, gr=(1.0, 1.3)),
+}
+
+
+def number_density(box, shapes):
+    """NumberDensity (src/core/observables/scalar/NumberDensity.cpp): N / V."""
+    return shapes.shape[0] / abs(np.linalg.det(box))
+
+
+def nematic_p2(shapes, axis_column=2):
+    """NematicOrder (src/core/observables/scalar/NematicOrder.cpp:9-28): Q = <3/2 a (x) a - 1/2>, P2 = the largest
+    eigenvalue; a = the shape's primary axis (orientation column 2 for spherocylinders)."""
+    rot = shapes[:, 3:].reshape(-1, 3, 3)
+    a = rot[:, :, axis_column]
+    q = 1.5 * (a[:, :, None] * a[:, None, :]).mean(axis=0) - 0.5 * np.eye(3)
+    return float(np.linalg.eigvalsh(q)[-1])
+
+
+def smectic_tau(box, shapes, max_hkl=(0, 0, 8)):
+    """SmecticOrder (src/core/observables/scalar/SmecticOrder.cpp): tau = max over integer (h, k, l) of
+    |1/N sum_j exp(2 pi i n . s_j)| with s_j the relative coordinates; only the l axis is scanned here (both sides
+    use this same function, the layers of an aligned-lattice start are normal to z)."""
+    rel = np.linalg.solve(box, shapes[:, :3].T).T
+    best = 0.0
+    for l in range(1, max_hkl[2] + 1):
+        tau = abs(np.exp(2j * math.pi * l * rel[:, 2]).mean())
+        best = max(best, tau)
+    return float(best)
+
+
+def pair_density_in_shell(box, shapes, r_lo, r_hi):
+    """PairDensityCorrelation with RadialEnumerator (src/core/observables/correlation/PairDensityCorrelation.cpp,
+    RadialEnumerator.cpp:19-30): g(r) averaged over the shell [r_lo, r_hi) = pairs in the shell / ideal-gas pairs."""
+    pos = shapes[:, :3]
+    n = pos.shape[0]
+    rel = np.linalg.solve(box, pos.T).T
+    count = 0
+    for i0 in range(0, n, 512):
+        d = rel[i0:i0 + 512, None, :] - rel[None, :, :]
+        d -= np.round(d)
+        r2 = ((d @ box.T) ** 2).sum(axis=2)
+        count += int(((r2 >= r_lo * r_lo) & (r2 < r_hi * r_hi)).sum())
+    shell = 4.0 / 3.0 * math.pi * (r_hi ** 3 - r_lo ** 3)
+    rho = n / abs(np.linalg.det(box))
+    return count / (n * rho * shell)
+
+
+def observables(case, box, shapes):
+    out = {"density": number_density(box, shapes), "g_shell": pair_density_in_shell(box, shapes, *case["gr"])}
+    if case["nematic"]:
+        out["p2"] = nematic_p2(shapes)
+        out["tau"] = smectic_tau(box, shapes)
+    return out
+
+
+def block_stats(series, blocks=10):
+    """mean and the standard error of the mean from `blocks` block averages."""
+    x = np.asarray(series, dtype=np.float64)
+    m = len(x) // blocks
+    means = x[:m * blocks].reshape(blocks, m).mean(axis=1)
+    return float(means.mean()), float(means.std(ddof=1) / math.sqrt(blocks))

@@ -9,8 +9,9 @@ one box-move proposal (Simulation::tryScaling semantics, rp_try_scaling / rp_rev
   e2e    = the same through the C ABI with HOST buffers: rp_upload (pinned host -> device) + cycle + rp_download
 N > 1 ranks (--parallelism):
   sharded  (default) ONE packing of the named workload, the sweep spatially sharded over the ranks (z-slabs of cell
-           layers, per-colour boundary-layer exchange + end-of-cycle exchange of accepted moves over NCCL, box-move
-           recount split with a device all-reduce) — bit-identical to the 1-GPU run; "scaling": "strong"
+           layers; k_sweep writes accept bytes and boundary-layer records into the peers' memory over NVLink, flag
+           kernels order the colours; box-move recount split with a device all-reduce) — bit-identical to the 1-GPU
+           run; "scaling": "strong"
   replicas independent packings (the pressure points of a scan, north_star), one per GPU, no data-path collective;
            "scaling": "weak"
 --impl reference times the reference's own OpenMP CPU implementation (oracle/_ref, unmodified sources) on the host.
@@ -370,8 +371,10 @@ def main():
                                        f"eta=0.475 + {args.therm} equilibration cycles, NpT T=1 p=1.2, "
                                        f"rototranslation(0.05, 0.05), delta_triclinic({box_step_for(n):g})",
                            "parallelism": ("1 GPU" if world == 1 else
-                                           f"spatially sharded sweep: {world} z-slabs of cell layers, NCCL per-colour "
-                                           "boundary exchange + end-of-cycle move exchange, state replicated"
+                                           f"spatially sharded sweep: {world} z-slabs of cell layers; accepted moves "
+                                           "travel as accept bytes + boundary-layer records written by k_sweep into "
+                                           "the peers' memory over NVLink, flag kernels order the colours; box-move "
+                                           "recount split + NCCL all-reduce; state replicated"
                                            if sharded else "replicas (pressure-scan points), one per GPU"),
                            "l2_policy": f"state {n * 96 / 1e6:.0f} MB + sorted records {n * 48 / 1e6:.0f} MB per "
                                         "step; every step rebuilds the sweep grid from all particles "

@@ -4,6 +4,9 @@
 #include "rp_shard.cuh"
 #include "rp_sweep_kernel.cuh"
 #include <dlfcn.h>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
 #include <nccl.h>
 
 namespace rp {
@@ -87,6 +90,13 @@ void shardInit(Handle *h, const unsigned char id[128], int rank, int nranks) {
 void shardDestroy(Handle *h) {
     if (!h->shard) return;
     Shard *s = h->shard;
+    for (int q = 0; q < 64; q++) {
+        for (int b = 0; b < 2; b++) if (s->peerBase[q][b]) cudaIpcCloseMemHandle(s->peerBase[q][b]);
+        if (s->peerFlags[q]) cudaIpcCloseMemHandle(s->peerFlags[q]);
+    }
+    if (s->flags) cudaFree(s->flags);
+    if (s->acc) cudaFree(s->acc);
+    if (s->dHandles) cudaFree(s->dHandles);
     if (s->comm) nccl.CommDestroy(static_cast<ncclComm_t>(s->comm));
     for (void *p : {(void *) s->sendBuf, (void *) s->recvBuf, (void *) s->gatherBuf, (void *) s->dLayerStart,
                     (void *) s->dCounts})
@@ -249,6 +259,184 @@ void shardGatherCycle(Handle *h, int nz, bool translated, bool rotated) {
     RP_NCCL(nccl.GroupEnd());
     for (int q = 0; q < P; q++)
         if (q != r) apply(h, s->gatherBuf + offset[q], counts[q], translated, rotated);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// peer-memory path
+// ---------------------------------------------------------------------------------------------------------------
+// Flag block of a rank (one IPC-mapped allocation): [3][64] uint32 epochs (grid-ready / colour / sweep-done, indexed
+// by SENDER rank), then [64][4] uint64 sweep counters of every rank.
+constexpr size_t FLAG_WORDS = 3 * 64, FLAG_BLOCK_BYTES = FLAG_WORDS * sizeof(unsigned int) + 64 * 4 * sizeof(unsigned long long);
+__host__ __device__ inline unsigned long long *counterBlock(unsigned int *flags) {
+    return reinterpret_cast<unsigned long long *>(flags + FLAG_WORDS);
+}
+
+struct IpcBundle { cudaIpcMemHandle_t mem[2]; cudaIpcMemHandle_t flags; };
+
+bool shardEnsurePeerMapping(Handle *h) {
+    Shard *s = h->shard;
+    const int P = s->nranks, r = s->rank;
+    if (P > SHARD_MAX_PEERS + 1 || std::getenv("RP_SHARD_NCCL")) return false;
+    if (s->p2pTried && !s->p2p) return false;
+    if (s->accCap < h->sgrid.itemCap || !s->acc) {
+        if (s->acc) cudaFree(s->acc);       // (peers close their mapping below, in this same collective call)
+        s->acc = nullptr;
+        RP_CUDA(cudaMalloc(&s->acc, h->sgrid.itemCap));
+        s->accCap = h->sgrid.itemCap;
+    }
+    void *local[2] = {h->sgrid.rec, s->acc};
+    if (s->p2p && std::memcmp(local, s->mappedLocal, sizeof(local)) == 0) return true;
+    // (all ranks take this branch in the same call: the replicas make identical allocation decisions)
+    s->p2pTried = true;
+    s->p2p = false;
+    if (!s->flags) {
+        RP_CUDA(cudaMalloc(&s->flags, FLAG_BLOCK_BYTES));
+        RP_CUDA(cudaMemset(s->flags, 0, FLAG_BLOCK_BYTES));
+        RP_CUDA(cudaMalloc(&s->dHandles, 64 * sizeof(IpcBundle)));
+    }
+    for (int q = 0; q < P; q++)
+        for (int b = 0; b < 2; b++)
+            if (s->peerBase[q][b]) { cudaIpcCloseMemHandle(s->peerBase[q][b]); s->peerBase[q][b] = nullptr; }
+    IpcBundle mine;
+    bool ok = true;
+    for (int b = 0; b < 2; b++) ok = ok && cudaIpcGetMemHandle(&mine.mem[b], local[b]) == cudaSuccess;
+    ok = ok && cudaIpcGetMemHandle(&mine.flags, s->flags) == cudaSuccess;
+    cudaGetLastError();
+    std::vector<IpcBundle> all(P);
+    unsigned long long okAll = ok ? 1 : 0;
+    RP_CUDA(cudaMemcpyAsync(s->dHandles + r * sizeof(IpcBundle), &mine, sizeof(mine), cudaMemcpyHostToDevice,
+                            h->stream));
+    RP_NCCL(nccl.AllGather(s->dHandles + r * sizeof(IpcBundle), s->dHandles, sizeof(IpcBundle), ncclUint8,
+                           commOf(h), h->stream));
+    RP_CUDA(cudaMemcpyAsync(all.data(), s->dHandles, P * sizeof(IpcBundle), cudaMemcpyDeviceToHost, h->stream));
+    RP_CUDA(cudaStreamSynchronize(h->stream));
+    for (int q = 0; q < P && ok; q++) {
+        if (q == r) continue;
+        for (int b = 0; b < 2 && ok; b++)
+            ok = cudaIpcOpenMemHandle(&s->peerBase[q][b], all[q].mem[b], cudaIpcMemLazyEnablePeerAccess)
+                 == cudaSuccess;
+        if (ok && !s->peerFlags[q])
+            ok = cudaIpcOpenMemHandle(reinterpret_cast<void **>(&s->peerFlags[q]), all[q].flags,
+                                      cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+    }
+    cudaGetLastError();
+    // everyone or no one: a rank that cannot map must not be written to through stale mappings
+    okAll = ok ? 1 : 0;
+    RP_CUDA(cudaMemcpyAsync(s->dCounts, &okAll, sizeof(okAll), cudaMemcpyHostToDevice, h->stream));
+    RP_NCCL(nccl.AllReduce(s->dCounts, s->dCounts, 1, ncclUint64, ncclMin, commOf(h), h->stream));
+    RP_CUDA(cudaMemcpyAsync(&okAll, s->dCounts, sizeof(okAll), cudaMemcpyDeviceToHost, h->stream));
+    RP_CUDA(cudaStreamSynchronize(h->stream));
+    s->p2p = okAll != 0;
+    std::memcpy(s->mappedLocal, local, sizeof(local));
+    return s->p2p;
+}
+
+PeerView shardPeerView(const Handle *h, int nLayersZ) {
+    PeerView v;
+    const Shard *s = h->shard;
+    const int P = s->nranks, r = s->rank;
+    for (int q = 0; q < P; q++) {
+        if (q == r) continue;
+        v.acc[v.n++] = static_cast<unsigned char *>(s->peerBase[q][1]);
+    }
+    int aLo, aHi;
+    shardSlab(nLayersZ / 2, P, r, &aLo, &aHi);
+    v.layerLo = 2 * aLo;
+    v.layerHi = 2 * aHi - 1;
+    v.recLo = static_cast<double *>(s->peerBase[(r + P - 1) % P][0]);
+    v.recHi = static_cast<double *>(s->peerBase[(r + 1) % P][0]);
+    return v;
+}
+
+// the write-back of k_sweep (rp_sweep_kernel2.cuh) for the accepted trials of the OTHER slabs, from this rank's own
+// copy of the trials
+__global__ void k_apply_accepts(int n, int slotBegin, int slotEnd, const unsigned char *__restrict__ acc,
+                                int translated, int rotated, Box box, size_t cap, const int *__restrict__ items,
+                                const double *__restrict__ trialRec, const double *__restrict__ trialOrient,
+                                double *__restrict__ rec, double *__restrict__ pos, double *__restrict__ orient,
+                                uint2 *__restrict__ meta)
+{
+    int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n || (slot >= slotBegin && slot < slotEnd) || !acc[slot]) return;
+    const int id = items[slot];
+    const double *t = trialRec + 6 * static_cast<size_t>(slot);
+    for (int q = 0; q < 6; q++) rec[6 * static_cast<size_t>(slot) + q] = t[q];
+    if (translated) {
+        V3 np = v3(t[0], t[1], t[2]);
+        V3 p = np + pbcCorrection(box, np);
+        pos[id] = p.x; pos[cap + id] = p.y; pos[2 * cap + id] = p.z;
+    }
+    if (rotated) for (int q = 0; q < 9; q++) orient[q * cap + id] = trialOrient[9 * static_cast<size_t>(slot) + q];
+    meta[slot].x = 4u;
+}
+
+void shardApplyAccepts(Handle *h, int slotBegin, int slotEnd, int n, bool translated, bool rotated) {
+    k_apply_accepts<<<(n + 255) / 256, 256, 0, h->stream>>>(n, slotBegin, slotEnd, h->shard->acc, translated ? 1 : 0,
+                                                           rotated ? 1 : 0, h->box, h->cap, h->sgrid.items,
+                                                           h->trialRec, h->trialOrient, h->sgrid.rec, h->pos,
+                                                           h->orient, static_cast<uint2 *>(h->trialMeta));
+    h->launches++;
+}
+
+struct FlagTargets {
+    int n;
+    unsigned int *to[SHARD_MAX_PEERS];     // flag word on the peer that I write
+    unsigned int *from[SHARD_MAX_PEERS];   // local flag word the peer writes
+    unsigned long long *cntTo[SHARD_MAX_PEERS];   // (sweep-done only) where my 4 counters go on the peer
+};
+
+// One launch per synchronisation point: tell the peers "everything I queued before this kernel is done" (the peer
+// writes of earlier kernels are complete at their kernel end; the system-scope fence keeps the flag behind them),
+// then poll until every peer of the set said the same.
+__global__ void k_signal_wait(FlagTargets t, unsigned int value, const unsigned long long *__restrict__ counters) {
+    if (threadIdx.x < t.n) {
+        if (counters)
+            for (int j = 0; j < 4; j++) t.cntTo[threadIdx.x][j] = counters[j];
+        __threadfence_system();
+        *reinterpret_cast<volatile unsigned int *>(t.to[threadIdx.x]) = value;
+        volatile unsigned int *f = t.from[threadIdx.x];
+        while (static_cast<int>(*f - value) < 0) __nanosleep(100);
+    }
+    __threadfence_system();
+}
+
+// dCounters[j] = sum over ranks (mine + what the peers stored with their sweep-done signal)
+__global__ void k_sum_counters(int nranks, int rank, const unsigned long long *__restrict__ block,
+                               unsigned long long *__restrict__ counters)
+{
+    int j = threadIdx.x;
+    if (j >= 4) return;
+    unsigned long long sum = counters[j];
+    for (int q = 0; q < nranks; q++) if (q != rank) sum += block[4 * q + j];
+    counters[j] = sum;
+}
+
+static int peerSet(const Shard *s, bool all, int out[SHARD_MAX_PEERS]) {
+    int n = 0;
+    const int P = s->nranks, r = s->rank;
+    if (all) { for (int q = 0; q < P; q++) if (q != r) out[n++] = q; return n; }
+    int lo = (r + P - 1) % P, hi = (r + 1) % P;
+    out[n++] = lo;
+    if (hi != lo) out[n++] = hi;
+    return n;
+}
+
+void shardSignalWait(Handle *h, ShardFlag kind, unsigned int value, bool all, bool withCounters) {
+    Shard *s = h->shard;
+    int q[SHARD_MAX_PEERS];
+    FlagTargets t;
+    t.n = peerSet(s, all, q);
+    for (int i = 0; i < t.n; i++) {
+        t.to[i] = s->peerFlags[q[i]] + kind * 64 + s->rank;
+        t.from[i] = s->flags + kind * 64 + q[i];
+        t.cntTo[i] = counterBlock(s->peerFlags[q[i]]) + 4 * s->rank;
+    }
+    k_signal_wait<<<1, 32, 0, h->stream>>>(t, value, withCounters ? h->dCounters : nullptr);
+    h->launches++;
+    if (withCounters) {
+        k_sum_counters<<<1, 32, 0, h->stream>>>(s->nranks, s->rank, counterBlock(s->flags), h->dCounters);
+        h->launches++;
+    }
 }
 
 void shardAllReduceU64(Handle *h, unsigned long long *dValues, int count) {

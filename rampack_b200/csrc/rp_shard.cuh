@@ -33,6 +33,22 @@ struct Shard {
     size_t layerCap = 0;
     std::vector<int> layerStart; // host copy
     unsigned long long *dCounts = nullptr;    // nranks message counts (all-gathered)
+    // ---- peer-memory path (default when the buffers of all ranks can be IPC-mapped; RP_SHARD_NCCL=1 disables it) ----
+    // Trials are a pure function of (Philox key, old state), and the old state is replicated: every rank generates
+    // the trials of ALL slots, so the only thing a rank has to tell the others is one ACCEPT BYTE per slot.  k_sweep
+    // stores it straight into every peer's `acc` array over NVLink; the records of accepted moves in the slab's two
+    // boundary layers also go straight into the z-neighbour's sorted records (read there in the next colour).
+    // Per-colour / per-sweep flags (k_signal / k_wait) order the kernels of different GPUs; after the last colour
+    // k_apply_accepts replays the accepted trials of the other slabs locally.
+    bool p2p = false, p2pTried = false;
+    unsigned char *acc = nullptr;    // one byte per sorted slot, written by the slot's owner rank
+    size_t accCap = 0;
+    void *mappedLocal[2] = {nullptr, nullptr};    // local rec / acc at mapping time
+    void *peerBase[64][2] = {};      // IPC-mapped rec / acc of rank q (nullptr for q == rank)
+    unsigned int *flags = nullptr;   // local flag block: [3][64] = grid-ready / colour / sweep-done epochs per sender
+    unsigned int *peerFlags[64] = {};
+    unsigned char *dHandles = nullptr;    // all-gather staging for the IPC handles
+    unsigned int sweepEpoch = 0;
     // timing of the last sharded sweep (ms, CUDA events on the handle's stream)
     double lastHaloMs = 0, lastGatherMs = 0;
     unsigned long long lastHaloBytes = 0, lastGatherBytes = 0;
@@ -52,5 +68,25 @@ void shardQueueLayerStarts(Handle *h, int nx, int ny, int nz);
 void shardHaloExchange(Handle *h, int colour, int nx, int ny, int nz, bool translated, bool rotated);
 void shardGatherCycle(Handle *h, int nz, bool translated, bool rotated);
 void shardAllReduceU64(Handle *h, unsigned long long *dValues, int count);
+
+// peer-memory path
+constexpr int SHARD_MAX_PEERS = 7;
+struct PeerView {                 // by-value kernel argument of k_sweep
+    int n = 0;                    // number of peers
+    unsigned char *acc[SHARD_MAX_PEERS];      // their accept-byte arrays
+    int layerLo = -1, layerHi = -1;           // my slab's bottom / top cell layer
+    double *recLo = nullptr, *recHi = nullptr;    // sorted records of the rank below / above (read my boundary layers)
+};
+enum ShardFlag { SHARD_FLAG_GRID = 0, SHARD_FLAG_COLOUR = 1, SHARD_FLAG_DONE = 2 };
+// (re)maps the peers' buffers when a local buffer moved since the last mapping; collective; returns whether the
+// peer-memory path is usable
+bool shardEnsurePeerMapping(Handle *h);
+PeerView shardPeerView(const Handle *h, int nLayersZ);
+// accepted trials of the slots outside [slotBegin, slotEnd) -> sorted records and canonical arrays
+void shardApplyAccepts(Handle *h, int slotBegin, int slotEnd, int n, bool translated, bool rotated);
+// One launch: flag[kind][my rank] = value on the peers (everyone, or the two z-neighbours), ordered after all prior
+// work of the stream, then poll the local flags of the same peers until they reach `value`.  withCounters (sweep
+// done): my four sweep counters travel with the signal and h->dCounters becomes the sum over ranks.
+void shardSignalWait(Handle *h, ShardFlag kind, unsigned int value, bool all, bool withCounters);
 
 }  // namespace rp

@@ -157,11 +157,24 @@ static void launchSweep(Handle *h, const SweepArgs &A0, const SweepGrid &sg, con
         activeLayers = aHi - aLo;
         h->shard->lastHaloBytes = h->shard->lastGatherBytes = 0;
     }
-    int nTrials = A0.slotEnd - A0.slotBegin;
+    // peer-memory path: accepted moves are written into all replicas by k_sweep itself, flags order the colours
+    const bool p2p = sharded && shardEnsurePeerMapping(h);
+    PeerView peers;
+    unsigned int epoch = 0;
+    if (p2p) {
+        peers = shardPeerView(h, sg.n[2]);
+        epoch = ++h->shard->sweepEpoch;
+    }
+    SweepArgs AT = A0;
+    if (p2p) { AT.slotBegin = 0; AT.slotEnd = n; }       // every rank holds the trials of all slots
+    int nTrials = AT.slotEnd - AT.slotBegin;
     if (nTrials > 0)
-        k_sweep_trials<HARD><<<(nTrials + 127) / 128, 128, 0, h->stream>>>(n, A0, sg, h->box, h->inter.scHalfPlus,
+        k_sweep_trials<HARD><<<(nTrials + 127) / 128, 128, 0, h->stream>>>(n, AT, sg, h->box, h->inter.scHalfPlus,
                                                                         g.items, g.keys, g.rec, h->orient, T);
     h->launches++;
+    if (p2p) {      // nobody writes into a replica whose grid of this sweep is not built yet
+        shardSignalWait(h, SHARD_FLAG_GRID, epoch, true, false);
+    }
     for (int c = 0; c < 8; c++) {
         SweepArgs A = A0;
         int col = colourOrder[c];
@@ -169,11 +182,18 @@ static void launchSweep(Handle *h, const SweepArgs &A0, const SweepGrid &sg, con
         int blocks = A.nActive[0] * A.nActive[1] * activeLayers;
         k_sweep<HARD, SW_THREADS><<<blocks, SW_THREADS, smem, h->stream>>>(A, sg, h->box, g.cellStart,
                                                                           g.items, g.rec, T, h->pos, h->orient,
-                                                                          h->dCounters, h->dFlags);
+                                                                          h->dCounters, h->dFlags, peers);
         h->launches++;
-        if (sharded) shardHaloExchange(h, col, sg.n[0], sg.n[1], sg.n[2], translated, rotated);
+        if (p2p) {
+            if (c < 7) {        // the z-neighbours read my boundary layers in the next colour
+                shardSignalWait(h, SHARD_FLAG_COLOUR, epoch * 8u + c + 1, false, false);
+            }
+        } else if (sharded) shardHaloExchange(h, col, sg.n[0], sg.n[1], sg.n[2], translated, rotated);
     }
-    if (sharded) {
+    if (p2p) {                  // all replicas identical again before the next grid build / box move / download
+        shardSignalWait(h, SHARD_FLAG_DONE, epoch, true, true);
+        shardApplyAccepts(h, A0.slotBegin, A0.slotEnd, n, translated, rotated);
+    } else if (sharded) {
         shardGatherCycle(h, sg.n[2], translated, rotated);
         shardAllReduceU64(h, h->dCounters, 4);
     }

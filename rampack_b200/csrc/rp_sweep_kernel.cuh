@@ -26,6 +26,7 @@
 
 #include "rp_internal.cuh"
 #include "rp_philox.cuh"
+#include "rp_shard.cuh"
 
 namespace rp {
 

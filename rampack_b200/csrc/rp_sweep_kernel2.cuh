@@ -7,7 +7,8 @@ template <int HARD, int THREADS>
 __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 3 : 4)
 k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
         const int *__restrict__ items, double *__restrict__ rec, TrialBuffers T, double *__restrict__ pos,
-        double *__restrict__ orient, unsigned long long *__restrict__ counters, int *__restrict__ flags)
+        double *__restrict__ orient, unsigned long long *__restrict__ counters, int *__restrict__ flags,
+        PeerView peers)
 {
     constexpr int WARPS = THREADS / 32;
     extern __shared__ __align__(16) unsigned char smemRaw[];
@@ -304,6 +305,24 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
                 const double *o = T.orient + 9 * static_cast<size_t>(ownStart + tid);
                 for (int q = 0; q < 9; q++) orient[q * A.cap + particleId] = o[q];
             }
+            // sharded run over peer memory: the z-neighbour reads my boundary layers in the next colour
+            if (peers.n > 0) {
+                if (cz == peers.layerLo) {
+                    double *pr_ = peers.recLo + 6 * static_cast<size_t>(ownStart + tid);
+                    for (int q = 0; q < 6; q++) pr_[q] = t[q];
+                }
+                if (cz == peers.layerHi) {
+                    double *pr_ = peers.recHi + 6 * static_cast<size_t>(ownStart + tid);
+                    for (int q = 0; q < 6; q++) pr_[q] = t[q];
+                }
+            }
+        }
+        // ... and every other rank learns the verdicts: one accept byte per slot (they hold the same trials)
+        if (tid < numOwn) {
+            const unsigned char a = static_cast<unsigned char>((sAccepted >> tid) & 1ull);
+            #pragma unroll
+            for (int pr = 0; pr < SHARD_MAX_PEERS; pr++)      // (unrolled: no dynamic indexing of the argument)
+                if (pr < peers.n) peers.acc[pr][ownStart + tid] = a;
         }
     }   // batches
 

@@ -61,7 +61,8 @@ def main():
         ok = (log == log1) and np.array_equal(b, b1) and np.array_equal(s, s1)
         moved = int(np.any(s1 != shapes, axis=1).sum())
         print(f"RESULT ok={ok} moved={moved} accepted={[l[1] for l in log if isinstance(l, tuple)]} "
-              f"halo_bytes={stats['halo_bytes']} gather_bytes={stats['gather_bytes']}", flush=True)
+              f"halo_bytes={stats['halo_bytes']} gather_bytes={stats['gather_bytes']} "
+              f"p2p={stats['halo_bytes'] == 0 and stats['gather_bytes'] == 0}", flush=True)
         if not ok:
             print("sharded log", log, "\nsingle  log", log1, flush=True)
         single.close()

@@ -217,7 +217,7 @@ def main():
     import torch
     import rampack_b200 as rp
     from rampack_b200 import workloads as W
-    from rampack_b200.simulation import Simulation, TriclinicDeltaScaler
+    from rampack_b200 import NativeSimulation
 
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if not torch.cuda.is_available():
@@ -263,39 +263,39 @@ def main():
     dev.set_interaction(desc)
     dev.upload(box, shapes)
     # each replica is one pressure point of a scan (north_star): rank r runs p = 1.2 + 0.1 r
-    sim = Simulation(dev, box, [(rp.RP_MOVE_ROTOTRANSLATION, TRANS_STEP, ROT_STEP)], TEMPERATURE,
-                     PRESSURE if sharded else PRESSURE + 0.1 * rank, TriclinicDeltaScaler(box_step_for(n)),
-                     seed=rseed)
-    for _ in range(args.therm):
-        sim.perform_cycle()
+    # the reference's Simulation cycle loop, in C++ inside the library (rp_sim, rampack_b200/csrc/rp_sim.cu); step
+    # sizes stay frozen (adjust_step_sizes = 0) so that both arms do the same work
+    sim = NativeSimulation(dev, [(rp.RP_MOVE_ROTOTRANSLATION, TRANS_STEP, ROT_STEP)], TEMPERATURE,
+                           PRESSURE if sharded else PRESSURE + 0.1 * rank,
+                           ("delta_triclinic", box_step_for(n), True), seed=rseed)
+    sim.run(args.therm)
     therm_box, therm_shapes = dev.download()
 
     # ---- device-resident timing: W warm-up + exactly K timed steps ----
-    for _ in range(args.warmup):
-        sim.perform_cycle()
+    sim.run(args.warmup)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     launches0 = dev.launch_count()
-    k0 = (sim.sweep_kernel_ms, sim.sweep_grid_ms, sim.scaling_ms, sim.scalings_evaluated, sim.moves.attempted,
-          sim.moves.accepted, sim.scalings.accepted)
+    s0 = sim.stats()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     with torch.cuda.stream(stream):
         e0.record(stream)
-        for _ in range(args.steps):
-            sim.perform_cycle()
+        sim.run(args.steps)
         e1.record(stream)
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1))
     clocks = sampler.stop() if rank == 0 else None
     launches = dev.launch_count() - launches0
-    sweep_ms = sim.sweep_kernel_ms - k0[0]
-    grid_ms = sim.sweep_grid_ms - k0[1]
-    scaling_ms = sim.scaling_ms - k0[2]
-    evaluated = sim.scalings_evaluated - k0[3]
-    attempted = sim.moves.attempted - k0[4]
-    accepted = sim.moves.accepted - k0[5]
+    s1 = sim.stats()
+    sweep_ms = s1.sweep_kernel_ms - s0.sweep_kernel_ms
+    grid_ms = s1.sweep_grid_ms - s0.sweep_grid_ms
+    scaling_ms = s1.scaling_ms - s0.scaling_ms
+    evaluated = s1.scalings_evaluated - s0.scalings_evaluated
+    attempted = s1.moves_attempted[0] - s0.moves_attempted[0]
+    accepted = s1.moves_accepted[0] - s0.moves_accepted[0]
+    scalings_accepted = s1.scalings_accepted - s0.scalings_accepted
     # sharded: every rank reports the counters of the ONE packing; replicas: one packing per rank
     total_attempted = float(attempted) if sharded else sum_over_ranks(float(attempted))
     value = total_attempted / (ms * 1e-3)
@@ -304,14 +304,14 @@ def main():
     b_now, s_now = dev.download()
     host = torch.empty((n, 12), dtype=torch.float64).pin_memory().numpy()
     host[:] = s_now
-    sim.box = b_now
+    e2e_box = b_now
     e2e_steps = max(3, min(args.steps, 10))
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        dev.upload(sim.box, host)
-        sim.perform_cycle()
-        dev.download(out=host)
+        dev.upload(e2e_box, host)
+        sim.run(1)
+        e2e_box, _ = dev.download(out=host)
     barrier()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
     e2e_value = (float(n * e2e_steps) if sharded else sum_over_ranks(float(n * e2e_steps))) / (e2e_ms * 1e-3)
@@ -387,7 +387,7 @@ def main():
                 "cpu_baseline": cpu_baseline,
                 "acceptance": accepted / max(1, attempted),
                 "volume_moves": {"attempted": args.steps, "evaluated": int(evaluated),
-                                 "accepted": int(sim.scalings.accepted - k0[6]),
+                                 "accepted": int(scalings_accepted),
                                  "evaluated_per_s": (evaluated / (scaling_ms * 1e-3)) if scaling_ms > 0 else None,
                                  "ms_per_evaluated": (scaling_ms / evaluated) if evaluated else None},
                 "comm_bytes_last_sweep": comm,

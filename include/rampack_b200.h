@@ -226,6 +226,11 @@ typedef struct rp_trial_trace {
 } rp_trial_trace;
 rp_status rp_sweep_trace(rp_handle *h, rp_trial_trace *out, uint64_t n);
 
+/* ---- Packing::renormalizeOrientations / fixRotationMatrix (Packing.cpp:1178-1219), called by
+ * Simulation::fixRotationMatrices every `rotation_matrix_fix_every` cycles.  allow_overlaps != 0 is the counting-mode
+ * variant.  rejected_out: fixes not applied because they would create an overlap (all-or-nothing on the device). ---- */
+rp_status rp_renormalize_orientations(rp_handle *h, int allow_overlaps, uint64_t *rejected_out);
+
 /* ---- counting mode + walls: Packing::toggleOverlapCounting / getCachedNumberOfOverlaps (Packing.cpp:1049-1060) ---- */
 rp_status rp_toggle_overlap_counting(rp_handle *h, int count_overlaps);
 rp_status rp_cached_overlaps(rp_handle *h, uint64_t *count_out);
@@ -250,6 +255,57 @@ rp_status rp_comm_stats(rp_handle *h, uint64_t *halo_bytes, uint64_t *gather_byt
  * [2 * out[0], 2 * out[1]) of `n_layers_z`; after a sub-sweep of `colour` (bit 2 = z parity of the active cells) it
  * sends the accepted moves of layer out[2] to rank out[4] and receives those of layer out[3] from rank out[5] */
 rp_status rp_shard_plan(int32_t n_layers_z, int32_t n_ranks, int32_t rank, int32_t colour, int32_t out[6]);
+
+/* ---- host cycle loop in C++: Simulation::performCycle / evaluateCounters / tryScaling (src/core/Simulation.cpp:
+ * 325-363, 493-607) with the particle moves delegated to rp_sweep and the box move to rp_try_scaling.  One host thread;
+ * every particle-level operation runs on the device.  Observables stay with the caller: run a block of cycles, then
+ * rp_download (or a device-side observable) — that is Simulation::integrate's averaging loop turned inside out. ---- */
+typedef enum rp_scaler_kind {
+    RP_SCALER_NONE = 0,             /* Environment::disableBoxScaling: NVT */
+    RP_SCALER_DELTA_V = 1,          /* TriclinicAdapter(DeltaVolumeScaler)          (volume_scalers/DeltaVolumeScaler.cpp) */
+    RP_SCALER_LINEAR = 2,           /* AnisotropicVolumeScaler + LinearScalingFactorSampler (…/LinearScalingFactorSampler.cpp) */
+    RP_SCALER_LOG = 3,              /* AnisotropicVolumeScaler + LogScalingFactorSampler    (…/LogScalingFactorSampler.cpp) */
+    RP_SCALER_TRICLINIC_DELTA = 4   /* TriclinicDeltaScaler                         (volume_scalers/TriclinicDeltaScaler.cpp) */
+} rp_scaler_kind;
+
+#define RP_SIM_MAX_SAMPLERS 4
+typedef struct rp_sim_config {
+    uint64_t seed;                  /* host generator for box proposals and their Metropolis draws (mts[0] in the reference) */
+    double temperature, pressure;
+    int32_t n_samplers;             /* MoveSampler list; every sampler attempts N moves per cycle */
+    int32_t scaler_kind;            /* rp_scaler_kind */
+    struct { int32_t kind; int32_t reserved; double translation_step, rotation_step; } samplers[RP_SIM_MAX_SAMPLERS];
+    double scaler_step;
+    /* LINEAR / LOG: groups of axes scaled by ONE sampled factor (ScalingDirection: bit 0 = x, 1 = y, 2 = z per group,
+     * e.g. isotropic {7}, anisotropic xyz {1, 2, 4}, "xy|z" {3, 4}); independent != 0 samples one random group per
+     * move (AnisotropicVolumeScaler.cpp:18-33).  TRICLINIC_DELTA: independent != 0 perturbs one random box vector,
+     * 0 all nine entries. */
+    int32_t n_direction_groups;
+    int32_t direction_groups[3];
+    int32_t independent;
+    int32_t rotation_matrix_fix_every;   /* Simulation::fixRotationMatrices period in cycles (Simulation.cpp:144-145,
+                                            750-769); 0 = never */
+} rp_sim_config;
+
+typedef struct rp_sim_stats {
+    uint64_t cycles;                          /* performed by this rp_sim */
+    uint64_t moves_attempted[RP_SIM_MAX_SAMPLERS], moves_accepted[RP_SIM_MAX_SAMPLERS];
+    uint64_t scalings_attempted, scalings_evaluated /* reached rp_try_scaling */, scalings_accepted;
+    double translation_step[RP_SIM_MAX_SAMPLERS], rotation_step[RP_SIM_MAX_SAMPLERS];   /* current (adapted) values */
+    double scaler_step;
+    double box[9];
+    double sweep_kernel_ms, sweep_grid_ms, scaling_ms;   /* device time inside the kernels, accumulated */
+} rp_sim_stats;
+
+typedef struct rp_sim rp_sim;
+rp_status rp_sim_create(rp_handle *h, const rp_sim_config *config, rp_sim **out);
+void rp_sim_destroy(rp_sim *s);
+/* `cycles` x Simulation::performCycle; adjust_step_sizes != 0 runs evaluateCounters after every cycle
+ * (thermalisation phase, Simulation.cpp:128-135), 0 leaves the step sizes alone (averaging phase) */
+rp_status rp_sim_run(rp_sim *s, uint64_t cycles, int adjust_step_sizes);
+rp_status rp_sim_stats_get(const rp_sim *s, rp_sim_stats *out);
+/* box proposal of the configured scaler for a given box (host logic, no device needed; tests) */
+rp_status rp_sim_propose_box(rp_sim *s, const double old_box[9], double new_box[9]);
 
 /* ---- timing hook for bench.py: device milliseconds spent inside the kernels of the last call ---- */
 rp_status rp_last_kernel_ms(rp_handle *h, double *sweep_ms, double *sweep_grid_ms, double *rebuild_ms,

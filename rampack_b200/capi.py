@@ -73,6 +73,32 @@ class SweepCounters(C.Structure):
                 ("rejected_overlap", C.c_uint64), ("rejected_energy", C.c_uint64), ("sub_sweeps", C.c_uint64), ("kernel_launches", C.c_uint64)]
 
 
+RP_SCALER_NONE, RP_SCALER_DELTA_V, RP_SCALER_LINEAR, RP_SCALER_LOG, RP_SCALER_TRICLINIC_DELTA = range(5)
+RP_SIM_MAX_SAMPLERS = 4
+
+
+class SimSampler(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("reserved", C.c_int32), ("translation_step", C.c_double),
+                ("rotation_step", C.c_double)]
+
+
+class SimConfig(C.Structure):
+    _fields_ = [("seed", C.c_uint64), ("temperature", C.c_double), ("pressure", C.c_double),
+                ("n_samplers", C.c_int32), ("scaler_kind", C.c_int32), ("samplers", SimSampler * RP_SIM_MAX_SAMPLERS),
+                ("scaler_step", C.c_double), ("n_direction_groups", C.c_int32), ("direction_groups", C.c_int32 * 3),
+                ("independent", C.c_int32), ("rotation_matrix_fix_every", C.c_int32)]
+
+
+class SimStats(C.Structure):
+    _fields_ = [("cycles", C.c_uint64), ("moves_attempted", C.c_uint64 * RP_SIM_MAX_SAMPLERS),
+                ("moves_accepted", C.c_uint64 * RP_SIM_MAX_SAMPLERS), ("scalings_attempted", C.c_uint64),
+                ("scalings_evaluated", C.c_uint64), ("scalings_accepted", C.c_uint64),
+                ("translation_step", C.c_double * RP_SIM_MAX_SAMPLERS),
+                ("rotation_step", C.c_double * RP_SIM_MAX_SAMPLERS), ("scaler_step", C.c_double),
+                ("box", C.c_double * 9), ("sweep_kernel_ms", C.c_double), ("sweep_grid_ms", C.c_double),
+                ("scaling_ms", C.c_double)]
+
+
 # rp_pair as a numpy structured dtype (same layout as the C struct: all members are 8 bytes wide)
 PAIR_DTYPE = np.dtype([("pos1", "<f8", 3), ("orientation1", "<f8", 9), ("idx1", "<u8"),
                        ("pos2", "<f8", 3), ("orientation2", "<f8", 9), ("idx2", "<u8"),
@@ -90,7 +116,8 @@ SYMBOLS = ["rp_create", "rp_destroy", "rp_last_error", "rp_version", "rp_set_int
            "rp_count_total_overlaps", "rp_total_energy", "rp_try_move", "rp_accept_move", "rp_try_scaling",
            "rp_revert_scaling", "rp_sweep", "rp_sweep_trace", "rp_toggle_overlap_counting", "rp_cached_overlaps",
            "rp_pair_test_batch", "rp_comm_unique_id", "rp_comm_init", "rp_comm_destroy", "rp_comm_stats", "rp_shard_plan",
-           "rp_neighbour_stats", "rp_measure_fp64_peak", "rp_last_kernel_ms", "rp_launch_count", "rp_synchronize"]
+           "rp_neighbour_stats", "rp_measure_fp64_peak", "rp_last_kernel_ms", "rp_launch_count", "rp_synchronize",
+           "rp_renormalize_orientations", "rp_sim_create", "rp_sim_destroy", "rp_sim_run", "rp_sim_stats_get", "rp_sim_propose_box"]
 
 _lib = None
 
@@ -116,6 +143,13 @@ def load():
     lib.rp_last_error.argtypes = [H]
     lib.rp_last_error.restype = C.c_char_p
     lib.rp_version.restype = C.c_char_p
+    lib.rp_renormalize_orientations.argtypes = [H, C.c_int, C.POINTER(C.c_uint64)]
+    lib.rp_sim_create.argtypes = [H, C.POINTER(SimConfig), C.POINTER(H)]
+    lib.rp_sim_destroy.argtypes = [H]
+    lib.rp_sim_destroy.restype = None
+    lib.rp_sim_run.argtypes = [H, C.c_uint64, C.c_int]
+    lib.rp_sim_stats_get.argtypes = [H, C.POINTER(SimStats)]
+    lib.rp_sim_propose_box.argtypes = [H, dp, dp]
     lib.rp_set_interaction.argtypes = [H, C.POINTER(InteractionDesc)]
     lib.rp_upload.argtypes = [H, dp, dp, C.c_uint64]
     lib.rp_download.argtypes = [H, dp, dp, C.c_uint64]
@@ -323,6 +357,11 @@ class Device:
         self._check(self.lib.rp_comm_stats(self.h, C.byref(a), C.byref(b)))
         return {"halo_bytes": a.value, "gather_bytes": b.value}
 
+    def renormalize_orientations(self, allow_overlaps=False):
+        rej = C.c_uint64()
+        self._check(self.lib.rp_renormalize_orientations(self.h, int(allow_overlaps), C.byref(rej)))
+        return rej.value
+
     def toggle_overlap_counting(self, on):
         self._check(self.lib.rp_toggle_overlap_counting(self.h, int(on)))
 
@@ -363,3 +402,71 @@ class Device:
 
     def synchronize(self):
         self._check(self.lib.rp_synchronize(self.h))
+
+
+class NativeSimulation:
+    """rp_sim: the reference's Simulation cycle loop (performCycle / tryScaling / evaluateCounters,
+    src/core/Simulation.cpp:325-363, 493-607) running in C++ inside the library.
+
+    samplers: list of (rp_move_kind, translation_step, rotation_step); scaler: None, ("delta_v", step),
+    ("linear" | "log", step, groups, independent) with groups = list of axis bit masks (1 = x, 2 = y, 4 = z), or
+    ("delta_triclinic", step, independent).  `device` may be None for the host-only parts (propose_box)."""
+
+    def __init__(self, device, samplers, temperature=1.0, pressure=1.0, scaler=None, seed=1234,
+                 rotation_matrix_fix_every=0):
+        self.lib = load()
+        self.device = device
+        cfg = SimConfig()
+        cfg.rotation_matrix_fix_every = rotation_matrix_fix_every
+        cfg.seed, cfg.temperature, cfg.pressure = seed, temperature, pressure
+        cfg.n_samplers = len(samplers)
+        for i, (kind, ts, rs) in enumerate(samplers):
+            cfg.samplers[i].kind, cfg.samplers[i].translation_step, cfg.samplers[i].rotation_step = kind, ts, rs
+        if scaler is None:
+            cfg.scaler_kind = RP_SCALER_NONE
+        else:
+            name = scaler[0]
+            cfg.scaler_kind = {"delta_v": RP_SCALER_DELTA_V, "linear": RP_SCALER_LINEAR, "log": RP_SCALER_LOG,
+                               "delta_triclinic": RP_SCALER_TRICLINIC_DELTA}[name]
+            cfg.scaler_step = scaler[1]
+            if name in ("linear", "log"):
+                groups = list(scaler[2]) if len(scaler) > 2 else [7]
+                cfg.n_direction_groups = len(groups)
+                for i, g in enumerate(groups):
+                    cfg.direction_groups[i] = g
+                cfg.independent = int(scaler[3]) if len(scaler) > 3 else 0
+            elif name == "delta_triclinic":
+                cfg.independent = int(scaler[2]) if len(scaler) > 2 else 1
+        self.s = C.c_void_p()
+        st = self.lib.rp_sim_create(device.h if device is not None else None, C.byref(cfg), C.byref(self.s))
+        if st != RP_OK:
+            raise (PreconditionError if st == RP_ERR_PRECONDITION else RpError)(st, self.lib.rp_last_error(None).decode())
+
+    def close(self):
+        if self.s:
+            self.lib.rp_sim_destroy(self.s)
+            self.s = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def run(self, cycles, adjust_step_sizes=False):
+        st = self.lib.rp_sim_run(self.s, int(cycles), int(adjust_step_sizes))
+        if st != RP_OK:
+            self.device._check(st)
+
+    def stats(self):
+        out = SimStats()
+        self.lib.rp_sim_stats_get(self.s, C.byref(out))
+        return out
+
+    def propose_box(self, box):
+        box = np.ascontiguousarray(box, dtype=np.float64).reshape(9)
+        out = np.empty(9)
+        st = self.lib.rp_sim_propose_box(self.s, dptr(box), dptr(out))
+        if st != RP_OK:
+            raise RpError(st, self.lib.rp_last_error(None).decode())
+        return out.reshape(3, 3)

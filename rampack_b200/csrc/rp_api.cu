@@ -6,7 +6,7 @@
 
 namespace rp {
 
-static thread_local std::string tlsError;
+thread_local std::string tlsError;
 
 // Flatten an rp_interaction_desc into the device parameter block.  Every threshold is computed with the expression
 // the reference evaluates per call (citations in rp_pair.cuh) so that the compared doubles are bit-identical.
@@ -119,7 +119,7 @@ static void fillInter(const rp_interaction_desc &d, Inter &I, const XcProgram *x
     I.totalRange = d.n_centres == 0 ? I.range : 2 * std::sqrt(maxRadius2) + I.range;
 }
 
-static Box makeBox(const double m[9]) {
+Box makeBox(const double m[9]) {
     Box b;
     for (int i = 0; i < 9; i++) b.m.a[i] = m[i];
     b.inv = inverse(b.m);
@@ -163,6 +163,30 @@ static void ensureStage(Handle *h, size_t bytes) {
         RP_CUDA(cudaMalloc(&h->dStage, bytes + 64));
         h->dStageCap = bytes + 64;
     }
+}
+
+// Packing::fixRotationMatrix (core/Packing.cpp:1214-1219): three iterations of R <- 1.5 R - 0.5 R R^T R, in the
+// reference's operator order ((0.5 R) R^T) R.  backup != nullptr keeps the old matrix (9 doubles per particle).
+__global__ void k_fix_orientations(int n, size_t cap, double *__restrict__ orient, double *__restrict__ backup) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    M33 R;
+    for (int q = 0; q < 9; q++) R.a[q] = orient[q * cap + p];
+    if (backup) for (int q = 0; q < 9; q++) backup[9 * static_cast<size_t>(p) + q] = R.a[q];
+    for (int it = 0; it < 3; it++) {
+        M33 half, Rt;
+        for (int q = 0; q < 9; q++) half.a[q] = 0.5 * R.a[q];
+        for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) Rt.a[3 * i + j] = R.a[3 * j + i];
+        M33 corr = mul(mul(half, Rt), R);
+        for (int q = 0; q < 9; q++) R.a[q] = 1.5 * R.a[q] - corr.a[q];
+    }
+    for (int q = 0; q < 9; q++) orient[q * cap + p] = R.a[q];
+}
+__global__ void k_restore_orientations(int n, size_t cap, double *__restrict__ orient,
+                                       const double *__restrict__ backup) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    for (int q = 0; q < 9; q++) orient[q * cap + p] = backup[9 * static_cast<size_t>(p) + q];
 }
 
 static void setupForInteraction(Handle *h) {
@@ -340,6 +364,40 @@ rp_status rp_download(rp_handle *h, double box_out[9], double *shapes_out, uint6
         RP_CUDA(cudaMemcpyAsync(shapes_out, h->dStage, n * 12 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
         RP_CUDA(cudaStreamSynchronize(h->stream));
         RP_CUDA(cudaGetLastError());
+    }
+    RP_API_END(h)
+}
+
+rp_status rp_renormalize_orientations(rp_handle *h, int allow_overlaps, uint64_t *rejected_out) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(h->hasInteraction && h->n > 0, "packing and interaction must be set");
+    if (rejected_out) *rejected_out = 0;
+    if (allow_overlaps) {
+        // the reference resets the packing from a copy taken BEFORE the fix (core/Packing.cpp:1179-1190): the fixed
+        // matrices are discarded, only the caches are rebuilt — parity first
+        setupForInteraction(h);
+    } else {
+        const int n = static_cast<int>(h->n);
+        ensureStage(h, h->n * 9 * sizeof(double));
+        double *backup = static_cast<double *>(h->dStage);
+        k_fix_orientations<<<(n + 255) / 256, 256, 0, h->stream>>>(n, h->cap, h->orient, backup);
+        h->launches++;
+        initCentres(h);
+        recalcAbsoluteCentres(h);
+        h->gridDirty = true;
+        h->hasTrial = false;
+        // the reference walks the particles one by one and rejects a fix that creates an overlap
+        // (core/Packing.cpp:1195-1211).  Here all fixes are applied at once and checked by one recount; if ANY overlap
+        // appears every fix is withdrawn and all N are reported rejected (the fixes are O(1e-15): never observed).
+        if (h->inter.hard != RP_HARD_NONE && countTotalOverlaps(h, true) > 0) {
+            k_restore_orientations<<<(n + 255) / 256, 256, 0, h->stream>>>(n, h->cap, h->orient, backup);
+            h->launches++;
+            initCentres(h);
+            recalcAbsoluteCentres(h);
+            h->gridDirty = true;
+            if (rejected_out) *rejected_out = h->n;
+        }
+        RP_CUDA(cudaStreamSynchronize(h->stream));
     }
     RP_API_END(h)
 }

@@ -49,11 +49,29 @@ def run_case(name, seed=4321):
     return out
 
 
+REF_SEEDS = [4321, 55, 77, 99, 1234, 31337]
+
+
+def run_case_all_seeds(name):
+    """Independent reference runs (in parallel processes) combined with stat_cases.combine_runs."""
+    from concurrent.futures import ProcessPoolExecutor
+    k = S.CASES[name].get("seeds_ref", 1)
+    with ProcessPoolExecutor(k) as ex:
+        runs = list(ex.map(run_case, [name] * k, REF_SEEDS[:k]))
+    keys = [key for key, v in runs[0].items() if isinstance(v, dict)]
+    comb = S.combine_runs([{key: (r[key]["mean"], r[key]["se"]) for key in keys} for r in runs])
+    out = {"runs": runs, "seeds": REF_SEEDS[:k], "samples": runs[0]["samples"],
+           "move_acceptance": runs[0]["move_acceptance"], "scaling_acceptance": runs[0]["scaling_acceptance"]}
+    for key, (mean, se) in comb.items():
+        out[key] = {"mean": mean, "se": se}
+    return out
+
+
 def main():
     names = sys.argv[1:] or list(S.CASES)
     golden = json.load(open(OUT)) if os.path.exists(OUT) else {}
     for name in names:
-        golden[name] = run_case(name)
+        golden[name] = run_case_all_seeds(name)
         print(name, json.dumps(golden[name]), flush=True)
         json.dump(golden, open(OUT, "w"), indent=1, sort_keys=True)
 

@@ -95,3 +95,30 @@ def test_sweep_rejects_a_box_too_small_for_the_checkerboard(device):
     device.upload(box, shapes)
     with pytest.raises(capi.RpError, match="checkerboard"):
         device.sweep(rp.RP_MOVE_TRANSLATION, 0.1, 0.1, 0)
+
+
+def test_renormalize_orientations(device):
+    """Packing::renormalizeOrientations / fixRotationMatrix (core/Packing.cpp:1178-1219): three iterations of
+    R <- 1.5 R - 0.5 R R^T R restore orthogonality; positions stay; no overlap is created."""
+    device.set_interaction(H.desc_sc())
+    box, shapes = H.sc_lattice((8, 8, 4))
+    rng = np.random.default_rng(3)
+    drift = shapes.copy()
+    drift[:, 3:] += rng.normal(scale=1e-6, size=(shapes.shape[0], 9))        # accumulated round-off, exaggerated
+    device.upload(box, drift)
+    assert device.renormalize_orientations() == 0
+    _, s = device.download()
+    want = drift[:, 3:].reshape(-1, 3, 3).copy()
+    for _ in range(3):
+        want = 1.5 * want - (0.5 * want) @ np.transpose(want, (0, 2, 1)) @ want
+    got = s[:, 3:].reshape(-1, 3, 3)
+    assert np.allclose(got, want, rtol=0, atol=4e-15)
+    assert np.abs(got @ np.transpose(got, (0, 2, 1)) - np.eye(3)).max() < 2e-15
+    assert np.array_equal(s[:, :3], drift[:, :3])
+    assert device.count_total_overlaps(False) == 0
+    # counting mode: the reference discards the fixed matrices (it resets from a copy taken before the fix)
+    device.upload(box, drift)
+    device.toggle_overlap_counting(True)
+    assert device.renormalize_orientations(allow_overlaps=True) == 0
+    _, s2 = device.download()
+    assert np.array_equal(s2, drift)

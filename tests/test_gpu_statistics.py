@@ -22,37 +22,69 @@ GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "sta
 TOLERANCE_SE = 2.0        # north_star: "within two combined standard errors"
 
 
-def run_device(case, seed=97531):
+class PythonLoop:
+    """The Python mirror of the cycle loop (rampack_b200/simulation.py) behind the interface of NativeSimulation."""
+
+    def __init__(self, dev, box, samplers, temperature, pressure, scaler, seed):
+        kind, step = scaler[0], scaler[1]
+        sc = DeltaVolumeScaler(step) if kind == "delta_v" else TriclinicDeltaScaler(step)
+        self.sim = Simulation(dev, box, samplers, temperature, pressure, sc, seed=seed)
+
+    def run(self, cycles):
+        for _ in range(cycles):
+            self.sim.perform_cycle()
+
+    def rates(self):
+        return (self.sim.moves.accepted / self.sim.moves.attempted,
+                self.sim.scalings.accepted / self.sim.scalings.attempted)
+
+
+class NativeLoop:
+    """rp_sim: the cycle loop in C++ inside the library (the product's host side)."""
+
+    def __init__(self, dev, box, samplers, temperature, pressure, scaler, seed):
+        self.sim = rp.NativeSimulation(dev, samplers, temperature, pressure, scaler, seed=seed)
+
+    def run(self, cycles):
+        self.sim.run(cycles)
+
+    def rates(self):
+        st = self.sim.stats()
+        return st.moves_accepted[0] / st.moves_attempted[0], st.scalings_accepted / st.scalings_attempted
+
+
+def run_device(case, loop=NativeLoop, seed=97531):
     dev = rp.Device(0, seed=seed)
     dev.set_interaction(case["desc"]())
     box, shapes = case["state"]()
     dev.upload(box, shapes)
-    kind, step = case["scaler"]
-    scaler = DeltaVolumeScaler(step) if kind == "delta_v" else TriclinicDeltaScaler(step)
-    sim = Simulation(dev, box, [(rp.RP_MOVE_ROTOTRANSLATION, case["trans_step"], case["rot_step"])],
-                     case["temperature"], case["pressure"], scaler, seed=seed)
-    for _ in range(case["therm"]):
-        sim.perform_cycle()
+    sim = loop(dev, box, [(rp.RP_MOVE_ROTOTRANSLATION, case["trans_step"], case["rot_step"])],
+               case["temperature"], case["pressure"], case["scaler"], seed)
+    sim.run(case["therm"])
     series = {}
     for _ in range(case["avg"] // case["every"]):
-        for _ in range(case["every"]):
-            sim.perform_cycle()
+        sim.run(case["every"])
         b, s = dev.download()
         for k, v in S.observables(case, b, s).items():
             series.setdefault(k, []).append(v)
     overlaps = dev.count_total_overlaps(False)
     launches = dev.launch_count()
+    rates = sim.rates()
     dev.close()
-    return {k: S.block_stats(v) for k, v in series.items()}, overlaps, launches, sim
+    return {k: S.block_stats(v) for k, v in series.items()}, overlaps, launches, rates
 
 
-@pytest.mark.parametrize("name", list(S.CASES))
-def test_observables_agree_with_the_reference_run(name):
+@pytest.mark.parametrize("name,loop", [(n, NativeLoop) for n in S.CASES] + [("hs_degenerate", PythonLoop)])
+def test_observables_agree_with_the_reference_run(name, loop):
     case = S.CASES[name]
     golden = json.load(open(GOLDEN))[name]
-    stats, overlaps, launches, sim = run_device(case)
-    assert overlaps == 0
-    assert launches > 10 * (case["therm"] + case["avg"])          # every cycle ran kernels of this library
+    runs = []
+    for k in range(case.get("seeds_dev", 1)):
+        stats, overlaps, launches, rates = run_device(case, loop, seed=97531 + 1000 * k)
+        assert overlaps == 0
+        assert launches > 10 * (case["therm"] + case["avg"])      # every cycle ran kernels of this library
+        runs.append(stats)
+    stats = S.combine_runs(runs)
     report = []
     worst = 0.0
     for key, (mean, se) in stats.items():
@@ -61,9 +93,32 @@ def test_observables_agree_with_the_reference_run(name):
         z = abs(mean - g["mean"]) / combined if combined > 0 else 0.0
         report.append(f"{key}: device {mean:.6g} +- {se:.2g}, reference {g['mean']:.6g} +- {g['se']:.2g}, z = {z:.2f}")
         worst = max(worst, z)
-    print(f"[{name}] move acceptance {sim.moves.accepted / sim.moves.attempted:.3f}, box-move acceptance "
-          f"{sim.scalings.accepted / sim.scalings.attempted:.3f}\n  " + "\n  ".join(report))
+    print(f"[{name}, {loop.__name__}] move acceptance {rates[0]:.3f}, box-move acceptance {rates[1]:.3f}\n  "
+          + "\n  ".join(report))
     assert worst <= TOLERANCE_SE, "\n".join(report)
     if case["eos_density"] is not None:
         mean, se = stats["density"]
         assert abs(mean - case["eos_density"]) <= 3 * max(se, 1e-4 * mean), (mean, se, case["eos_density"])
+
+
+def test_step_sizes_adapt_during_thermalisation():
+    """Simulation::evaluateCounters (src/core/Simulation.cpp:533-607): acceptance > 0.2 -> steps x 1.1, < 0.1 -> / 1.1,
+    evaluated every 100 N moves / 100 box moves.  Start from far too small steps, as the reference's own validation
+    test does (test/validation_tests/SimulationTest.cpp:49-75)."""
+    case = S.CASES["hs_degenerate"]
+    dev = rp.Device(0, seed=11)
+    dev.set_interaction(case["desc"]())
+    box, shapes = case["state"]()
+    dev.upload(box, shapes)
+    sim = rp.NativeSimulation(dev, [(rp.RP_MOVE_TRANSLATION, 0.005, 0.0)], 1.0, 1.0, ("delta_v", 0.05), seed=11)
+    sim.run(6000, adjust_step_sizes=True)
+    st0 = sim.stats()
+    assert st0.translation_step[0] > 0.05 and st0.scaler_step > 0.5          # both grew by orders of magnitude
+    sim.run(1000, adjust_step_sizes=False)
+    st1 = sim.stats()
+    assert st1.translation_step[0] == st0.translation_step[0] and st1.scaler_step == st0.scaler_step
+    rate = (st1.moves_accepted[0] - st0.moves_accepted[0]) / (st1.moves_attempted[0] - st0.moves_attempted[0])
+    srate = (st1.scalings_accepted - st0.scalings_accepted) / (st1.scalings_attempted - st0.scalings_attempted)
+    assert 0.07 < rate < 0.35 and 0.05 < srate < 0.4, (rate, srate)
+    assert dev.count_total_overlaps(False) == 0
+    dev.close()

@@ -267,7 +267,7 @@ def main():
     # sizes stay frozen (adjust_step_sizes = 0) so that both arms do the same work
     sim = NativeSimulation(dev, [(rp.RP_MOVE_ROTOTRANSLATION, TRANS_STEP, ROT_STEP)], TEMPERATURE,
                            PRESSURE if sharded else PRESSURE + 0.1 * rank,
-                           ("delta_triclinic", box_step_for(n), True), seed=rseed)
+                           ("delta_triclinic", box_step_for(n), False), seed=rseed)
     sim.run(args.therm)
     therm_box, therm_shapes = dev.download()
 

@@ -233,6 +233,11 @@ rp_status rp_renormalize_orientations(rp_handle *h, int allow_overlaps, uint64_t
 
 /* ---- counting mode + walls: Packing::toggleOverlapCounting / getCachedNumberOfOverlaps (Packing.cpp:1049-1060) ---- */
 rp_status rp_toggle_overlap_counting(rp_handle *h, int count_overlaps);
+/* Packing::toggleWalls (Packing.cpp:1081-1084): a hard wall on the two box faces normal to axis i when walls[i] != 0;
+ * wall overlaps (Interaction::overlapWithWall, Packing::countParticleWallOverlaps, Packing.cpp:1086-1142) then count
+ * like pair overlaps in rp_count_total_overlaps, rp_try_move, rp_try_scaling and rp_sweep.  (The reference does not
+ * refresh a cached overlap count here either; call it before rp_toggle_overlap_counting.) */
+rp_status rp_toggle_walls(rp_handle *h, const int32_t walls[3]);
 rp_status rp_cached_overlaps(rp_handle *h, uint64_t *count_out);
 
 /* ---- parity harness: Interaction::overlapBetween / calculateEnergyBetween on explicit pairs ---- */

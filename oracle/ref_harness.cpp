@@ -360,6 +360,11 @@ void rpr_toggle_overlap_counting(void *pp, void *tp, int on) {
     static_cast<RefPacking *>(pp)->packing->toggleOverlapCounting(on != 0, inter);
 }
 
+// Packing::toggleWalls (src/core/Packing.cpp:1081-1084)
+void rpr_toggle_walls(void *pp, const int walls[3]) {
+    static_cast<RefPacking *>(pp)->packing->toggleWalls({walls[0] != 0, walls[1] != 0, walls[2] != 0});
+}
+
 std::uint64_t rpr_cached_overlaps(void *pp) { return static_cast<RefPacking *>(pp)->packing->getCachedNumberOfOverlaps(); }
 
 // NeighbourGrid::positionToCellNo (src/core/NeighbourGrid.cpp:13-34) on a grid built like Packing::rebuildNeighbourGrid

@@ -114,6 +114,8 @@ def load_ref(native=False):
     lib.rpr_revert_scaling.restype = None
     lib.rpr_toggle_overlap_counting.argtypes = [V, V, C.c_int]
     lib.rpr_toggle_overlap_counting.restype = None
+    lib.rpr_toggle_walls.argtypes = [V, C.POINTER(C.c_int)]
+    lib.rpr_toggle_walls.restype = None
     lib.rpr_cached_overlaps.argtypes = [V]
     lib.rpr_cached_overlaps.restype = C.c_uint64
     lib.rpr_cell_numbers.argtypes = [dp, C.c_double, dp, C.c_uint64, u64p, u64p]
@@ -235,6 +237,9 @@ class RefPacking:
 
     def toggle_overlap_counting(self, on):
         self.lib.rpr_toggle_overlap_counting(self.ptr, self.traits.ptr, int(on))
+
+    def toggle_walls(self, walls):
+        self.lib.rpr_toggle_walls(self.ptr, (C.c_int * 3)(*[int(w) for w in walls]))
 
     def cached_overlaps(self):
         return self.lib.rpr_cached_overlaps(self.ptr)

@@ -117,7 +117,7 @@ SYMBOLS = ["rp_create", "rp_destroy", "rp_last_error", "rp_version", "rp_set_int
            "rp_revert_scaling", "rp_sweep", "rp_sweep_trace", "rp_toggle_overlap_counting", "rp_cached_overlaps",
            "rp_pair_test_batch", "rp_comm_unique_id", "rp_comm_init", "rp_comm_destroy", "rp_comm_stats", "rp_shard_plan",
            "rp_neighbour_stats", "rp_measure_fp64_peak", "rp_last_kernel_ms", "rp_launch_count", "rp_synchronize",
-           "rp_renormalize_orientations", "rp_sim_create", "rp_sim_destroy", "rp_sim_run", "rp_sim_stats_get", "rp_sim_propose_box"]
+           "rp_renormalize_orientations", "rp_toggle_walls", "rp_sim_create", "rp_sim_destroy", "rp_sim_run", "rp_sim_stats_get", "rp_sim_propose_box"]
 
 _lib = None
 
@@ -143,6 +143,7 @@ def load():
     lib.rp_last_error.argtypes = [H]
     lib.rp_last_error.restype = C.c_char_p
     lib.rp_version.restype = C.c_char_p
+    lib.rp_toggle_walls.argtypes = [H, C.POINTER(C.c_int32)]
     lib.rp_renormalize_orientations.argtypes = [H, C.c_int, C.POINTER(C.c_uint64)]
     lib.rp_sim_create.argtypes = [H, C.POINTER(SimConfig), C.POINTER(H)]
     lib.rp_sim_destroy.argtypes = [H]
@@ -356,6 +357,9 @@ class Device:
         a, b = C.c_uint64(), C.c_uint64()
         self._check(self.lib.rp_comm_stats(self.h, C.byref(a), C.byref(b)))
         return {"halo_bytes": a.value, "gather_bytes": b.value}
+
+    def toggle_walls(self, walls):
+        self._check(self.lib.rp_toggle_walls(self.h, (C.c_int32 * 3)(*[int(w) for w in walls])))
 
     def renormalize_orientations(self, allow_overlaps=False):
         rej = C.c_uint64()

@@ -27,6 +27,7 @@ static void fillInter(const rp_interaction_desc &d, Inter &I, const XcProgram *x
             RP_EXPECT(d.radius > 0, "radius > 0");
             RP_EXPECT(d.n_centres == 0, "sphere has no interaction centres");
             I.sphereThr2 = (2 * d.radius) * (2 * d.radius);      // std::pow(2*r, 2)
+            I.radius = d.radius;
             hardRange = 2 * d.radius;
             hardConvex = true;
             break;
@@ -34,6 +35,7 @@ static void fillInter(const rp_interaction_desc &d, Inter &I, const XcProgram *x
             RP_EXPECT(d.radius > 0 && d.length >= 0, "radius > 0 && length >= 0");
             RP_EXPECT(d.n_centres == 0, "spherocylinder has no interaction centres");
             I.scInner2 = 4 * d.radius * d.radius;
+            I.radius = d.radius;
             I.scOuter2 = (2 * d.radius + d.length) * (2 * d.radius + d.length);
             I.scHalfMinus = 0.5 * -1 * d.length;
             I.scHalfPlus = 0.5 * 1 * d.length;
@@ -365,6 +367,13 @@ rp_status rp_download(rp_handle *h, double box_out[9], double *shapes_out, uint6
         RP_CUDA(cudaStreamSynchronize(h->stream));
         RP_CUDA(cudaGetLastError());
     }
+    RP_API_END(h)
+}
+
+rp_status rp_toggle_walls(rp_handle *h, const int32_t walls[3]) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(walls != nullptr, "walls != NULL");
+    h->wallMask = (walls[0] ? 1 : 0) | (walls[1] ? 2 : 0) | (walls[2] ? 4 : 0);
     RP_API_END(h)
 }
 

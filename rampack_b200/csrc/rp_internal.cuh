@@ -148,6 +148,7 @@ struct Handle {
     int trialKind = 0;
     long long lastMoveOverlapDelta = 0;
 
+    int wallMask = 0;             // Packing::hasWall, bit per axis (Packing.cpp:1075-1084)
     // overlap counting (Packing::overlapCounting / numOverlaps)
     bool overlapCounting = false;
     unsigned long long numOverlaps = 0;

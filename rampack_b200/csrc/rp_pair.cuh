@@ -19,6 +19,7 @@ struct Inter {
     double totalRange;  // Interaction::getTotalRangeRadius() (core/Interaction.cpp:55-70)
     // sphere (core/shapes/SphereTraits.cpp:56-65): std::pow(2*r, 2)
     double sphereThr2;
+    double radius;      // sphere / spherocylinder radius (wall tests)
     // spherocylinder (core/shapes/SpherocylinderTraits.cpp:28-46): 4*r*r, std::pow(2*r + l, 2), 0.5*(+-1)*l
     double scInner2, scOuter2, scHalfMinus, scHalfPlus;
     // central potentials (core/interactions/*.cpp)

@@ -9,6 +9,7 @@
 #include "rp_internal.cuh"
 #include "rp_recount_cull.cuh"
 #include "rp_shard.cuh"
+#include "rp_wall.cuh"
 #include <limits>
 #include <cstdlib>
 
@@ -292,6 +293,32 @@ static void ensureCellEnergy(Handle *h, size_t need) {
     }
 }
 
+// Packing::countWallOverlaps (core/Packing.cpp:561-580): one thread per particle, block sum, one atomic per block
+__global__ void k_count_wall_overlaps(int n, ParticleView P, const double *__restrict__ crelAll,
+                                      const Inter *__restrict__ interPtr, Walls W,
+                                      unsigned long long *__restrict__ counter)
+{
+    __shared__ Inter I;
+    __shared__ unsigned int blockSum;
+    for (int i = threadIdx.x; i < static_cast<int>(sizeof(Inter) / sizeof(int)); i += blockDim.x)
+        reinterpret_cast<int *>(&I)[i] = reinterpret_cast<const int *>(interPtr)[i];
+    if (threadIdx.x == 0) blockSum = 0;
+    __syncthreads();
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned int c = 0;
+    if (p < n) {
+        V3 pos = loadPos(P, p);
+        M33 o = loadOrient(P, p);
+        c = particleWallOverlaps(I, W, pos, o, [&](int centre) {
+            size_t idx = static_cast<size_t>(p) * I.k + centre;
+            return v3(crelAll[idx], crelAll[P.ccap + idx], crelAll[2 * P.ccap + idx]);
+        });
+    }
+    if (c) atomicAdd(&blockSum, c);
+    __syncthreads();
+    if (threadIdx.x == 0 && blockSum) atomicAdd(counter, static_cast<unsigned long long>(blockSum));
+}
+
 unsigned long long countTotalOverlaps(Handle *h, bool earlyExit) {
     if (!h->inter.hard) return 0;
     ensureGrid(h);
@@ -340,6 +367,13 @@ unsigned long long countTotalOverlaps(Handle *h, bool earlyExit) {
     }
     h->launches++;
     if (culled && shardActive(h)) shardAllReduceU64(h, h->dCounters, 1);
+    if (h->wallMask) {       // + Packing::countWallOverlaps (every rank of a sharded run counts all walls itself)
+        const int n = static_cast<int>(h->n);
+        k_count_wall_overlaps<<<(n + 255) / 256, 256, 0, st>>>(n, particleView(h), h->crel, h->dInter,
+                                                               makeWalls(h->box, h->wallMask, I.totalRange),
+                                                               h->dCounters);
+        h->launches++;
+    }
     unsigned long long result = 0;
     RP_CUDA(cudaMemcpyAsync(&result, h->dCounters, sizeof(result), cudaMemcpyDeviceToHost, st));
     RP_CUDA(cudaStreamSynchronize(st));
@@ -460,7 +494,8 @@ __device__ void scanParticle(const TrialState &S, int orig, const ParticleView &
 __global__ void __launch_bounds__(256) k_try_move(ParticleView P, const double *__restrict__ crelAll, GridView g,
                                                   int hasGrid, Box box, const Inter *__restrict__ interPtr,
                                                   int particle, int moveKind, V3 translation, M33 rotation,
-                                                  int counting, double *__restrict__ tmp, double *__restrict__ out)
+                                                  int counting, Walls W, double *__restrict__ tmp,
+                                                  double *__restrict__ out)
 {
     __shared__ Inter I;
     __shared__ Box sbox;
@@ -510,6 +545,17 @@ __global__ void __launch_bounds__(256) k_try_move(ParticleView P, const double *
     if (hard || soft)
         scanParticle(trial, particle, P, g, hasGrid, sbox, I, hard, soft, ovT, enT);
 
+    if (threadIdx.x == 0 && W.mask && hard) {
+        // + countParticleWallOverlaps of the scanned states (core/Packing.cpp:424-428)
+        if (counting)
+            ovO += particleWallOverlaps(I, W, orig.pos, orig.orient, [&](int c) {
+                int idx = particle * I.k + c;
+                return v3(crelAll[idx], crelAll[P.ccap + idx], crelAll[2 * P.ccap + idx]);
+            });
+        ovT += particleWallOverlaps(I, W, trial.pos, trial.orient, [&](int c) {
+            return v3(tmp[TMP_CREL + 3 * c], tmp[TMP_CREL + 3 * c + 1], tmp[TMP_CREL + 3 * c + 2]);
+        });
+    }
     double vals[4] = {static_cast<double>(ovO), static_cast<double>(ovT), enO, enT};
     for (int q = 0; q < 4; q++) {
         red[threadIdx.x] = vals[q];
@@ -554,7 +600,7 @@ double tryMove(Handle *h, const rp_move &m) {
     else std::memset(&g, 0, sizeof(g));
     k_try_move<<<1, 256, 0, st>>>(particleView(h), h->crel, g, h->hasGrid ? 1 : 0, h->box, h->dInter,
                                   static_cast<int>(m.particle), m.kind, tr, rot, h->overlapCounting ? 1 : 0,
-                                  h->tmpState, h->dMoveOut);
+                                  makeWalls(h->box, h->wallMask, h->inter.totalRange), h->tmpState, h->dMoveOut);
     h->launches++;
     double out[4];
     RP_CUDA(cudaMemcpyAsync(out, h->dMoveOut, sizeof(out), cudaMemcpyDeviceToHost, st));

@@ -169,8 +169,9 @@ static void launchSweep(Handle *h, const SweepArgs &A0, const SweepGrid &sg, con
     if (p2p) { AT.slotBegin = 0; AT.slotEnd = n; }       // every rank holds the trials of all slots
     int nTrials = AT.slotEnd - AT.slotBegin;
     if (nTrials > 0)
-        k_sweep_trials<HARD><<<(nTrials + 127) / 128, 128, 0, h->stream>>>(n, AT, sg, h->box, h->inter.scHalfPlus,
-                                                                        g.items, g.keys, g.rec, h->orient, T);
+        k_sweep_trials<HARD><<<(nTrials + 127) / 128, 128, 0, h->stream>>>(
+            n, AT, sg, h->box, h->inter.scHalfPlus, g.items, g.keys, g.rec, h->orient, T,
+            makeWalls(h->box, h->wallMask, h->inter.totalRange), h->inter.radius);
     h->launches++;
     if (p2p) {      // nobody writes into a replica whose grid of this sweep is not built yet
         shardSignalWait(h, SHARD_FLAG_GRID, epoch, true, false);
@@ -453,7 +454,7 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
     devEnsure(h->genRec, h->genRecCap, recw * h->n);
     devEnsure(h->genTrialRec, h->genTrialRecCap, recw * h->n);
     devEnsure(h->genTrialCrel, h->genTrialCrelCap, 3 * static_cast<size_t>(std::max(I.k, 1)) * h->n);
-    devEnsure(h->genTrialU, h->genTrialUCap, 2 * h->n);
+    devEnsure(h->genTrialU, h->genTrialUCap, 3 * h->n);
     ensureTrialBuffers(h);
     GenTrialBuffers T;
     T.rec = h->genTrialRec;
@@ -461,6 +462,7 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
     T.crel = h->genTrialCrel;
     T.u = h->genTrialU;
     T.dE = h->genTrialU + h->n;
+    T.wall = h->wallMask ? reinterpret_cast<int2 *>(h->genTrialU + 2 * h->n) : nullptr;
     T.meta = static_cast<uint2 *>(h->trialMeta);
 
     int recBlocks = static_cast<int>((static_cast<size_t>(g.numCells) * 32 + 255) / 256);
@@ -485,7 +487,7 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
     }
     RP_CUDA(cudaEventRecord(h->ev[2], st));
     k_gen_trials<<<(n + 127) / 128, 128, 0, st>>>(n, A, sg, h->box, h->dInter, g.items, g.keys, h->genRec, h->orient,
-                                                  h->crel, T);
+                                                  h->crel, T, makeWalls(h->box, h->wallMask, I.totalRange), h->pos);
     h->launches++;
     for (int c = 0; c < 8; c++) {
         GenArgs Ac = A;

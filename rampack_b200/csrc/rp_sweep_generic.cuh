@@ -24,6 +24,7 @@
 
 #include "rp_internal.cuh"
 #include "rp_philox.cuh"
+#include "rp_wall.cuh"
 
 namespace rp {
 
@@ -58,6 +59,7 @@ struct GenTrialBuffers {
     double *u;         // Metropolis variate
     double *dE;        // written by k_gen_sweep: the value Packing::tryMove would have returned (rp_sweep_trace)
     uint2 *meta;       // x: 0 alive / 2 left the cell, y: order key
+    int2 *wall;        // wall overlaps of the {old, new} state (Packing::countParticleWallOverlaps); nullptr: no walls
 };
 
 __device__ __forceinline__ V3 ld3(const double *p) { return v3(p[0], p[1], p[2]); }
@@ -158,7 +160,8 @@ __global__ void __launch_bounds__(128) k_gen_trials(int n, GenArgs A, SweepGrid 
                                                     const int *__restrict__ items, const int *__restrict__ keys,
                                                     const double *__restrict__ rec,
                                                     const double *__restrict__ orient,
-                                                    const double *__restrict__ crelAll, GenTrialBuffers T)
+                                                    const double *__restrict__ crelAll, GenTrialBuffers T,
+                                                    Walls W, const double *__restrict__ posAll)
 {
     __shared__ Inter I;
     for (int i = threadIdx.x; i < static_cast<int>(sizeof(Inter) / sizeof(int)); i += blockDim.x)
@@ -194,10 +197,24 @@ __global__ void __launch_bounds__(128) k_gen_trials(int n, GenArgs A, SweepGrid 
         size_t idx = static_cast<size_t>(id) * I.k + c;
         crel[c] = v3(crelAll[idx], crelAll[A.ccap + idx], crelAll[2 * A.ccap + idx]);
     }
+    int wallOld = 0;
+    if (T.wall && A.counting && I.hard != RP_HARD_NONE) {
+        // the state the particle is in now, on its stored (wrapped) position
+        V3 cp = v3(posAll[id], posAll[A.cap + id], posAll[2 * A.cap + id]);
+        wallOld = static_cast<int>(particleWallOverlaps(I, W, cp, O, [&](int c) { return crel[c]; }));
+    }
     if (rotated) {
         M33 R = drawRotation(rng, A.rotStep);
         O = mul(R, O);
         for (int c = 0; c < I.k; c++) crel[c] = mul(R, crel[c]);
+    }
+    if (T.wall) {
+        int wallNew = 0;
+        if (rej == 0 && I.hard != RP_HARD_NONE) {
+            V3 cp = p + pbcCorrection(box, p);       // the wrapped position the write-back would store
+            wallNew = static_cast<int>(particleWallOverlaps(I, W, cp, O, [&](int c) { return crel[c]; }));
+        }
+        T.wall[slot] = make_int2(wallOld, wallNew);
     }
     fillRecord(I, A, box, T.rec + static_cast<size_t>(slot) * A.L.recw, p, O, crel);
     double *o = T.orient + 9 * static_cast<size_t>(slot);
@@ -359,7 +376,14 @@ k_gen_sweep(GenArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr
             enO += __shfl_xor_sync(0xffffffffu, enO, o);
             enN += __shfl_xor_sync(0xffffffffu, enN, o);
         }
-        if (lane == 0) { ovOld[i] = oO; ovNew[i] = oN; eOld[i] = enO; eNew[i] = enN; }
+        if (lane == 0) {
+            if (T.wall && rejected[i] == 0) {       // + countParticleWallOverlaps (core/Packing.cpp:424-428)
+                const int2 w = T.wall[ownStart + i];
+                oO += w.x;
+                oN += w.y;
+            }
+            ovOld[i] = oO; ovNew[i] = oN; eOld[i] = enO; eNew[i] = enN;
+        }
     }
     // processing order: rank of the random key
     for (int i = tid; i < numOwn; i += GEN_THREADS) {

@@ -27,6 +27,7 @@
 #include "rp_internal.cuh"
 #include "rp_philox.cuh"
 #include "rp_shard.cuh"
+#include "rp_wall.cuh"
 
 namespace rp {
 
@@ -124,7 +125,8 @@ template <int HARD>
 __global__ void __launch_bounds__(128) k_sweep_trials(int n, SweepArgs A, SweepGrid sg, Box box, double halfLength,
                                                       const int *__restrict__ items, const int *__restrict__ keys,
                                                       const double *__restrict__ rec,
-                                                      const double *__restrict__ orient, TrialBuffers T)
+                                                      const double *__restrict__ orient, TrialBuffers T, Walls W,
+                                                      double radius)
 {
     const int slot = A.slotBegin + blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= A.slotEnd || slot >= n) return;
@@ -178,6 +180,25 @@ __global__ void __launch_bounds__(128) k_sweep_trials(int n, SweepArgs A, SweepG
         if (HARD == RP_HARD_SPHEROCYLINDER) h = column(newOrient, 2) * halfLength;
         double *o = T.orient + 9 * static_cast<size_t>(slot);
         for (int q = 0; q < 9; q++) o[q] = newOrient.a[q];
+    }
+    if (W.mask && rej == 0) {
+        // hard walls (Packing::countParticleWallOverlaps, core/Packing.cpp:1086-1142, with the sphere / spherocylinder
+        // overlapWithWall): a trial touching a wall is rejected like an overlap with a frozen particle.  The test
+        // runs on the wrapped position the write-back would store.
+        V3 cp = p + pbcCorrection(box, p);
+        for (int i = 0; i < 3; i++) {
+            if (!((W.mask >> i) & 1)) continue;
+            V3 wv = W.normal[i], origin;
+            if (dot(cp, wv) < W.halfTotalRange) origin = v3(0, 0, 0);
+            else if (dot(W.furtherOrigin - cp, wv) < W.halfTotalRange) {
+                origin = W.furtherOrigin;
+                wv = v3(-wv.x, -wv.y, -wv.z);
+            } else continue;
+            bool hit;
+            if (HARD == RP_HARD_SPHERE) hit = dot(wv, cp - origin) < radius;
+            else hit = dot(wv, (cp + h) - origin) < radius || dot(wv, (cp - h) - origin) < radius;
+            if (hit) rej = 1;
+        }
     }
     double *t = T.rec + 6 * static_cast<size_t>(slot);
     t[0] = p.x; t[1] = p.y; t[2] = p.z; t[3] = h.x; t[4] = h.y; t[5] = h.z;

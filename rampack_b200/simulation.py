@@ -13,7 +13,7 @@ from . import capi
 class TriclinicDeltaScaler:
     """TriclinicDeltaScaler::updateBox (src/core/volume_scalers/TriclinicDeltaScaler.cpp:7-25)."""
 
-    def __init__(self, step, independent=True):
+    def __init__(self, step, independent=False):
         self.step = step
         self.independent = independent
 

@@ -137,7 +137,10 @@ typedef struct rp_grid_info {
 } rp_grid_info;
 
 /* One explicit trial move — the arguments of Packing::tryTranslation / tryRotation / tryMove (Packing.cpp:84-164) */
-typedef enum rp_move_kind { RP_MOVE_TRANSLATION = 0, RP_MOVE_ROTATION = 1, RP_MOVE_ROTOTRANSLATION = 2 } rp_move_kind;
+typedef enum rp_move_kind {
+    RP_MOVE_TRANSLATION = 0, RP_MOVE_ROTATION = 1, RP_MOVE_ROTOTRANSLATION = 2,
+    RP_MOVE_FLIP = 3     /* rp_sweep only: FlipSampler (src/core/move_samplers/FlipSampler.cpp:18-41) */
+} rp_move_kind;
 
 typedef struct rp_move {
     uint64_t particle;       /* particleIdx */
@@ -155,6 +158,13 @@ typedef struct rp_sweep_params {
     double rotation_step;         /* already clamped to pi (RototranslationSampler.cpp:33) */
     double temperature;           /* Metropolis: u <= exp(-dE/T) (Simulation.cpp:483) */
     uint64_t cycle;               /* cycle number: part of the Philox counter, makes runs reproducible */
+    /* RP_MOVE_FLIP: half-turn about the shape's flip axis (ShapeGeometry::findFlipAxis, body frame), followed by the
+     * translation that puts the geometric origin (ShapeGeometry::getGeometricOrigin, body frame) back in place.  The
+     * reference attempts N / flip_every flips of randomly drawn particles per cycle; here every particle attempts one
+     * with probability 1 / flip_every (same expected number, no particle twice). */
+    double flip_axis[3];
+    double flip_origin[3];
+    uint64_t flip_every;
 } rp_sweep_params;
 
 typedef struct rp_sweep_counters {
@@ -208,16 +218,18 @@ rp_status rp_revert_scaling(rp_handle *h);
 rp_status rp_sweep(rp_handle *h, const rp_sweep_params *params, rp_sweep_counters *counters_out);
 
 /* Parity harness: what the last rp_sweep call did, one entry per particle.  Replaying the entries in the order
- * (colour_step, cell, order_key, slot) through Packing::tryMove / acceptMove of the reference must reproduce every
+ * (colour_step, cell, batch, order_key, slot) through Packing::tryMove / acceptMove of the reference must reproduce every
  * accept / reject decision (tests/test_gpu_sweep_replay.py). */
 typedef struct rp_trial_trace {
     uint64_t particle;
     int32_t colour_step;      /* 0..7: the sub-sweep that processed the particle */
     int32_t cell;             /* sweep-grid cell (the active domain of the trial) */
-    uint32_t order_key;       /* processing order inside the cell: ascending (order_key, slot) */
+    uint32_t order_key;       /* processing order inside the cell: ascending (batch, order_key, slot) */
     int32_t slot;
-    int32_t status;           /* 0 rejected (overlap or Metropolis), 1 accepted, 2 rejected: left the active cell */
-    int32_t reserved;
+    int32_t status;           /* 0 rejected (overlap or Metropolis), 1 accepted, 2 rejected: left the active cell,
+                                 3 not attempted (RP_MOVE_FLIP: the particle was not drawn) */
+    int32_t batch;            /* cells with more than 64 trials are resolved in batches of 64 slots (hard spheres /
+                                 spherocylinders): ascending batch first */
     double position[3];       /* trial mass centre in the image frame of the sweep grid (not wrapped) */
     double orientation[9];    /* trial orientation */
     double image_shift[3];    /* image-frame position of the particle = canonical position + image_shift */
@@ -279,7 +291,12 @@ typedef struct rp_sim_config {
     double temperature, pressure;
     int32_t n_samplers;             /* MoveSampler list; every sampler attempts N moves per cycle */
     int32_t scaler_kind;            /* rp_scaler_kind */
-    struct { int32_t kind; int32_t reserved; double translation_step, rotation_step; } samplers[RP_SIM_MAX_SAMPLERS];
+    struct {
+        int32_t kind; int32_t reserved;
+        double translation_step, rotation_step;
+        double flip_axis[3], flip_origin[3];     /* RP_MOVE_FLIP */
+        uint64_t flip_every;
+    } samplers[RP_SIM_MAX_SAMPLERS];
     double scaler_step;
     /* LINEAR / LOG: groups of axes scaled by ONE sampled factor (ScalingDirection: bit 0 = x, 1 = y, 2 = z per group,
      * e.g. isotropic {7}, anisotropic xyz {1, 2, 4}, "xy|z" {3, 4}); independent != 0 samples one random group per

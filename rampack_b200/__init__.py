@@ -7,4 +7,4 @@ from . import build  # noqa: F401
 from .capi import (Device, RpError, PreconditionError, make_desc, load, PAIR_DTYPE, TRACE_DTYPE,  # noqa: F401
                    RP_HARD_NONE, RP_HARD_SPHERE, RP_HARD_SPHEROCYLINDER, RP_HARD_POLYSPHERE,
                    RP_HARD_POLYSPHEROCYLINDER, RP_HARD_XENOCOLLIDE, XcProgram, RP_SOFT_NONE, RP_SOFT_LJ, RP_SOFT_WCA, RP_SOFT_SIC,
-                   RP_MOVE_TRANSLATION, RP_MOVE_ROTATION, RP_MOVE_ROTOTRANSLATION, NativeSimulation)
+                   RP_MOVE_TRANSLATION, RP_MOVE_ROTATION, RP_MOVE_ROTOTRANSLATION, RP_MOVE_FLIP, NativeSimulation)

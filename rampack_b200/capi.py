@@ -22,7 +22,7 @@ RP_OK, RP_ERR_PRECONDITION, RP_ERR_CUDA, RP_ERR_STATE, RP_ERR_UNSUPPORTED, RP_ER
 RP_XC_SUM, RP_XC_DIFF, RP_XC_MAX = 16, 17, 18
 RP_XC_MAX_NODES = RP_XC_MAX_ENTRIES = 32
 RP_SOFT_NONE, RP_SOFT_LJ, RP_SOFT_WCA, RP_SOFT_SIC = range(4)
-RP_MOVE_TRANSLATION, RP_MOVE_ROTATION, RP_MOVE_ROTOTRANSLATION = range(3)
+RP_MOVE_TRANSLATION, RP_MOVE_ROTATION, RP_MOVE_ROTOTRANSLATION, RP_MOVE_FLIP = range(4)
 
 
 class XcNode(C.Structure):
@@ -65,7 +65,8 @@ class Move(C.Structure):
 
 class SweepParams(C.Structure):
     _fields_ = [("kind", C.c_int32), ("pass_", C.c_int32), ("translation_step", C.c_double),
-                ("rotation_step", C.c_double), ("temperature", C.c_double), ("cycle", C.c_uint64)]
+                ("rotation_step", C.c_double), ("temperature", C.c_double), ("cycle", C.c_uint64),
+                ("flip_axis", C.c_double * 3), ("flip_origin", C.c_double * 3), ("flip_every", C.c_uint64)]
 
 
 class SweepCounters(C.Structure):
@@ -79,7 +80,8 @@ RP_SIM_MAX_SAMPLERS = 4
 
 class SimSampler(C.Structure):
     _fields_ = [("kind", C.c_int32), ("reserved", C.c_int32), ("translation_step", C.c_double),
-                ("rotation_step", C.c_double)]
+                ("rotation_step", C.c_double), ("flip_axis", C.c_double * 3), ("flip_origin", C.c_double * 3),
+                ("flip_every", C.c_uint64)]
 
 
 class SimConfig(C.Structure):
@@ -106,7 +108,7 @@ PAIR_DTYPE = np.dtype([("pos1", "<f8", 3), ("orientation1", "<f8", 9), ("idx1", 
 assert PAIR_DTYPE.itemsize == 8 * 29
 # rp_trial_trace
 TRACE_DTYPE = np.dtype([("particle", "<u8"), ("colour_step", "<i4"), ("cell", "<i4"), ("order_key", "<u4"),
-                        ("slot", "<i4"), ("status", "<i4"), ("reserved", "<i4"), ("position", "<f8", 3),
+                        ("slot", "<i4"), ("status", "<i4"), ("batch", "<i4"), ("position", "<f8", 3),
                         ("orientation", "<f8", 9), ("image_shift", "<f8", 3), ("u", "<f8"), ("dE", "<f8")])
 assert TRACE_DTYPE.itemsize == 8 + 6 * 4 + 8 * 17
 
@@ -324,8 +326,12 @@ class Device:
     def revert_scaling(self):
         self._check(self.lib.rp_revert_scaling(self.h))
 
-    def sweep(self, kind, translation_step, rotation_step, cycle, temperature=1.0, pass_=0):
+    def sweep(self, kind, translation_step, rotation_step, cycle, temperature=1.0, pass_=0, flip_axis=(0, 0, 0),
+              flip_origin=(0, 0, 0), flip_every=0):
         p = SweepParams(kind, pass_, translation_step, rotation_step, temperature, cycle)
+        p.flip_axis[:] = flip_axis
+        p.flip_origin[:] = flip_origin
+        p.flip_every = flip_every
         c = SweepCounters()
         self._check(self.lib.rp_sweep(self.h, C.byref(p), C.byref(c)))
         return c
@@ -424,8 +430,13 @@ class NativeSimulation:
         cfg.rotation_matrix_fix_every = rotation_matrix_fix_every
         cfg.seed, cfg.temperature, cfg.pressure = seed, temperature, pressure
         cfg.n_samplers = len(samplers)
-        for i, (kind, ts, rs) in enumerate(samplers):
+        for i, smp in enumerate(samplers):
+            kind, ts, rs = smp[:3]
             cfg.samplers[i].kind, cfg.samplers[i].translation_step, cfg.samplers[i].rotation_step = kind, ts, rs
+            if kind == RP_MOVE_FLIP:      # (RP_MOVE_FLIP, 0, 0, flip_every, flip_axis, flip_origin)
+                cfg.samplers[i].flip_every = smp[3]
+                cfg.samplers[i].flip_axis[:] = smp[4]
+                cfg.samplers[i].flip_origin[:] = smp[5] if len(smp) > 5 else (0, 0, 0)
         if scaler is None:
             cfg.scaler_kind = RP_SCALER_NONE
         else:

@@ -141,6 +141,7 @@ void evaluateCounters(rp_sim *s) {
     boxHeights(s->h->box, heights);
     const double maxTranslation = std::min(heights[0], std::min(heights[1], heights[2])) / 2;
     for (int i = 0; i < s->cfg.n_samplers; i++) {
+        if (s->cfg.samplers[i].kind == RP_MOVE_FLIP) continue;      // FlipSampler::increase/decreaseStepSize: no-ops
         if (s->curMoves[i] < 100 * N) continue;
         const double rate = static_cast<double>(s->curAccepted[i]) / static_cast<double>(s->curMoves[i]);
         s->curMoves[i] = s->curAccepted[i] = 0;
@@ -180,6 +181,11 @@ void performCycle(rp_sim *s, bool adjust) {
         p.rotation_step = std::min(s->st.rotation_step[i], M_PI);
         p.temperature = s->cfg.temperature;
         p.cycle = s->st.cycles;
+        for (int q = 0; q < 3; q++) {
+            p.flip_axis[q] = s->cfg.samplers[i].flip_axis[q];
+            p.flip_origin[q] = s->cfg.samplers[i].flip_origin[q];
+        }
+        p.flip_every = s->cfg.samplers[i].flip_every;
         rp_sweep_counters c;
         check(s, rp_sweep(h, &p, &c));
         s->st.moves_attempted[i] += c.attempted;
@@ -217,9 +223,10 @@ rp_status rp_sim_create(rp_handle *h, const rp_sim_config *config, rp_sim **out)
     }
     for (int i = 0; ok && i < c.n_samplers; i++) {
         int k = c.samplers[i].kind;
-        ok = k >= RP_MOVE_TRANSLATION && k <= RP_MOVE_ROTOTRANSLATION
-             && (k == RP_MOVE_ROTATION || c.samplers[i].translation_step > 0)
-             && (k == RP_MOVE_TRANSLATION || c.samplers[i].rotation_step > 0);
+        ok = k >= RP_MOVE_TRANSLATION && k <= RP_MOVE_FLIP
+             && (k == RP_MOVE_ROTATION || k == RP_MOVE_FLIP || c.samplers[i].translation_step > 0)
+             && (k == RP_MOVE_TRANSLATION || k == RP_MOVE_FLIP || c.samplers[i].rotation_step > 0)
+             && (k != RP_MOVE_FLIP || c.samplers[i].flip_every > 0);
     }
     if (!ok) { rp::tlsError = "rp_sim_create: invalid configuration (steps > 0, temperature > 0, known kinds)"; return RP_ERR_PRECONDITION; }
     rp_sim *s = new rp_sim;

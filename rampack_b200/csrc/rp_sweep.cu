@@ -224,11 +224,22 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
 
 void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
     const Inter &I = h->inter;
-    const bool fast = fastPathEligible(h);
-    RP_EXPECT(p.kind >= RP_MOVE_TRANSLATION && p.kind <= RP_MOVE_ROTOTRANSLATION, "unknown sampler kind");
+    const bool flip = p.kind == RP_MOVE_FLIP;
+    const bool fast = fastPathEligible(h) && !flip;
+    RP_EXPECT(p.kind >= RP_MOVE_TRANSLATION && p.kind <= RP_MOVE_FLIP, "unknown sampler kind");
     bool translated = p.kind != RP_MOVE_ROTATION, rotated = p.kind != RP_MOVE_TRANSLATION;
-    if (translated) RP_EXPECT(p.translation_step > 0, "translationStepSize > 0");
-    if (rotated) RP_EXPECT(p.rotation_step > 0, "rotationStepSize > 0");
+    if (flip) {
+        // FlipSampler (move_samplers/FlipSampler.cpp:10, 13-16, 45-51)
+        RP_EXPECT(p.flip_every > 0, "flipEvery > 0");
+        RP_EXPECT(h->n > p.flip_every, "numParticles > this->flipEvery");
+        RP_EXPECT(p.flip_axis[0] != 0 || p.flip_axis[1] != 0 || p.flip_axis[2] != 0, "flip axis must not be zero");
+        const double EPSILON = 1e-14;
+        translated = !(p.flip_origin[0] * p.flip_origin[0] + p.flip_origin[1] * p.flip_origin[1]
+                       + p.flip_origin[2] * p.flip_origin[2] < EPSILON * EPSILON);
+    } else {
+        if (translated) RP_EXPECT(p.translation_step > 0, "translationStepSize > 0");
+        if (rotated) RP_EXPECT(p.rotation_step > 0, "rotationStepSize > 0");
+    }
     if (I.soft != RP_SOFT_NONE) RP_EXPECT(p.temperature > 0, "temperature > 0");
 
     double heights[3];
@@ -439,6 +450,13 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
     A.transStep = p.translation_step;
     A.rotStep = p.rotation_step;
     A.temperature = I.soft != RP_SOFT_NONE ? p.temperature : 1.0;
+    if (p.kind == RP_MOVE_FLIP) {
+        for (int i = 0; i < 3; i++) { A.flipAxis[i] = p.flip_axis[i]; A.flipOrigin[i] = p.flip_origin[i]; }
+        A.flipProb = 1.0 / static_cast<double>(p.flip_every);
+        const double EPSILON = 1e-14;
+        A.flipOriginZero = (p.flip_origin[0] * p.flip_origin[0] + p.flip_origin[1] * p.flip_origin[1]
+                            + p.flip_origin[2] * p.flip_origin[2] < EPSILON * EPSILON) ? 1 : 0;
+    }
     A.seed = h->seed;
     A.cycle = static_cast<unsigned int>(p.cycle);
     A.pass = static_cast<unsigned int>(p.pass);
@@ -558,18 +576,22 @@ void sweepTrace(Handle *h, rp_trial_trace *out, unsigned long long n) {
     int stepOfColour[8];
     for (int c = 0; c < 8; c++) stepOfColour[h->lastColourOrder[c]] = c;
     const int *sn = h->lastSweepN;
+    int prevCell = -1;
+    unsigned long long cellFirst = 0;
     for (unsigned long long slot = 0; slot < n; slot++) {
         const int id = items[slot];
         rp_trial_trace &t = out[id];
         const int cell = keys[id] & 0x0FFFFFFF, f = (keys[id] >> 28) & 7;
+        if (cell != prevCell) { prevCell = cell; cellFirst = slot; }
         const int cx = cell % sn[0], cy = (cell / sn[0]) % sn[1], cz = cell / (sn[0] * sn[1]);
         t.particle = id;
         t.colour_step = stepOfColour[(cx & 1) | ((cy & 1) << 1) | ((cz & 1) << 2)];
         t.cell = cell;
         t.order_key = meta[slot].y;
         t.slot = static_cast<int>(slot);
-        t.status = meta[slot].x == 4u ? 1 : (meta[slot].x == 2u ? 2 : 0);
-        t.reserved = 0;
+        t.status = meta[slot].x == 4u ? 1 : (meta[slot].x == 2u ? 2 : (meta[slot].x == 5u ? 3 : 0));
+        // the specialised kernel resolves a cell holding more than SW_MAXOWN trials in batches of SW_MAXOWN slots
+        t.batch = h->lastSweepGeneric ? 0 : static_cast<int>((slot - cellFirst) / SW_MAXOWN);
         for (int d = 0; d < 3; d++) t.position[d] = rec[slot * recw + d];
         for (int q = 0; q < 9; q++) t.orientation[q] = haveOrient ? orient[slot * 9 + q] : canon[q * n + id];
         const V3 s = f ? h->lastImageShift[f] : v3(0, 0, 0);

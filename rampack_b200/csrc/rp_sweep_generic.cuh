@@ -45,6 +45,9 @@ struct GenArgs {
     int colour[3], nActive[3];
     int capOwn;
     int counting;            // Packing::overlapCounting
+    // RP_MOVE_FLIP (FlipSampler.cpp:18-41): body-frame flip axis, geometric origin, attempt probability 1 / flipEvery
+    double flipAxis[3], flipOrigin[3], flipProb;
+    int flipOriginZero;
     double cullRange2;       // (totalRange * (1 + 1e-9))^2: mass centres farther apart cannot interact; LJ: +inf
     int refN[3];             // LJ: real cells of the reference-geometry grid
     double refRelCell[3];
@@ -131,6 +134,18 @@ __global__ void k_gen_records(int numCells, GenArgs A, SweepGrid sg, Box box, co
     }
 }
 
+// Matrix<3, 3>::rotation(axis, angle): identity + K*sina + ((1 - cosa)*K)*K (geometry/Matrix.tpp:437-449)
+__device__ __forceinline__ M33 rodrigues(V3 axis, double angle) {
+    double sina = sin(angle), cosa = cos(angle);
+    M33 K = {{0, -axis.z, axis.y, axis.z, 0, -axis.x, -axis.y, axis.x, 0}};
+    M33 sK;
+    for (int q = 0; q < 9; q++) sK.a[q] = (1 - cosa) * K.a[q];
+    M33 KK = mul(sK, K);
+    M33 R;
+    for (int q = 0; q < 9; q++) R.a[q] = (((q % 4 == 0) ? 1.0 : 0.0) + K.a[q] * sina) + KK.a[q];
+    return R;
+}
+
 // MoveSampler rotation: axis uniform in the unit ball by rejection then normalised, angle U(-a, a)
 // (RototranslationSampler.cpp:35-43), Rodrigues matrix identity + K*sina + ((1 - cosa)*K)*K (Matrix.tpp:437-449)
 __device__ __forceinline__ M33 drawRotation(Rng &rng, double rotStep) {
@@ -143,14 +158,7 @@ __device__ __forceinline__ M33 drawRotation(Rng &rng, double rotStep) {
     double nrm = sqrt(n2);
     axis = v3(axis.x / nrm, axis.y / nrm, axis.z / nrm);
     double angle = rng.uniform(-rotStep, rotStep);
-    double sina = sin(angle), cosa = cos(angle);
-    M33 K = {{0, -axis.z, axis.y, axis.z, 0, -axis.x, -axis.y, axis.x, 0}};
-    M33 sK;
-    for (int q = 0; q < 9; q++) sK.a[q] = (1 - cosa) * K.a[q];
-    M33 KK = mul(sK, K);
-    M33 R;
-    for (int q = 0; q < 9; q++) R.a[q] = (((q % 4 == 0) ? 1.0 : 0.0) + K.a[q] * sina) + KK.a[q];
-    return R;
+    return rodrigues(axis, angle);
 }
 
 // trial moves of all particles (one thread per sorted slot): Shape::translate / rotate (Shape.cpp:9-16),
@@ -173,25 +181,47 @@ __global__ void __launch_bounds__(128) k_gen_trials(int n, GenArgs A, SweepGrid 
     const int cell = keys[id] & 0x0FFFFFFF;
     const int cc[3] = {cell % sg.n[0], (cell / sg.n[0]) % sg.n[1], cell / (sg.n[0] * sg.n[1])};
     V3 p = ld3(rec + static_cast<size_t>(slot) * A.L.recw);
-    const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION);
-    const bool translated = (A.kind == RP_MOVE_TRANSLATION || A.kind == RP_MOVE_ROTOTRANSLATION);
+    const bool flip = A.kind == RP_MOVE_FLIP;
+    const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION || flip);
+    const bool translated = (A.kind == RP_MOVE_TRANSLATION || A.kind == RP_MOVE_ROTOTRANSLATION
+                             || (flip && !A.flipOriginZero));
     Rng rng;
     rng.init(A.seed, static_cast<unsigned int>(id), A.cycle, A.pass);
     unsigned int rej = 0;
+    M33 O;
+    for (int q = 0; q < 9; q++) O.a[q] = orient[q * A.cap + id];
+    M33 R = {{1, 0, 0, 0, 1, 0, 0, 0, 1}};
+    if (flip) {
+        // the particle attempts a flip with probability 1 / flipEvery; the others sit this sampler out
+        if (!(rng.uniform() < A.flipProb)) rej = 5;
+        // shapeFlipAxis = (orientation * flipAxis).normalized(); rotation(shapeFlipAxis, M_PI) (FlipSampler.cpp:27-29)
+        V3 ax = mul(O, v3(A.flipAxis[0], A.flipAxis[1], A.flipAxis[2]));
+        double nrm = sqrt(norm2(ax));
+        ax = v3(ax.x / nrm, ax.y / nrm, ax.z / nrm);
+        R = rodrigues(ax, 3.14159265358979323846);
+    }
     if (translated) {
-        double tx = rng.uniform(-A.transStep, A.transStep);
-        double ty = rng.uniform(-A.transStep, A.transStep);
-        double tz = rng.uniform(-A.transStep, A.transStep);
-        p = p + v3(tx, ty, tz);
+        V3 shift;
+        if (flip) {
+            // translation = -rotation * shapeGeometricOrigin + shapeGeometricOrigin (FlipSampler.cpp:34-36)
+            V3 g = mul(O, v3(A.flipOrigin[0], A.flipOrigin[1], A.flipOrigin[2]));
+            V3 rg = mul(R, g);
+            shift = v3(-rg.x, -rg.y, -rg.z) + g;
+        } else {
+            double tx = rng.uniform(-A.transStep, A.transStep);
+            double ty = rng.uniform(-A.transStep, A.transStep);
+            double tz = rng.uniform(-A.transStep, A.transStep);
+            shift = v3(tx, ty, tz);
+        }
+        p = p + shift;
         V3 rel = absToRel(box, p);
         double q[3] = {rel.x - sg.shift[0], rel.y - sg.shift[1], rel.z - sg.shift[2]};
         for (int d = 0; d < 3; d++) {
+            if (rej == 5) break;
             if (q[d] < 0 || q[d] >= 1) rej = 2;
             else if (static_cast<int>(q[d] / sg.relCell[d]) != cc[d]) rej = 2;
         }
     }
-    M33 O;
-    for (int q = 0; q < 9; q++) O.a[q] = orient[q * A.cap + id];
     V3 crel[RP_MAX_CENTRES];
     for (int c = 0; c < I.k; c++) {
         size_t idx = static_cast<size_t>(id) * I.k + c;
@@ -204,7 +234,7 @@ __global__ void __launch_bounds__(128) k_gen_trials(int n, GenArgs A, SweepGrid 
         wallOld = static_cast<int>(particleWallOverlaps(I, W, cp, O, [&](int c) { return crel[c]; }));
     }
     if (rotated) {
-        M33 R = drawRotation(rng, A.rotStep);
+        if (!flip) R = drawRotation(rng, A.rotStep);
         O = mul(R, O);
         for (int c = 0; c < I.k; c++) crel[c] = mul(R, crel[c]);
     }
@@ -280,7 +310,7 @@ k_gen_sweep(GenArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr
     extern __shared__ __align__(16) unsigned char smemRaw[];
     __shared__ Inter I;
     __shared__ int cellBegin[28], cellSrc[27], cellT[27];
-    __shared__ int sStats[4];
+    __shared__ int sStats[5];
     __shared__ long long sOverlapDelta;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -299,7 +329,7 @@ k_gen_sweep(GenArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr
         cellBegin[tid] = (tid == 13) ? 0 : cellStart[c2 + 1] - cellStart[c2];   // the own cell is not frozen
         cellT[tid] = tIdx;
     }
-    if (tid == 0) { sStats[0] = sStats[1] = sStats[2] = sStats[3] = 0; sOverlapDelta = 0; }
+    if (tid == 0) { sStats[0] = sStats[1] = sStats[2] = sStats[3] = sStats[4] = 0; sOverlapDelta = 0; }
     __syncthreads();
     if (tid == 0) {
         int acc = 0;
@@ -399,12 +429,13 @@ k_gen_sweep(GenArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr
 
     // ---- phase 2: sequential pass through the cell (warp 0), other particles of the cell in their CURRENT state ----
     if (warp == 0) {
-        int nAcc = 0, nRejDomain = 0, nRejOverlap = 0, nRejEnergy = 0;
+        int nAcc = 0, nRejDomain = 0, nRejOverlap = 0, nRejEnergy = 0, nIdle = 0;
         long long overlapDelta = 0;
         const V3 zero = v3(0, 0, 0);
         for (int step = 0; step < numOwn; step++) {
             const int i = seq[step];
             if (rejected[i] == 2) { nRejDomain++; continue; }
+            if (rejected[i] == 5) { nIdle++; continue; }      // RP_MOVE_FLIP: not drawn this cycle
             const double *ta = tri + static_cast<size_t>(i) * recw, *oa = cur + static_cast<size_t>(i) * recw;
             int oO = 0, oN = 0;
             double enO = 0, enN = 0;
@@ -454,14 +485,16 @@ k_gen_sweep(GenArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr
         }
         if (lane == 0) {
             sStats[0] = nAcc; sStats[1] = nRejDomain; sStats[2] = nRejOverlap; sStats[3] = nRejEnergy;
+            sStats[4] = nIdle;
             sOverlapDelta = overlapDelta;
         }
     }
     __syncthreads();
 
     // ---- write-back of the accepted moves ----
-    const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION);
-    const bool translated = (A.kind == RP_MOVE_TRANSLATION || A.kind == RP_MOVE_ROTOTRANSLATION);
+    const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION || A.kind == RP_MOVE_FLIP);
+    const bool translated = (A.kind == RP_MOVE_TRANSLATION || A.kind == RP_MOVE_ROTOTRANSLATION
+                             || (A.kind == RP_MOVE_FLIP && !A.flipOriginZero));
     for (int i = warp; i < numOwn; i += WARPS) {
         if (!accepted[i]) continue;
         const int slot = ownStart + i;
@@ -489,7 +522,7 @@ k_gen_sweep(GenArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr
         }
     }
     if (tid == 0) {
-        atomicAdd(&counters[0], static_cast<unsigned long long>(numOwn));
+        atomicAdd(&counters[0], static_cast<unsigned long long>(numOwn - sStats[4]));
         atomicAdd(&counters[1], static_cast<unsigned long long>(sStats[0]));
         atomicAdd(&counters[2], static_cast<unsigned long long>(sStats[1]));
         atomicAdd(&counters[3], static_cast<unsigned long long>(sStats[2]));

@@ -49,7 +49,7 @@ RP_HD bool overlapWithWall(const Inter &I, V3 pos, const M33 &orientation, int i
         case RP_HARD_XENOCOLLIDE: {
             const XcProgram &P = *I.xc;
             V3 normalVector = mulT(orientation, wallVector);
-            V3 supportPoint = xcSupport<0>(P, P.root[idx], v3(-normalVector.x, -normalVector.y, -normalVector.z));
+            V3 supportPoint = xcSupport<XC_MAX_DEPTH>(P, P.root[idx], v3(-normalVector.x, -normalVector.y, -normalVector.z));
             V3 origin = mulT(orientation, wallOrigin - pos);
             double distanceSupport = -dot(supportPoint, normalVector);
             double distanceWall = -dot(origin, normalVector);

@@ -34,7 +34,7 @@ def test_struct_layouts_match_header():
     assert C.sizeof(capi.XcProgram) == 8 + 32 * 64 + 32 * 104 + 16 * 4
     assert C.sizeof(capi.Config) == 24
     assert C.sizeof(capi.Move) == 16 + 12 * 8
-    assert C.sizeof(capi.SweepParams) == 8 + 4 * 8
+    assert C.sizeof(capi.SweepParams) == 8 + 4 * 8 + 7 * 8          # + flip_axis[3], flip_origin[3], flip_every
     assert C.sizeof(capi.SweepCounters) == 7 * 8
     assert capi.PAIR_DTYPE.itemsize == 29 * 8
     assert C.sizeof(capi.GridInfo) == 4 * 4 + 8 + 8 + 8

@@ -23,7 +23,7 @@ pytestmark = pytest.mark.gpu
 
 def replay_sweep(ref, trace, before, kind, temperature, box):
     """Feeds the traced trials to the reference in processing order.  Returns (trials replayed, mismatches)."""
-    order = np.lexsort((trace["slot"], trace["order_key"], trace["cell"], trace["colour_step"]))
+    order = np.lexsort((trace["slot"], trace["order_key"], trace["batch"], trace["cell"], trace["colour_step"]))
     mismatches = []
     replayed = 0
     max_de_err = 0.0
@@ -31,6 +31,8 @@ def replay_sweep(ref, trace, before, kind, temperature, box):
         t = trace[idx]
         if t["status"] == 2:
             continue            # left its active cell: Packing.cpp:95-96 returns +inf before any pair work
+        if t["status"] == 3:
+            continue            # RP_MOVE_FLIP: the particle was not drawn this cycle
         i = int(t["particle"])
         old_pos, old_orient = before[i, :3], before[i, 3:].reshape(3, 3)
         translation = (t["position"] - t["image_shift"]) - old_pos if kind != rp.RP_MOVE_ROTATION else np.zeros(3)
@@ -190,3 +192,44 @@ def test_replay_overlap_counting_relaxation(device):
     box, shapes = kmer_lattice((8, 8, 8), 3, 2.0, rng)          # compressed: many overlaps
     desc = H.desc_kmer(3, soft=rp.RP_SOFT_SIC, epsilon=2.0, sigma=1.0)
     run_replay(device, desc, box, shapes, rp.RP_MOVE_ROTOTRANSLATION, 0.3, 0.3, 3, temperature=1.0, counting=True)
+
+
+def test_replay_flip_sampler(device):
+    """FlipSampler (src/core/move_samplers/FlipSampler.cpp:18-41): a half-turn about the flip axis of the shape plus
+    the translation that keeps the geometric origin in place; every particle attempts it with probability
+    1 / flip_every.  The traced trials are replayed through the reference like any rototranslation."""
+    desc = H.desc_kmer(3)
+    box = np.diag([15.0, 15.0, 15.0])
+    rng = np.random.default_rng(12)
+    shapes = H.random_packing(rng, 450, box)
+    device.toggle_overlap_counting(False)
+    device.set_interaction(desc)
+    device.upload(box, shapes)
+    ref = R.RefPacking(R.RefTraits(desc), box, shapes)
+    device.toggle_overlap_counting(True)        # random start: overlaps are counted, not forbidden
+    ref.toggle_overlap_counting(True)
+    axis, origin, every = np.array([1.0, 0.0, 0.0]), np.array([0.0, 0.0, 0.4]), 3
+    attempted = accepted = 0
+    for cycle in range(4):
+        _, before = device.download()
+        before = before.copy()
+        c = device.sweep(rp.RP_MOVE_FLIP, 0.0, 0.0, cycle, flip_axis=axis, flip_origin=origin, flip_every=every)
+        trace = device.sweep_trace()
+        drawn = trace[trace["status"] != 3]
+        assert c.attempted == drawn.shape[0]
+        for t in drawn[:60]:
+            i = int(t["particle"])
+            o_old, o_new = before[i, 3:].reshape(3, 3), t["orientation"].reshape(3, 3)
+            rot = o_new @ o_old.T
+            world_axis = o_old @ axis
+            assert np.allclose(rot @ world_axis, world_axis, atol=1e-12) and abs(np.trace(rot) + 1) < 1e-12
+            new_pos = t["position"] - t["image_shift"]
+            assert np.allclose(new_pos + o_new @ origin, before[i, :3] + o_old @ origin, atol=1e-12)
+        replayed, mismatches, _ = replay_sweep(ref, trace, before, rp.RP_MOVE_ROTOTRANSLATION, 1.0, box)
+        assert not mismatches, mismatches[:5]
+        attempted += int(c.attempted)
+        accepted += int(c.accepted)
+        assert device.cached_overlaps() == ref.cached_overlaps()
+    assert 0.25 * 4 * 450 < attempted < 0.42 * 4 * 450      # about a third of the particles is drawn per cycle
+    assert accepted > 0
+    device.toggle_overlap_counting(False)

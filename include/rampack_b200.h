@@ -273,6 +273,18 @@ rp_status rp_comm_stats(rp_handle *h, uint64_t *halo_bytes, uint64_t *gather_byt
  * sends the accepted moves of layer out[2] to rank out[4] and receives those of layer out[3] from rank out[5] */
 rp_status rp_shard_plan(int32_t n_layers_z, int32_t n_ranks, int32_t rank, int32_t colour, int32_t out[6]);
 
+/* ---- device-side order parameters (the callers of a host-readable Packing in the reference; here they read the
+ * resident state, so sampling them does not download 96 bytes per particle).
+ * rp_nematic_order: NematicOrder::calculate (src/core/observables/NematicOrder.cpp:9-55) — Q = (3 <a a> - 1) / 2 with
+ *   a = orientation * primary_axis (ShapeGeometry::getPrimaryAxis in the body frame), row-major Q in q_out, P2 = the
+ *   eigenvalue of the largest magnitude.
+ * rp_smectic_order: SmecticOrder::calculate (src/core/observables/SmecticOrder.cpp:14-62) with the constant shape
+ *   function — tau = max over (h, k, l) in the reference's half-space scan of |sum_j exp(i k . r_j)| / V, r_j = position
+ *   + orientation * focal_point (named point in the body frame; NULL or zeros = the position), k = 2 pi M^-T (h, k, l). */
+rp_status rp_nematic_order(rp_handle *h, const double primary_axis[3], double q_out[9], double *p2_out);
+rp_status rp_smectic_order(rp_handle *h, const int32_t hkl_range[3], const double focal_point[3], double *tau_out,
+                           int32_t hkl_out[3], double k_out[3]);
+
 /* ---- host cycle loop in C++: Simulation::performCycle / evaluateCounters / tryScaling (src/core/Simulation.cpp:
  * 325-363, 493-607) with the particle moves delegated to rp_sweep and the box move to rp_try_scaling.  One host thread;
  * every particle-level operation runs on the device.  Observables stay with the caller: run a block of cycles, then

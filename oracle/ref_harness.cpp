@@ -15,6 +15,9 @@
 #include <limits>
 
 #include "core/Packing.h"
+#include "core/observables/NematicOrder.h"
+#include "core/observables/SmecticOrder.h"
+#include <cstdio>
 #include "core/PeriodicBoundaryConditions.h"
 #include "core/NeighbourGrid.h"
 #include "core/Simulation.h"
@@ -363,6 +366,28 @@ void rpr_toggle_overlap_counting(void *pp, void *tp, int on) {
 // Packing::toggleWalls (src/core/Packing.cpp:1081-1084)
 void rpr_toggle_walls(void *pp, const int walls[3]) {
     static_cast<RefPacking *>(pp)->packing->toggleWalls({walls[0] != 0, walls[1] != 0, walls[2] != 0});
+}
+
+// NematicOrder / SmecticOrder of the reference (src/core/observables/NematicOrder.cpp, SmecticOrder.cpp) on the
+// packing: out = {P2, Q11, Q12, Q13, Q22, Q23, Q33, |tau|, kx, ky, kz}, hklOut = the (h, k, l) of the maximum
+int rpr_observables(void *pp, void *tp, const int hklRange[3], double out[11], int hklOut[3]) {
+    try {
+        const Packing &packing = *static_cast<RefPacking *>(pp)->packing;
+        const ShapeTraits &traits = *static_cast<Traits *>(tp)->traits;
+        NematicOrder nematic(true);
+        nematic.calculate(packing, 1, 1, traits);
+        auto nv = nematic.getIntervalValues();
+        for (std::size_t i = 0; i < 7; i++) out[i] = nv[i];
+        SmecticOrder smectic({std::size_t(hklRange[0]), std::size_t(hklRange[1]), std::size_t(hklRange[2])}, true);
+        smectic.calculate(packing, 1, 1, traits);
+        auto sv = smectic.getIntervalValues();
+        for (std::size_t i = 0; i < 4; i++) out[7 + i] = sv[i];
+        auto nominal = smectic.getNominalValues().front();
+        std::sscanf(nominal.c_str(), "%d.%d.%d", &hklOut[0], &hklOut[1], &hklOut[2]);
+        return 0;
+    } catch (const std::exception &) {
+        return 1;
+    }
 }
 
 std::uint64_t rpr_cached_overlaps(void *pp) { return static_cast<RefPacking *>(pp)->packing->getCachedNumberOfOverlaps(); }

@@ -114,6 +114,7 @@ def load_ref(native=False):
     lib.rpr_revert_scaling.restype = None
     lib.rpr_toggle_overlap_counting.argtypes = [V, V, C.c_int]
     lib.rpr_toggle_overlap_counting.restype = None
+    lib.rpr_observables.argtypes = [V, V, C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_int)]
     lib.rpr_toggle_walls.argtypes = [V, C.POINTER(C.c_int)]
     lib.rpr_toggle_walls.restype = None
     lib.rpr_cached_overlaps.argtypes = [V]
@@ -237,6 +238,16 @@ class RefPacking:
 
     def toggle_overlap_counting(self, on):
         self.lib.rpr_toggle_overlap_counting(self.ptr, self.traits.ptr, int(on))
+
+    def observables(self, hkl_range=(5, 5, 5)):
+        """The reference's NematicOrder / SmecticOrder: dict(p2, q (3x3), tau, k (3), hkl)."""
+        out, hkl = (C.c_double * 11)(), (C.c_int * 3)()
+        st = self.lib.rpr_observables(self.ptr, self.traits.ptr, (C.c_int * 3)(*hkl_range), out, hkl)
+        if st != 0:
+            raise RuntimeError("reference observables failed")
+        o = list(out)
+        q = np.array([[o[1], o[2], o[3]], [o[2], o[4], o[5]], [o[3], o[5], o[6]]])
+        return {"p2": o[0], "q": q, "tau": o[7], "k": np.array(o[8:11]), "hkl": tuple(hkl)}
 
     def toggle_walls(self, walls):
         self.lib.rpr_toggle_walls(self.ptr, (C.c_int * 3)(*[int(w) for w in walls]))

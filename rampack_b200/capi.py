@@ -119,7 +119,7 @@ SYMBOLS = ["rp_create", "rp_destroy", "rp_last_error", "rp_version", "rp_set_int
            "rp_revert_scaling", "rp_sweep", "rp_sweep_trace", "rp_toggle_overlap_counting", "rp_cached_overlaps",
            "rp_pair_test_batch", "rp_comm_unique_id", "rp_comm_init", "rp_comm_destroy", "rp_comm_stats", "rp_shard_plan",
            "rp_neighbour_stats", "rp_measure_fp64_peak", "rp_last_kernel_ms", "rp_launch_count", "rp_synchronize",
-           "rp_renormalize_orientations", "rp_toggle_walls", "rp_sim_create", "rp_sim_destroy", "rp_sim_run", "rp_sim_stats_get", "rp_sim_propose_box"]
+           "rp_renormalize_orientations", "rp_toggle_walls", "rp_nematic_order", "rp_smectic_order", "rp_sim_create", "rp_sim_destroy", "rp_sim_run", "rp_sim_stats_get", "rp_sim_propose_box"]
 
 _lib = None
 
@@ -146,6 +146,8 @@ def load():
     lib.rp_last_error.restype = C.c_char_p
     lib.rp_version.restype = C.c_char_p
     lib.rp_toggle_walls.argtypes = [H, C.POINTER(C.c_int32)]
+    lib.rp_nematic_order.argtypes = [H, dp, dp, dp]
+    lib.rp_smectic_order.argtypes = [H, C.POINTER(C.c_int32), dp, dp, C.POINTER(C.c_int32), dp]
     lib.rp_renormalize_orientations.argtypes = [H, C.c_int, C.POINTER(C.c_uint64)]
     lib.rp_sim_create.argtypes = [H, C.POINTER(SimConfig), C.POINTER(H)]
     lib.rp_sim_destroy.argtypes = [H]
@@ -363,6 +365,21 @@ class Device:
         a, b = C.c_uint64(), C.c_uint64()
         self._check(self.lib.rp_comm_stats(self.h, C.byref(a), C.byref(b)))
         return {"halo_bytes": a.value, "gather_bytes": b.value}
+
+    def nematic_order(self, primary_axis=(0.0, 0.0, 1.0)):
+        """(Q tensor 3x3, P2) — NematicOrder of the resident packing."""
+        axis = np.ascontiguousarray(primary_axis, dtype=np.float64)
+        q, p2 = np.empty(9), C.c_double()
+        self._check(self.lib.rp_nematic_order(self.h, dptr(axis), dptr(q), C.byref(p2)))
+        return q.reshape(3, 3), p2.value
+
+    def smectic_order(self, hkl_range=(5, 5, 5), focal_point=None):
+        """(|tau|, (h, k, l), k vector) — SmecticOrder of the resident packing."""
+        rng = (C.c_int32 * 3)(*hkl_range)
+        focal = np.ascontiguousarray(focal_point if focal_point is not None else (0, 0, 0), dtype=np.float64)
+        tau, hkl, k = C.c_double(), (C.c_int32 * 3)(), np.empty(3)
+        self._check(self.lib.rp_smectic_order(self.h, rng, dptr(focal), C.byref(tau), hkl, dptr(k)))
+        return tau.value, tuple(hkl), k
 
     def toggle_walls(self, walls):
         self._check(self.lib.rp_toggle_walls(self.h, (C.c_int32 * 3)(*[int(w) for w in walls])))

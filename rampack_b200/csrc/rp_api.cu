@@ -370,6 +370,27 @@ rp_status rp_download(rp_handle *h, double box_out[9], double *shapes_out, uint6
     RP_API_END(h)
 }
 
+rp_status rp_nematic_order(rp_handle *h, const double primary_axis[3], double q_out[9], double *p2_out) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(h->n > 0 && primary_axis != nullptr, "packing must be set, primary_axis != NULL");
+    nematicOrder(h, primary_axis, q_out, p2_out);
+    RP_API_END(h)
+}
+
+rp_status rp_smectic_order(rp_handle *h, const int32_t hkl_range[3], const double focal_point[3], double *tau_out,
+                           int32_t hkl_out[3], double k_out[3]) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(h->n > 0 && hkl_range != nullptr, "packing must be set, hkl_range != NULL");
+    // SmecticOrder::SmecticOrder (core/observables/SmecticOrder.cpp:70-71)
+    RP_EXPECT(hkl_range[0] >= 0 && hkl_range[1] >= 0 && hkl_range[2] >= 0, "hklRange[i] >= 0");
+    RP_EXPECT(hkl_range[0] != 0 || hkl_range[1] != 0 || hkl_range[2] != 0, "any hklRange[i] != 0");
+    RP_EXPECT(hkl_range[0] <= 32 && hkl_range[1] <= 32 && hkl_range[2] <= 32, "hklRange[i] <= 32");
+    int range[3] = {hkl_range[0], hkl_range[1], hkl_range[2]}, hkl[3];
+    smecticOrder(h, range, focal_point, tau_out, hkl, k_out);
+    if (hkl_out) for (int i = 0; i < 3; i++) hkl_out[i] = hkl[i];
+    RP_API_END(h)
+}
+
 rp_status rp_toggle_walls(rp_handle *h, const int32_t walls[3]) {
     RP_API_BEGIN(h)
     RP_EXPECT(walls != nullptr, "walls != NULL");

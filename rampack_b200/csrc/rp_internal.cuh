@@ -229,6 +229,9 @@ void buildXcProgram(const rp_xc_program &src, int nRoots, XcProgram &dst);
 // ---- rp_stats.cu ----
 void neighbourStats(Handle *h, double *kCand, double *kFull);
 void fp64Peak(Handle *h, double *dfmaGflops, double *dmulDaddGflops);
+// ---- rp_observe.cu ----
+void nematicOrder(Handle *h, const double axis[3], double qOut[9], double *p2Out);
+void smecticOrder(Handle *h, const int range[3], const double focal[3], double *tauAbs, int hklOut[3], double kOut[3]);
 // ---- rp_sweep.cu ----
 void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out);
 void cullThresholds(const Handle *h, const double relCell[3], float *thr2, float *half);

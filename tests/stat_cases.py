@@ -52,7 +52,10 @@ def sc_columns(ncells, cell, seed=5):
 # harness runs.
 # name -> protocol.  Thermodynamic points follow test/validation_tests/SimulationTest.cpp (:77-101 degenerate hard
 # sphere gas, :103-148 hard spherocylinder gas) at a particle number the checkerboard sweep admits (box >= 2 cells of
-# totalRange per axis), plus the L/D = 5 spherocylinder fluid of BASELINE config 2 at a nematic pressure (p D^3 / kT = 1.3).
+# totalRange per axis), plus the L/D = 5 spherocylinders of BASELINE config 2 as an isotropic fluid under triclinic box moves
+# (p D^3 / kT = 0.3, started at its equilibrium density).  Denser L/D = 5 states were tried and dropped: from any lattice
+# start the density still drifts after 1e5 cycles at p = 0.6 ... 2.5 (slow director / layer relaxation), and the two
+# samplers have different kinetics, so only EQUILIBRIUM averages are comparable.
 CASES = {
     "hs_degenerate": dict(
         desc=lambda: rp.make_desc(hard=rp.RP_HARD_SPHERE, radius=0.5), state=lambda: sphere_lattice(8, 1.36),
@@ -65,11 +68,11 @@ CASES = {
         temperature=1.0, pressure=0.5, trans_step=0.5, rot_step=0.6, nematic=True,
         scaler=("delta_v", 20.0), therm=5000, avg=20000, every=20, eos_density=0.09454087, gr=(1.0, 1.5),
         seeds_ref=4, seeds_dev=3),
-    "sc_l5_dense": dict(
+    "sc_l5_isotropic": dict(
         desc=lambda: rp.make_desc(hard=rp.RP_HARD_SPHEROCYLINDER, radius=0.5, length=5.0),
-        state=lambda: sc_columns((12, 12, 4), (1.2, 1.2, 6.5)),
-        temperature=1.0, pressure=1.3, trans_step=0.12, rot_step=0.06, nematic=True,
-        scaler=("delta_triclinic", 0.004, False), therm=10000, avg=20000, every=20, eos_density=None, gr=(1.0, 1.3),
+        state=lambda: sc_lattice((10, 10, 3), (1.64, 1.64, 7.0)),
+        temperature=1.0, pressure=0.3, trans_step=0.5, rot_step=0.4, nematic=True,
+        scaler=("delta_triclinic", 0.03, False), therm=5000, avg=20000, every=20, eos_density=None, gr=(1.0, 1.3),
         # slow fluctuations (volume with one box move per cycle, director, density waves): block averages of ONE run
         # underestimate the error (two runs of the same code differ by 3-4 block-SE), so for every case both sides
         # run several seeds and the error is taken from the seed-to-seed scatter

@@ -1,0 +1,73 @@
+"""Device-side order parameters against the reference's own observable classes (NematicOrder, SmecticOrder —
+src/core/observables/NematicOrder.cpp:9-55, SmecticOrder.cpp:14-62) evaluated on the same packing.  Bar: 1e-12
+(the reference adds particle by particle, the device in a fixed block tree: same terms, different rounding)."""
+import numpy as np
+import pytest
+
+import rampack_b200 as rp
+from oracle import refwrap as R
+import helpers as H
+from test_gpu_parity import triclinic_box
+
+pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not R.have_ref(), reason="checked against oracle/_ref")]
+
+
+def states():
+    rng = np.random.default_rng(21)
+    box, lattice = H.sc_lattice((10, 10, 4))
+    # layered and aligned, slightly perturbed: P2 close to 1, a strong (0, 0, 4) density wave
+    smectic = lattice.copy()
+    smectic[:, :3] += rng.normal(scale=0.05, size=(lattice.shape[0], 3))
+    smectic[:, :3] = np.mod(smectic[:, :3], np.diag(box))
+    tilt = H.random_rotations(rng, lattice.shape[0])
+    small = np.eye(3)[None] * 0.9 + 0.1 * tilt
+    u, _, vt = np.linalg.svd(small)
+    smectic[:, 3:] = (u @ vt).reshape(-1, 9)
+    tbox = triclinic_box(22, 25, 30)
+    return {"smectic": (box, smectic), "isotropic_triclinic": (tbox, H.random_packing(rng, 3000, tbox)),
+            "aligned_random_positions": (tbox, H.random_packing(rng, 2500, tbox, aligned=True))}
+
+
+@pytest.mark.parametrize("name", ["smectic", "isotropic_triclinic", "aligned_random_positions"])
+def test_order_parameters(device, name):
+    box, shapes = states()[name]
+    desc = H.desc_sc()
+    device.toggle_overlap_counting(False)
+    device.set_interaction(desc)
+    device.upload(box, shapes)
+    ref = R.RefPacking(R.RefTraits(desc), box, shapes)
+    hkl_range = (3, 3, 6)
+    want = ref.observables(hkl_range)
+    if name != "aligned_random_positions":          # perfectly aligned: the reference's Assert(p > 0) is at its edge
+        q, p2 = device.nematic_order((0.0, 0.0, 1.0))
+        assert np.allclose(q, want["q"], rtol=0, atol=1e-13)
+        assert p2 == pytest.approx(want["p2"], abs=1e-12)
+    tau, hkl, k = device.smectic_order(hkl_range)
+    assert tau == pytest.approx(want["tau"], rel=1e-11, abs=1e-15)
+    if name == "smectic":
+        assert hkl == want["hkl"] == (0, 0, 4) and p2 > 0.9
+        assert np.allclose(k, want["k"], rtol=1e-14, atol=1e-14)
+
+
+def test_order_parameters_at_scale_are_deterministic(device):
+    box, shapes = H.sc_lattice((60, 60, 30))         # 108 000 particles
+    device.set_interaction(H.desc_sc())
+    device.upload(box, shapes)
+    for cycle in range(3):
+        device.sweep(rp.RP_MOVE_ROTOTRANSLATION, 0.2, 0.1, cycle)
+    a = (device.nematic_order(), device.smectic_order((1, 1, 32)))
+    b = (device.nematic_order(), device.smectic_order((1, 1, 32)))
+    assert np.array_equal(a[0][0], b[0][0]) and a[0][1] == b[0][1] and a[1][0] == b[1][0]
+    assert a[0][1] > 0.95 and a[1][1] == (0, 0, 30)
+    _, s = device.download()
+    axes = s[:, 3:].reshape(-1, 3, 3)[:, :, 2]
+    qn = 1.5 * (axes[:, :, None] * axes[:, None, :]).mean(axis=0) - 0.5 * np.eye(3)
+    assert np.allclose(a[0][0], qn, rtol=0, atol=1e-13)
+
+
+def test_observable_preconditions(device):
+    box, shapes = H.sc_lattice((8, 8, 3))
+    device.set_interaction(H.desc_sc())
+    device.upload(box, shapes)
+    with pytest.raises(rp.PreconditionError):
+        device.smectic_order((0, 0, 0))

@@ -364,7 +364,8 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
     {
         cullThresholds(h, sg.relCell, &A.cullThr2, &A.cullHalf);
         // test hook: with the cull disabled every pair takes the exact FP64 test; the results must be bit-identical
-        if (std::getenv("RP_SWEEP_NO_CULL")) A.cullThr2 = 3.0e38f;
+        A.cull2Thr2 = std::nextafterf(static_cast<float>(I.scInner2 + 1e-3 * I.range * I.range), INFINITY);
+        if (std::getenv("RP_SWEEP_NO_CULL")) A.cullThr2 = A.cull2Thr2 = 3.0e38f;
     }
     A.cap = h->cap;
     A.aOff2 = 0;

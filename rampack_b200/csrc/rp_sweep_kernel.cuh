@@ -41,7 +41,8 @@ struct SweepGrid {
 
 constexpr int SW_MAXOWN = 64;      // trials resolved together (bit matrices are 64 bits wide)
 constexpr int SW_PUSH = 4;         // queue entries a lane may push per round
-constexpr int SW_WQCAP = 32 * SW_PUSH + 64;     // per-warp queue of (trial, candidate) pairs awaiting the exact test
+constexpr int SW_WQCAP1 = 32 * SW_PUSH + 64;    // per-warp queue of (trial, candidate) pairs that passed the first cull
+constexpr int SW_WQCAP = SW_WQCAP1 + 128;       // ... followed by the queue of pairs awaiting the exact test
 
 // the few interaction constants the sweep kernels need (rp::Inter thresholds, computed on the host with the
 // reference's expressions), passed by value
@@ -61,6 +62,7 @@ struct SweepArgs {
     int capOwn;                 // capacity of the trial region (max cell population)
     float cullThr2;             // FP32 cull threshold (squared distance) including the FP32 error bound
     float cullHalf;             // spherocylinders: half length of the axis segment
+    float cull2Thr2;            // spherocylinders: threshold of the FP32 segment-segment cull (squared distance)
     SweepInter inter;
     size_t cap;
     int aOff2;                  // sharded runs: first active-cell layer (z) of this rank's slab, else 0
@@ -115,6 +117,42 @@ __device__ __forceinline__ bool exactOverlap(const SweepInter &I, const double *
     V3 h1 = v3(t[3], t[4], t[5]), h2 = v3(c[3], c[4], c[5]);
     double s = segmentDistance2(p1 - h1, p1 + h1, p2 - h2, p2 + h2);
     return (d2 < I.scInner2) || (!(d2 >= I.scOuter2) && s < I.scInner2);
+}
+
+// Second FP32 cull for spherocylinders: squared distance between the two axis segments in single precision against
+// thr2 = 4r^2 + 1e-3 (l + 2r)^2.  Centred parametrisation P1(s) = c1 + s h1, P2(t) = c2 + t h2, s, t in [-1, 1]:
+// s = clamp(sN / denom) from the unconstrained optimum, t = the optimum for that s, and when t had to be clamped s =
+// the optimum for the clamped t.  Whatever rounding does to s (ill-conditioned for nearly parallel axes), the other
+// parameter is optimal for it, so the computed squared distance exceeds the true minimum only by
+// (denom / |h|^2) (s - s*)^2 relative to the clamped optimum: with absolute errors ~3e-5 in sN and ~1e-5 in denom
+// that is < 3e-5 in every regime (denom above the noise: quadratic in a small ds; denom inside the noise: the
+// coefficient itself is tiny; sign of sN lost: then |sN| is noise and the two ends differ by 4 |sN| / |h|^2), plus
+// ~1e-5 of input rounding (coordinates relative to the cell centre).  Observed maximum over 1.6e7 random pairs
+// including axes parallel to 1e-8: 4e-6 (tests/test_cull_math.py).  The margin is 0.036 for l = 5, r = 0.5 — and the
+// reference's own segment distance is never BELOW the true minimum — so a pair this cull drops is disjoint for the
+// FP64 test.  (Checked like the first cull: RP_SWEEP_NO_CULL=1 must give a bit-identical trajectory.)
+__device__ __forceinline__ bool segmentCullPass(const double *__restrict__ c, const V3 &origin, const float4 tf,
+                                                const float4 tu, float half, float thr2)
+{
+    const float dx = tf.x - static_cast<float>(c[0] - origin.x), dy = tf.y - static_cast<float>(c[1] - origin.y),
+                dz = tf.z - static_cast<float>(c[2] - origin.z);
+    const float h1x = tu.x * half, h1y = tu.y * half, h1z = tu.z * half;
+    const float h2x = static_cast<float>(c[3]), h2y = static_cast<float>(c[4]), h2z = static_cast<float>(c[5]);
+    const float a = half * half;                                  // |h1|^2 = |h2|^2
+    const float b = fmaf(h1z, h2z, fmaf(h1y, h2y, h1x * h2x));
+    const float cc = fmaf(h1z, dz, fmaf(h1y, dy, h1x * dx));
+    const float f = fmaf(h2z, dz, fmaf(h2y, dy, h2x * dx));
+    const float denom = fmaf(a, a, -b * b);
+    const float inva = __fdividef(1.0f, a);
+    float s = __fdividef(fmaf(b, f, -cc * a), fmaxf(denom, 1e-20f));    // nearly parallel: the SIGN still decides the end
+    s = fminf(fmaxf(s, -1.0f), 1.0f);
+    const float t0 = fmaf(b, s, f) * inva;
+    const float t = fminf(fmaxf(t0, -1.0f), 1.0f);
+    const float s1 = fminf(fmaxf(fmaf(b, t, -cc) * inva, -1.0f), 1.0f);
+    s = (t != t0) ? s1 : s;
+    const float px = fmaf(-t, h2x, fmaf(s, h1x, dx)), py = fmaf(-t, h2y, fmaf(s, h1y, dy)),
+                pz = fmaf(-t, h2z, fmaf(s, h1z, dz));
+    return !(fmaf(pz, pz, fmaf(py, py, px * px)) >= thr2);        // NaN passes
 }
 
 // ---------------------------------------------------------------------------------------------------------------

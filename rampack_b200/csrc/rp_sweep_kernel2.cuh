@@ -161,12 +161,36 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
         // Warps grab chunks of 32 candidates from a shared counter.  A: conservative FP32 cull of the chunk against
         // all trials (spheres: centre distance; spherocylinders: distance of the candidate's centre from the trial's
         // axis segment — a necessary condition for the two segments to come closer than 2r); survivors go to the
-        // warp's queue.  B: whenever 32 entries are queued they take the exact FP64 test with every lane busy.
+        // warp's queue.  B: whenever 64 entries are queued they take (spherocylinders) the FP32 segment-segment cull
+        // and its survivors, again in batches of 64, the exact FP64 test with every lane busy.
         {
             const float thrF = A.cullThr2, halfF = A.cullHalf;
             const unsigned long long dead = sRejMask;
-            unsigned int *q = queue + warp * SW_WQCAP;
-            int qn = 0;
+            unsigned int *q = queue + warp * SW_WQCAP;       // survivors of the centre-to-axis cull
+            unsigned int *q2 = q + SW_WQCAP1;                // survivors of the FP32 segment cull, awaiting FP64
+            int qn = 0, q2n = 0;
+            const unsigned int ltMask = (1u << lane) - 1u;
+            // B1: conservative FP32 segment-segment cull of 64 queued pairs (two per lane), survivors compacted into
+            // q2 by ballot; B2: the exact FP64 test on every full batch of 64 survivors
+            auto segmentCull = [&](unsigned int e0, unsigned int e1, bool v0, bool v1) {
+                if (HARD == RP_HARD_SPHEROCYLINDER) {
+                    const int t0 = e0 >> 16, c0 = e0 & 0xffff, t1 = e1 >> 16, c1 = e1 & 0xffff;
+                    v0 = v0 && !vrej[t0] && segmentCullPass(cand + 6 * static_cast<size_t>(c0), origin, trialF[t0],
+                                                            trialU[t0], halfF, A.cull2Thr2);
+                    v1 = v1 && !vrej[t1] && segmentCullPass(cand + 6 * static_cast<size_t>(c1), origin, trialF[t1],
+                                                            trialU[t1], halfF, A.cull2Thr2);
+                }
+                const unsigned int b0 = __ballot_sync(0xffffffffu, v0), b1 = __ballot_sync(0xffffffffu, v1);
+                if (v0) q2[q2n + __popc(b0 & ltMask)] = e0;
+                if (v1) q2[q2n + __popc(b0) + __popc(b1 & ltMask)] = e1;
+                q2n += __popc(b0) + __popc(b1);
+                __syncwarp();
+                while (q2n >= 64) {
+                    q2n -= 64;
+                    exactTest2(q2[q2n + lane], q2[q2n + 32 + lane], true, true);
+                }
+                __syncwarp();
+            };
             const int numChunks = (numCand + 31) >> 5;
             for (;;) {
                 int chunk = 0;
@@ -235,14 +259,18 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
                     __syncwarp();
                     while (qn >= 64) {
                         qn -= 64;
-                        exactTest2(q[qn + lane], q[qn + 32 + lane], true, true);
+                        segmentCull(q[qn + lane], q[qn + 32 + lane], true, true);
                     }
                     __syncwarp();
                 }
             }
             if (qn > 0) {
                 const bool v0 = lane < qn, v1 = lane + 32 < qn;
-                exactTest2(v0 ? q[lane] : 0u, v1 ? q[lane + 32] : 0u, v0, v1);
+                segmentCull(v0 ? q[lane] : 0u, v1 ? q[lane + 32] : 0u, v0, v1);
+            }
+            if (q2n > 0) {
+                const bool v0 = lane < q2n, v1 = lane + 32 < q2n;
+                exactTest2(v0 ? q2[lane] : 0u, v1 ? q2[lane + 32] : 0u, v0, v1);
             }
         }
 

@@ -13,6 +13,9 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
     constexpr int WARPS = THREADS / 32;
     extern __shared__ __align__(16) unsigned char smemRaw[];
     __shared__ float4 trialF[SW_MAXOWN], trialU[SW_MAXOWN];
+    // the same FP32 trial data for the packed (f32x2) cull loop, two trials per entry: (-x0, -x1, -y0, -y1),
+    // (-z0, -z1, ux0, ux1), (uy0, uy1, uz0, uz1)
+    __shared__ float4 trialP[SW_MAXOWN / 2 + 1][3];
     __shared__ unsigned long long ownMask[SW_MAXOWN], newMask[SW_MAXOWN], seqOwn[SW_MAXOWN], seqNew[SW_MAXOWN];
     __shared__ unsigned int orderKey[SW_MAXOWN];
     __shared__ int seqInfo[SW_MAXOWN];
@@ -125,11 +128,20 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
             if (HARD == RP_HARD_SPHEROCYLINDER)      // FP32 unit axis of the trial for the capsule cull
                 trialU[tid] = make_float4(static_cast<float>(h.x / I.scHalf), static_cast<float>(h.y / I.scHalf),
                                           static_cast<float>(h.z / I.scHalf), 0.f);
+            {
+                float *tp = reinterpret_cast<float *>(&trialP[tid >> 1][0]) + (tid & 1);
+                tp[0] = -trialF[tid].x; tp[2] = -trialF[tid].y; tp[4] = -trialF[tid].z;
+                if (HARD == RP_HARD_SPHEROCYLINDER) { tp[6] = trialU[tid].x; tp[8] = trialU[tid].y; tp[10] = trialU[tid].z; }
+            }
             rejected[tid] = static_cast<int>(meta.x);
             orderKey[tid] = meta.y;
             ownMask[tid] = 0ull;
             newMask[tid] = 0ull;
             if (meta.x) atomicOr(&sRejMask, 1ull << tid);
+        }
+        if (tid == numOwn && (numOwn & 1)) {        // odd count: the partner of the last trial is out of everyone's reach
+            float *tp = reinterpret_cast<float *>(&trialP[tid >> 1][0]) + 1;
+            tp[0] = -1e18f; tp[2] = 0.f; tp[4] = 0.f; tp[6] = 0.f; tp[8] = 0.f; tp[10] = 0.f;
         }
         __syncthreads();
 
@@ -208,27 +220,38 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
                     cyf = static_cast<float>(r[1] - origin.y);
                     czf = static_cast<float>(r[2] - origin.z);
                 }
+                // two trials per iteration with the packed FP32 instructions of sm_100 (FADD2 / FMUL2 / FFMA2): the
+                // same operations in the same order as the scalar form, half the issue slots
                 unsigned int mlo = 0, mhi = 0;
+                const float2 cx2 = make_float2(cxf, cxf), cy2 = make_float2(cyf, cyf), cz2 = make_float2(czf, czf);
+                const int numPairs = (numOwn + 1) >> 1;
                 #pragma unroll
                 for (int half = 0; half < 2; half++) {
-                    const int i0 = half * 32, i1 = min(numOwn, i0 + 32);
+                    const int k0 = half * 16, k1 = min(numPairs, k0 + 16);
                     unsigned int bit = 1, mm = 0;
                     #pragma unroll 4
-                    for (int i = i0; i < i1; i++) {
-                        const float4 tf = trialF[i];
-                        float dx = cxf - tf.x, dy = cyf - tf.y, dz = czf - tf.z;
-                        float d2;
+                    for (int k = k0; k < k1; k++) {
+                        const float4 pa = trialP[k][0], pb = trialP[k][1];
+                        const float2 dx = __fadd2_rn(cx2, make_float2(pa.x, pa.y)),
+                                     dy = __fadd2_rn(cy2, make_float2(pa.z, pa.w)),
+                                     dz = __fadd2_rn(cz2, make_float2(pb.x, pb.y));
+                        float2 d2;
                         if (HARD == RP_HARD_SPHEROCYLINDER) {
-                            const float4 tu = trialU[i];
-                            float s = fmaf(dz, tu.z, fmaf(dy, tu.y, dx * tu.x));
-                            s = fminf(fmaxf(s, -halfF), halfF);
-                            float rx = fmaf(-s, tu.x, dx), ry = fmaf(-s, tu.y, dy), rz = fmaf(-s, tu.z, dz);
-                            d2 = fmaf(rz, rz, fmaf(ry, ry, rx * rx));
+                            const float4 pc = trialP[k][2];
+                            const float2 ux = make_float2(pb.z, pb.w), uy = make_float2(pc.x, pc.y),
+                                         uz = make_float2(pc.z, pc.w);
+                            const float2 t = __ffma2_rn(dz, uz, __ffma2_rn(dy, uy, __fmul2_rn(dx, ux)));
+                            const float2 ns = make_float2(fminf(fmaxf(-t.x, -halfF), halfF),
+                                                          fminf(fmaxf(-t.y, -halfF), halfF));
+                            const float2 rx = __ffma2_rn(ns, ux, dx), ry = __ffma2_rn(ns, uy, dy),
+                                         rz = __ffma2_rn(ns, uz, dz);
+                            d2 = __ffma2_rn(rz, rz, __ffma2_rn(ry, ry, __fmul2_rn(rx, rx)));
                         } else {
-                            d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                            d2 = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
                         }
-                        if (d2 < thrF) mm |= bit;
-                        bit <<= 1;
+                        if (d2.x < thrF) mm |= bit;
+                        if (d2.y < thrF) mm |= bit << 1;
+                        bit <<= 2;
                     }
                     if (half == 0) mlo = mm; else mhi = mm;
                 }

@@ -39,6 +39,9 @@ struct SweepGrid {
     V3 trans[27];
 };
 
+// staging order of the 27 neighbour cells (codes (dz+1)*9 + (dy+1)*3 + (dx+1)): own cell, faces, edges, corners
+__device__ const unsigned char SW_STAGE_ORDER[27] = {13, 4, 10, 12, 14, 16, 22, 1, 3, 5, 7, 9, 11, 15, 17, 19, 21, 23, 25,
+                                                     0, 2, 6, 8, 18, 20, 24, 26};
 constexpr int SW_MAXOWN = 64;      // trials resolved together (bit matrices are 64 bits wide)
 constexpr int SW_PUSH = 4;         // queue entries a lane may push per round
 constexpr int SW_WQCAP1 = 32 * SW_PUSH + 64;    // per-warp queue of (trial, candidate) pairs that passed the first cull

@@ -40,11 +40,13 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
     const int cx = 2 * a0 + A.colour[0], cy = 2 * a1 + A.colour[1], cz = 2 * a2 + A.colour[2];
     const int ownCell = (cz * sg.n[1] + cy) * sg.n[0] + cx;
 
-    // neighbour code c = (dz+1)*9 + (dy+1)*3 + (dx+1): the three cells of an x-run are adjacent in the staging area
-    // exactly as they are in the cell-sorted global order (cells are flattened x-fastest)
+    // neighbour code c = (dz+1)*9 + (dy+1)*3 + (dx+1).  Staging position p holds the cell with code SW_STAGE_ORDER[p]:
+    // the own cell first, then the 6 face, 12 edge and 8 corner neighbours — chunks of candidates are handed out in
+    // this order, so the expensive ones (many survivors of the cull) come first and the warps finish together
     if (tid < 27) {
         int tIdx;
-        int c2 = neighbourCell(sg.n, cx, cy, cz, tid % 3 - 1, (tid / 3) % 3 - 1, tid / 9 - 1, &tIdx);
+        const int code = SW_STAGE_ORDER[tid];
+        int c2 = neighbourCell(sg.n, cx, cy, cz, code % 3 - 1, (code / 3) % 3 - 1, code / 9 - 1, &tIdx);
         cellSrc[tid] = cellStart[c2];
         cellBegin[tid] = cellStart[c2 + 1] - cellStart[c2];     // count, turned into an offset below
         cellT[tid] = tIdx;
@@ -66,7 +68,7 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
             if (lane >= d) incl += v;
         }
         const int total = __shfl_sync(0xffffffffu, incl, 26);
-        const int numOwnT = __shfl_sync(0xffffffffu, cnt, 13);
+        const int numOwnT = __shfl_sync(0xffffffffu, cnt, 0);
         const bool ok = numOwnT > 0 && total <= A.capOld && numOwnT <= A.capOwn;
         if (lane == 0 && ok) mbarExpectTx(&sBar, static_cast<unsigned int>((total + numOwnT) * 48));
         __syncwarp();
@@ -82,7 +84,7 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
         }
     }
     __syncthreads();
-    const int numOld = cellBegin[27], ownBeginAll = cellBegin[13], numOwnAll = cellBegin[14] - cellBegin[13];
+    const int numOld = cellBegin[27], ownBeginAll = cellBegin[0], numOwnAll = cellBegin[1] - cellBegin[0];
     if (numOwnAll == 0) return;
     if (numOld > A.capOld || numOwnAll > A.capOwn) {
         if (tid == 0) atomicOr(&flags[3], 1);
@@ -144,6 +146,17 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
             tp[0] = -1e18f; tp[2] = 0.f; tp[4] = 0.f; tp[6] = 0.f; tp[8] = 0.f; tp[10] = 0.f;
         }
         __syncthreads();
+
+        // position of every trial in the cell's random order (needed by phase C; computed here, off the critical path:
+        // the other warps are already culling)
+        int rank = 0;
+        if (tid < numOwn) {
+            const unsigned int k = orderKey[tid];
+            for (int j = 0; j < numOwn; j++) {
+                const unsigned int kj = orderKey[j];
+                rank += (kj < k) || (kj == k && j < tid);
+            }
+        }
 
         volatile int *vrej = rejected;
         auto record = [&](int ti, int cj) {
@@ -211,7 +224,7 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
                 if (chunk >= numChunks) break;
                 const int jj = (chunk << 5) + lane;
                 const bool valid = jj < numCand;
-                const int j = jj < numOld ? jj : jj + batch0;
+                const int j = jj < numOwn ? newBegin + jj : jj - numOwn;      // the new states of the trials first
                 // a far-away dummy for the invalid slots keeps the loop branch-free
                 float cxf = 1e18f, cyf = 0.f, czf = 0.f;
                 if (valid) {         // FP32 copy of the position in cell-local coordinates
@@ -298,14 +311,6 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
         }
 
         // ---- phase C: sequential resolution inside the cell, random order, from the bit matrices ----
-        int rank = 0;
-        if (tid < numOwn) {
-            const unsigned int k = orderKey[tid];
-            for (int j = 0; j < numOwn; j++) {
-                const unsigned int kj = orderKey[j];
-                rank += (kj < k) || (kj == k && j < tid);
-            }
-        }
         __syncthreads();
         if (tid < numOwn) {
             seqOwn[rank] = ownMask[tid];

@@ -275,29 +275,26 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
                 if (nw >= 0 && nw < numOwn) m &= ~(1ull << nw);
                 m &= ~dead;
 
-                // push at most SW_PUSH entries per lane and round; run the exact tests on every full batch of 64
-                while (__any_sync(0xffffffffu, m != 0ull)) {
-                    const int cnt = min(__popcll(m), SW_PUSH);
-                    int incl = cnt;
-                    #pragma unroll
-                    for (int d = 1; d < 32; d <<= 1) {
-                        int v = __shfl_up_sync(0xffffffffu, incl, d);
-                        if (lane >= d) incl += v;
+                // push: one entry per lane and round, queue slots from a ballot (no scan); whenever 64 entries are
+                // queued they go through the second cull
+                #pragma unroll 1
+                for (int half = 0; half < 2; half++) {
+                    unsigned int mm = half ? static_cast<unsigned int>(m >> 32) : static_cast<unsigned int>(m);
+                    unsigned int has;
+                    while ((has = __ballot_sync(0xffffffffu, mm != 0u)) != 0u) {
+                        if (mm != 0u) {
+                            const unsigned int i = static_cast<unsigned int>(__ffs(static_cast<int>(mm)) - 1 + 32 * half);
+                            mm &= mm - 1u;
+                            q[qn + __popc(has & ltMask)] = (i << 16) | static_cast<unsigned int>(j);
+                        }
+                        qn += __popc(has);
+                        __syncwarp();
+                        if (qn >= 64) {
+                            qn -= 64;
+                            segmentCull(q[qn + lane], q[qn + 32 + lane], true, true);
+                        }
+                        __syncwarp();
                     }
-                    const int total = __shfl_sync(0xffffffffu, incl, 31);
-                    int at = qn + incl - cnt;
-                    for (int k = 0; k < cnt; k++) {
-                        const int i = __ffsll(static_cast<long long>(m)) - 1;
-                        m &= m - 1;
-                        q[at + k] = (static_cast<unsigned int>(i) << 16) | static_cast<unsigned int>(j);
-                    }
-                    qn += total;
-                    __syncwarp();
-                    while (qn >= 64) {
-                        qn -= 64;
-                        segmentCull(q[qn + lane], q[qn + 32 + lane], true, true);
-                    }
-                    __syncwarp();
                 }
             }
             if (qn > 0) {

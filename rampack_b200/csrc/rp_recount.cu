@@ -338,6 +338,7 @@ unsigned long long countTotalOverlaps(Handle *h, bool earlyExit) {
         A.inter.scHalf = I.scHalfPlus;
         A.earlyExit = earlyExit ? 1 : 0;
         cullThresholds(h, g.relCell, &A.cullThr2, &A.cullHalf);
+        A.cull2Thr2 = std::nextafterf(static_cast<float>(I.scInner2 + 1e-3 * I.range * I.range), INFINITY);
         A.cellBegin = 0;
         A.cellEnd = g.numCells;
         if (shardActive(h)) {

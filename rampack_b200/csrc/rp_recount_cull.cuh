@@ -1,6 +1,7 @@
 // rp_recount_cull.cuh — full-system overlap recount for single-centre hard spheres / spherocylinders with the same
-// two-stage pair test as the sweep kernel: conservative FP32 cull (warp-wide, branch-free), survivors compacted into
-// a per-warp queue, exact FP64 test (reference operation order) 64 pairs at a time.  Included by rp_recount.cu.
+// staged pair test as the sweep kernel: conservative FP32 cull (warp-wide, branch-free), survivors compacted into
+// a per-warp queue, (spherocylinders) FP32 segment-segment cull 64 pairs at a time, its survivors compacted again,
+// exact FP64 test (reference operation order) 64 pairs at a time.  Included by rp_recount.cu.
 //
 // Pair enumeration = the reference's (core/Packing.cpp:431-559): every real cell x {own cell i < j, 13 "positive"
 // neighbour cells (9a + 3b + c > 13, core/NeighbourGrid.cpp:127-131)}; one warp per cell.
@@ -12,11 +13,12 @@
 namespace rp {
 
 constexpr int RC_WARPS = 4;
-constexpr int RC_QCAP = 32 * SW_PUSH + 64;
+constexpr int RC_QCAP = 96;       // first-cull survivors: < 64 waiting + 32 pushed per round
+constexpr int RC_Q2CAP = 128;     // second-cull survivors: < 64 waiting + 64 per round
 
 struct RecountArgs {
     SweepInter inter;
-    float cullThr2, cullHalf;
+    float cullThr2, cullHalf, cull2Thr2;
     int earlyExit;
     int cellBegin, cellEnd;     // cells this launch covers (sharded runs: this rank's share)
 };
@@ -27,7 +29,7 @@ k_recount_cull(GridView g, Box box, RecountArgs A, unsigned long long *__restric
 {
     __shared__ float4 sOwnF[RC_WARPS][SW_MAXOWN], sOwnU[RC_WARPS][SW_MAXOWN];
     __shared__ double sOwn6[RC_WARPS][SW_MAXOWN][6];
-    __shared__ unsigned long long sQueue[RC_WARPS][RC_QCAP];
+    __shared__ unsigned long long sQueue[RC_WARPS][RC_QCAP], sQueue2[RC_WARPS][RC_Q2CAP];
     __shared__ int sNbBegin[RC_WARPS][16], sNbStart[RC_WARPS][16], sNbT[RC_WARPS][16];
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -37,7 +39,7 @@ k_recount_cull(GridView g, Box box, RecountArgs A, unsigned long long *__restric
     const SweepInter &I = A.inter;
     float4 *ownF = sOwnF[warp], *ownU = sOwnU[warp];
     double (*own6)[6] = sOwn6[warp];
-    unsigned long long *q = sQueue[warp];
+    unsigned long long *q = sQueue[warp], *q2 = sQueue2[warp];
     int *nbBegin = sNbBegin[warp], *nbStart = sNbStart[warp], *nbT = sNbT[warp];
 
     const int cx = cell % g.n[0], cy = (cell / g.n[0]) % g.n[1], cz = cell / (g.n[0] * g.n[1]);
@@ -68,7 +70,8 @@ k_recount_cull(GridView g, Box box, RecountArgs A, unsigned long long *__restric
     const V3 origin = relToAbs(box, v3((cx + 0.5) * g.relCell[0], (cy + 0.5) * g.relCell[1], (cz + 0.5) * g.relCell[2]));
     const float thrF = A.cullThr2, halfF = A.cullHalf;
     unsigned long long overlaps = 0;
-    int qn = 0;
+    int qn = 0, q2n = 0;
+    const unsigned int ltMask = (1u << lane) - 1u;
 
     // exact tests of two queue entries per lane; entry = own index (6 bits) | candidate cell slot k (4 bits) << 8 |
     // sorted index of the candidate << 16
@@ -89,6 +92,36 @@ k_recount_cull(GridView g, Box box, RecountArgs A, unsigned long long *__restric
         const bool r0 = exactOverlap<HARD>(I, own6[e0 & 0x3f], c0);
         const bool r1 = exactOverlap<HARD>(I, own6[e1 & 0x3f], c1);
         overlaps += (v0 && r0) + (v1 && r1);
+    };
+
+    // second cull (segmentCullPass, rp_sweep_kernel.cuh) of two queue entries per lane; survivors to q2 by ballot
+    auto segmentCull2 = [&](unsigned long long e0, unsigned long long e1, bool v0, bool v1) {
+        if (HARD == RP_HARD_SPHEROCYLINDER) {
+            const unsigned long long es[2] = {e0, e1};
+            bool pass[2] = {v0, v1};
+            #pragma unroll
+            for (int w = 0; w < 2; w++) {
+                if (!pass[w]) continue;
+                const int k = static_cast<int>((es[w] >> 8) & 0xf);
+                const int j = static_cast<int>(es[w] >> 16);
+                const int i = static_cast<int>(es[w] & 0x3f);
+                const V3 t = g.trans[nbT[k]];
+                const double c[6] = {g.px[j] + t.x, g.py[j] + t.y, g.pz[j] + t.z,
+                                     g.ax[j] * I.scHalf, g.ay[j] * I.scHalf, g.az[j] * I.scHalf};
+                pass[w] = segmentCullPass(c, origin, ownF[i], ownU[i], halfF, A.cull2Thr2);
+            }
+            v0 = pass[0]; v1 = pass[1];
+        }
+        const unsigned int b0 = __ballot_sync(0xffffffffu, v0), b1 = __ballot_sync(0xffffffffu, v1);
+        if (v0) q2[q2n + __popc(b0 & ltMask)] = e0;
+        if (v1) q2[q2n + __popc(b0) + __popc(b1 & ltMask)] = e1;
+        q2n += __popc(b0) + __popc(b1);
+        __syncwarp();
+        while (q2n >= 64) {
+            q2n -= 64;
+            exact2(q2[q2n + lane], q2[q2n + 32 + lane], true, true);
+        }
+        __syncwarp();
     };
 
     for (int batch0 = 0; batch0 < nOwnAll; batch0 += SW_MAXOWN) {
@@ -154,36 +187,39 @@ k_recount_cull(GridView g, Box box, RecountArgs A, unsigned long long *__restric
             }
             if (!valid) m = 0ull;
 
-            while (__any_sync(0xffffffffu, m != 0ull)) {
-                const int cnt = min(__popcll(m), SW_PUSH);
-                int inc2 = cnt;
-                #pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    int v = __shfl_up_sync(0xffffffffu, inc2, d);
-                    if (lane >= d) inc2 += v;
+            // push: one entry per lane and round, queue slots from a ballot
+            #pragma unroll 1
+            for (int half = 0; half < 2; half++) {
+                unsigned int mm = half ? static_cast<unsigned int>(m >> 32) : static_cast<unsigned int>(m);
+                unsigned int has;
+                while ((has = __ballot_sync(0xffffffffu, mm != 0u)) != 0u) {
+                    if (mm != 0u) {
+                        const int i = __ffs(static_cast<int>(mm)) - 1 + 32 * half;
+                        mm &= mm - 1u;
+                        q[qn + __popc(has & ltMask)] = static_cast<unsigned long long>(i)
+                                                       | (static_cast<unsigned long long>(k) << 8)
+                                                       | (static_cast<unsigned long long>(j) << 16);
+                    }
+                    qn += __popc(has);
+                    __syncwarp();
+                    if (qn >= 64) {
+                        qn -= 64;
+                        segmentCull2(q[qn + lane], q[qn + 32 + lane], true, true);
+                    }
+                    __syncwarp();
                 }
-                const int tot = __shfl_sync(0xffffffffu, inc2, 31);
-                int at = qn + inc2 - cnt;
-                for (int kk = 0; kk < cnt; kk++) {
-                    const int i = __ffsll(static_cast<long long>(m)) - 1;
-                    m &= m - 1;
-                    q[at + kk] = static_cast<unsigned long long>(i) | (static_cast<unsigned long long>(k) << 8)
-                                 | (static_cast<unsigned long long>(j) << 16);
-                }
-                qn += tot;
-                __syncwarp();
-                while (qn >= 64) {
-                    qn -= 64;
-                    exact2(q[qn + lane], q[qn + 32 + lane], true, true);
-                }
-                __syncwarp();
             }
         }
         // drain before the own records are replaced by the next batch
         if (qn > 0) {
             const bool v0 = lane < qn, v1 = lane + 32 < qn;
-            exact2(v0 ? q[lane] : 0ull, v1 ? q[lane + 32] : 0ull, v0, v1);
+            segmentCull2(v0 ? q[lane] : 0ull, v1 ? q[lane + 32] : 0ull, v0, v1);
             qn = 0;
+        }
+        if (q2n > 0) {
+            const bool v0 = lane < q2n, v1 = lane + 32 < q2n;
+            exact2(v0 ? q2[lane] : 0ull, v1 ? q2[lane + 32] : 0ull, v0, v1);
+            q2n = 0;
         }
         if (A.earlyExit && __any_sync(0xffffffffu, overlaps > 0)) break;
     }

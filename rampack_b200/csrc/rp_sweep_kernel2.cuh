@@ -173,6 +173,12 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
             const int t0 = e0 >> 16, c0 = e0 & 0xffff, t1 = e1 >> 16, c1 = e1 & 0xffff;
             v0 = v0 && !vrej[t0];
             v1 = v1 && !vrej[t1];
+            if (!__any_sync(0xffffffffu, v1)) {        // a short tail: one test per lane
+                if (v0 && exactOverlap<HARD>(I, cand + 6 * static_cast<size_t>(newBegin + t0),
+                                             cand + 6 * static_cast<size_t>(c0)))
+                    record(t0, c0);
+                return;
+            }
             if (!(v0 || v1)) return;
             const bool r0 = exactOverlap<HARD>(I, cand + 6 * static_cast<size_t>(newBegin + t0),
                                                cand + 6 * static_cast<size_t>(c0));

@@ -57,6 +57,9 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
     }
     __syncthreads();
     const int ownStartAll = cellStart[ownCell];
+    // trial meta of the first batch: requested now, used after the staging has landed
+    uint2 metaFirst = make_uint2(0u, 0u);
+    if (tid < min(cellStart[ownCell + 1] - ownStartAll, SW_MAXOWN)) metaFirst = T.meta[ownStartAll + tid];
     if (warp == 0) {
         // exclusive scan of the 27 cell populations -> staging offsets; every lane then issues the 1-D TMA bulk copy
         // of its own cell (lane 27: the trial records of the own cell)
@@ -122,7 +125,7 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
         if (tid == 0) { sAccepted = 0ull; sRejMask = 0ull; qCount = 0; }
         __syncthreads();       // staging passes done (first batch) / previous batch fully written back
         if (tid < numOwn) {
-            const uint2 meta = T.meta[ownStart + tid];
+            const uint2 meta = batch0 == 0 ? metaFirst : T.meta[ownStart + tid];
             const double *r = cand + 6 * static_cast<size_t>(newBegin + tid);
             V3 p = v3(r[0], r[1], r[2]), h = v3(r[3], r[4], r[5]);
             trialF[tid] = make_float4(static_cast<float>(p.x - origin.x), static_cast<float>(p.y - origin.y),
@@ -320,6 +323,17 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
             seqNew[rank] = newMask[tid];
             seqInfo[rank] = (rejected[tid] << 8) | tid;
         }
+        // global loads of the write-back issued now: their latency passes while thread 0 resolves the cell
+        double oNew[9];
+        int particleId = 0;
+        if (tid < numOwn) {
+            particleId = items[ownStart + tid];
+            if (rotated) {
+                const double *o = T.orient + 9 * static_cast<size_t>(ownStart + tid);
+                #pragma unroll
+                for (int q = 0; q < 9; q++) oNew[q] = o[q];
+            }
+        }
         __syncthreads();
         if (tid == 0) {
             unsigned long long moved = 0ull;
@@ -345,7 +359,6 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
         // ---- write-back of the accepted moves: sorted record (image frame) and canonical arrays (wrapped) ----
         if (tid < numOwn && ((sAccepted >> tid) & 1ull)) {
             const double *t = cand + 6 * static_cast<size_t>(newBegin + tid);
-            const int particleId = items[ownStart + tid];
             double *r = rec + 6 * static_cast<size_t>(ownStart + tid);
             for (int q = 0; q < 6; q++) r[q] = t[q];
             T.meta[ownStart + tid].x = 4u;      // accepted (read back by rp_sweep_trace only)
@@ -361,8 +374,8 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
                 pos[particleId] = p.x; pos[A.cap + particleId] = p.y; pos[2 * A.cap + particleId] = p.z;
             }
             if (rotated) {
-                const double *o = T.orient + 9 * static_cast<size_t>(ownStart + tid);
-                for (int q = 0; q < 9; q++) orient[q * A.cap + particleId] = o[q];
+                #pragma unroll
+                for (int q = 0; q < 9; q++) orient[q * A.cap + particleId] = oNew[q];
             }
             // sharded run over peer memory: the z-neighbour reads my boundary layers in the next colour
             if (peers.n > 0) {

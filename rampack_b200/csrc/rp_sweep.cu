@@ -129,7 +129,8 @@ void cullThresholds(const Handle *h, const double relCell[3], float *thr2, float
         E += 1.5 * relCell[i] * std::sqrt(norm2(relToAbs(h->box, v3(i == 0, i == 1, i == 2))));
     double R = I.range, u = std::ldexp(1.0, -24), delta = 4 * E * u;
     double Rc = (I.hard == RP_HARD_SPHEROCYLINDER) ? std::sqrt(I.scInner2) + I.scHalfPlus : R;
-    double margin = 8 * Rc * (8 * delta + 8 * u * R) + 1e-5 * Rc * Rc;
+    // + 64 u R^2: the sweep kernel evaluates |d|^2 + s (s - 2 d.u) (cancellation of terms up to R^2)
+    double margin = 8 * Rc * (8 * delta + 8 * u * R) + 1e-5 * Rc * Rc + 64 * u * R * R;
     *thr2 = std::nextafterf(static_cast<float>(Rc * Rc + margin), INFINITY);
     *half = static_cast<float>(I.scHalfPlus);
 }

@@ -111,6 +111,7 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
         }
     }
 
+    const float invHalfF = HARD == RP_HARD_SPHEROCYLINDER ? __fdividef(1.0f, A.cullHalf) : 0.f;
     const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION);
     const bool translated = (A.kind == RP_MOVE_TRANSLATION || A.kind == RP_MOVE_ROTOTRANSLATION);
 
@@ -131,8 +132,8 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
             trialF[tid] = make_float4(static_cast<float>(p.x - origin.x), static_cast<float>(p.y - origin.y),
                                       static_cast<float>(p.z - origin.z), 0.f);
             if (HARD == RP_HARD_SPHEROCYLINDER)      // FP32 unit axis of the trial for the capsule cull
-                trialU[tid] = make_float4(static_cast<float>(h.x / I.scHalf), static_cast<float>(h.y / I.scHalf),
-                                          static_cast<float>(h.z / I.scHalf), 0.f);
+                trialU[tid] = make_float4(static_cast<float>(h.x) * invHalfF, static_cast<float>(h.y) * invHalfF,
+                                          static_cast<float>(h.z) * invHalfF, 0.f);
             {
                 float *tp = reinterpret_cast<float *>(&trialP[tid >> 1][0]) + (tid & 1);
                 tp[0] = -trialF[tid].x; tp[2] = -trialF[tid].y; tp[4] = -trialF[tid].z;

@@ -18,9 +18,10 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
     __shared__ float4 trialP[SW_MAXOWN / 2 + 1][3];
     __shared__ unsigned long long ownMask[SW_MAXOWN], newMask[SW_MAXOWN], seqOwn[SW_MAXOWN], seqNew[SW_MAXOWN];
     __shared__ unsigned int orderKey[SW_MAXOWN];
-    __shared__ int seqInfo[SW_MAXOWN];
+    __shared__ unsigned long long seqBit[SW_MAXOWN];
     __shared__ int rejected[SW_MAXOWN];     // 0 = alive, 1 = overlap with a frozen particle, 2 = left the cell
     __shared__ unsigned long long sAccepted, sRejMask, sBar;
+    __shared__ int sDomain;
     __shared__ int cellBegin[28], cellSrc[27], cellT[27];
     __shared__ int sStats[3];
     __shared__ int qCount;
@@ -123,7 +124,7 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
         const int newBegin = numOld + batch0;          // new states of this batch's trials inside cand[]
         const int numCand = numOld + numOwn;
 
-        if (tid == 0) { sAccepted = 0ull; sRejMask = 0ull; qCount = 0; }
+        if (tid == 0) { sAccepted = 0ull; sRejMask = 0ull; qCount = 0; sDomain = 0; }
         __syncthreads();       // staging passes done (first batch) / previous batch fully written back
         if (tid < numOwn) {
             const uint2 meta = batch0 == 0 ? metaFirst : T.meta[ownStart + tid];
@@ -144,6 +145,7 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
             ownMask[tid] = 0ull;
             newMask[tid] = 0ull;
             if (meta.x) atomicOr(&sRejMask, 1ull << tid);
+            if (meta.x == 2u) atomicAdd(&sDomain, 1);
         }
         if (tid == numOwn && (numOwn & 1)) {        // odd count: the partner of the last trial is out of everyone's reach
             float *tp = reinterpret_cast<float *>(&trialP[tid >> 1][0]) + 1;
@@ -322,9 +324,11 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
         // ---- phase C: sequential resolution inside the cell, random order, from the bit matrices ----
         __syncthreads();
         if (tid < numOwn) {
-            seqOwn[rank] = ownMask[tid];
-            seqNew[rank] = newMask[tid];
-            seqInfo[rank] = (rejected[tid] << 8) | tid;
+            // a rejected trial (left its cell, hit a wall or a frozen particle) is blocked whatever has moved
+            const bool alive = rejected[tid] == 0;
+            seqOwn[rank] = alive ? ownMask[tid] : ~0ull;
+            seqNew[rank] = alive ? newMask[tid] : ~0ull;
+            seqBit[rank] = 1ull << tid;
         }
         // global loads of the write-back issued now: their latency passes while thread 0 resolves the cell
         double oNew[9];
@@ -339,23 +343,17 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
         }
         __syncthreads();
         if (tid == 0) {
+            // the only loop-carried value is `moved`: select, or, compare, predicated or per step
             unsigned long long moved = 0ull;
-            int nAcc = 0, nRejDomain = 0, nRejOverlap = 0;
             #pragma unroll 4
             for (int step = 0; step < numOwn; step++) {
-                const int info = seqInfo[step];
                 const unsigned long long blockers = (seqOwn[step] & ~moved) | (seqNew[step] & moved);
-                const int r = info >> 8;
-                if (r == 2) nRejDomain++;
-                else if (r == 1 || blockers != 0ull) nRejOverlap++;
-                else {
-                    // hard interactions only: Metropolis u <= exp(-0/T) always accepts (Simulation.cpp:483)
-                    moved |= 1ull << (info & 0xff);
-                    nAcc++;
-                }
+                // hard interactions only: Metropolis u <= exp(-0/T) always accepts (Simulation.cpp:483)
+                moved |= blockers == 0ull ? seqBit[step] : 0ull;
             }
+            const int nAcc = __popcll(moved), nRejDomain = sDomain;
             sAccepted = moved;
-            sStats[0] += nAcc; sStats[1] += nRejDomain; sStats[2] += nRejOverlap;
+            sStats[0] += nAcc; sStats[1] += nRejDomain; sStats[2] += numOwn - nAcc - nRejDomain;
         }
         __syncthreads();
 

@@ -22,7 +22,7 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
     __shared__ int rejected[SW_MAXOWN];     // 0 = alive, 1 = overlap with a frozen particle, 2 = left the cell
     __shared__ unsigned long long sAccepted, sRejMask, sBar;
     __shared__ int sDomain;
-    __shared__ int cellBegin[28], cellSrc[27], cellT[27];
+    __shared__ int cellBegin[28], cellT[27];
     __shared__ int sStats[3];
     __shared__ int qCount;
 
@@ -43,28 +43,24 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
 
     // neighbour code c = (dz+1)*9 + (dy+1)*3 + (dx+1).  Staging position p holds the cell with code SW_STAGE_ORDER[p]:
     // the own cell first, then the 6 face, 12 edge and 8 corner neighbours — chunks of candidates are handed out in
-    // this order, so the expensive ones (many survivors of the cull) come first and the warps finish together
-    if (tid < 27) {
-        int tIdx;
-        const int code = SW_STAGE_ORDER[tid];
-        int c2 = neighbourCell(sg.n, cx, cy, cz, code % 3 - 1, (code / 3) % 3 - 1, code / 9 - 1, &tIdx);
-        cellSrc[tid] = cellStart[c2];
-        cellBegin[tid] = cellStart[c2 + 1] - cellStart[c2];     // count, turned into an offset below
-        cellT[tid] = tIdx;
-    }
-    if (tid == 0) {
-        sStats[0] = 0; sStats[1] = 0; sStats[2] = 0;
-        mbarInit(&sBar, 1);
-    }
-    __syncthreads();
-    const int ownStartAll = cellStart[ownCell];
-    // trial meta of the first batch: requested now, used after the staging has landed
-    uint2 metaFirst = make_uint2(0u, 0u);
-    if (tid < min(cellStart[ownCell + 1] - ownStartAll, SW_MAXOWN)) metaFirst = T.meta[ownStartAll + tid];
+    // this order, so the expensive ones (many survivors of the cull) come first and the warps finish together.
+    // Warp 0 does the whole set-up in registers (one round trip to the cell table, scan, TMA issue) — the only CTA
+    // barrier before the data lands is the one below.
+    int ownStartAll, ownCountAll;
     if (warp == 0) {
+        int cnt = 0, src = 0, tIdx = 13;
+        if (lane < 27) {
+            const int code = SW_STAGE_ORDER[lane];
+            const int c2 = neighbourCell(sg.n, cx, cy, cz, code % 3 - 1, (code / 3) % 3 - 1, code / 9 - 1, &tIdx);
+            src = cellStart[c2];
+            cnt = cellStart[c2 + 1] - src;
+        }
+        if (lane == 0) {
+            sStats[0] = 0; sStats[1] = 0; sStats[2] = 0;
+            mbarInit(&sBar, 1);
+        }
         // exclusive scan of the 27 cell populations -> staging offsets; every lane then issues the 1-D TMA bulk copy
         // of its own cell (lane 27: the trial records of the own cell)
-        const int cnt = lane < 27 ? cellBegin[lane] : 0;
         int incl = cnt;
         #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -72,21 +68,29 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
             if (lane >= d) incl += v;
         }
         const int total = __shfl_sync(0xffffffffu, incl, 26);
-        const int numOwnT = __shfl_sync(0xffffffffu, cnt, 0);
-        const bool ok = numOwnT > 0 && total <= A.capOld && numOwnT <= A.capOwn;
-        if (lane == 0 && ok) mbarExpectTx(&sBar, static_cast<unsigned int>((total + numOwnT) * 48));
+        ownStartAll = __shfl_sync(0xffffffffu, src, 0);
+        ownCountAll = __shfl_sync(0xffffffffu, cnt, 0);
+        const bool ok = ownCountAll > 0 && total <= A.capOld && ownCountAll <= A.capOwn;
+        if (lane == 0 && ok) mbarExpectTx(&sBar, static_cast<unsigned int>((total + ownCountAll) * 48));
         __syncwarp();
         if (lane < 27) {
             cellBegin[lane] = incl - cnt;
+            cellT[lane] = tIdx;
             if (lane == 26) cellBegin[27] = incl;
             if (ok && cnt > 0)
-                bulkCopyG2S(cand + 6 * static_cast<size_t>(incl - cnt), rec + 6 * static_cast<size_t>(cellSrc[lane]),
+                bulkCopyG2S(cand + 6 * static_cast<size_t>(incl - cnt), rec + 6 * static_cast<size_t>(src),
                             static_cast<unsigned int>(cnt * 48), &sBar);
         } else if (lane == 27 && ok) {
             bulkCopyG2S(cand + 6 * static_cast<size_t>(total), T.rec + 6 * static_cast<size_t>(ownStartAll),
-                        static_cast<unsigned int>(numOwnT * 48), &sBar);
+                        static_cast<unsigned int>(ownCountAll * 48), &sBar);
         }
+    } else {
+        ownStartAll = cellStart[ownCell];
+        ownCountAll = cellStart[ownCell + 1] - ownStartAll;
     }
+    // trial meta of the first batch: requested now, used after the staging has landed
+    uint2 metaFirst = make_uint2(0u, 0u);
+    if (tid < min(ownCountAll, SW_MAXOWN)) metaFirst = T.meta[ownStartAll + tid];
     __syncthreads();
     const int numOld = cellBegin[27], ownBeginAll = cellBegin[0], numOwnAll = cellBegin[1] - cellBegin[0];
     if (numOwnAll == 0) return;

@@ -282,6 +282,14 @@ rp_status rp_shard_plan(int32_t n_layers_z, int32_t n_ranks, int32_t rank, int32
  *   function — tau = max over (h, k, l) in the reference's half-space scan of |sum_j exp(i k . r_j)| / V, r_j = position
  *   + orientation * focal_point (named point in the body frame; NULL or zeros = the position), k = 2 pi M^-T (h, k, l). */
 rp_status rp_nematic_order(rp_handle *h, const double primary_axis[3], double q_out[9], double *p2_out);
+/* rp_pair_density_correlation: one snapshot of PairDensityCorrelation with RadialEnumerator
+ *   (src/core/observables/correlation/PairDensityCorrelation.cpp:8-41, RadialEnumerator.cpp:12-50): every pair i < j of
+ *   focal points (position + orientation * focal_point; NULL or zeros = the position) at the reference's minimum-image
+ *   distance d <= max_r lands in bin floor(d / (max_r / n_bins)) (the last bin also takes d == max_r); counts_out[b] =
+ *   pairs in bin b (equal to the reference's counts), g_out[b] = counts * 2 / (N * expected molecules in the shell at
+ *   the packing's number density).  Either output may be NULL.  n_bins <= 4096. */
+rp_status rp_pair_density_correlation(rp_handle *h, double max_r, int32_t n_bins, const double focal_point[3],
+                                      uint64_t *counts_out, double *g_out);
 rp_status rp_smectic_order(rp_handle *h, const int32_t hkl_range[3], const double focal_point[3], double *tau_out,
                            int32_t hkl_out[3], double k_out[3]);
 

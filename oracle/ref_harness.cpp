@@ -17,6 +17,8 @@
 #include "core/Packing.h"
 #include "core/observables/NematicOrder.h"
 #include "core/observables/SmecticOrder.h"
+#include "core/observables/correlation/PairDensityCorrelation.h"
+#include "core/observables/correlation/RadialEnumerator.h"
 #include <cstdio>
 #include "core/PeriodicBoundaryConditions.h"
 #include "core/NeighbourGrid.h"
@@ -384,6 +386,31 @@ int rpr_observables(void *pp, void *tp, const int hklRange[3], double out[11], i
         for (std::size_t i = 0; i < 4; i++) out[7 + i] = sv[i];
         auto nominal = smectic.getNominalValues().front();
         std::sscanf(nominal.c_str(), "%d.%d.%d", &hklOut[0], &hklOut[1], &hklOut[2]);
+        return 0;
+    } catch (const std::exception &) {
+        return 1;
+    }
+}
+
+// One snapshot of the reference's PairDensityCorrelation with RadialEnumerator("o")
+// (src/core/observables/correlation/PairDensityCorrelation.cpp:8-41): g(r) per bin and the pair counts, read back from
+// the class's own print() (distance, value, count)
+int rpr_pair_density(void *pp, void *tp, double maxR, std::uint64_t numBins, double *gOut, double *countOut) {
+    try {
+        const Packing &packing = *static_cast<RefPacking *>(pp)->packing;
+        const ShapeTraits &traits = *static_cast<Traits *>(tp)->traits;
+        PairDensityCorrelation rho(std::make_shared<RadialEnumerator>(), maxR, numBins, true);
+        rho.addSnapshot(packing, 1, 1, traits);
+        std::ostringstream out;
+        out.precision(17);
+        rho.print(out);
+        std::istringstream in(out.str());
+        for (std::uint64_t b = 0; b < numBins; b++) {
+            double x, y, c;
+            if (!(in >> x >> y >> c)) return 2;
+            gOut[b] = y;
+            countOut[b] = c;
+        }
         return 0;
     } catch (const std::exception &) {
         return 1;

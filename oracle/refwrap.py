@@ -249,6 +249,16 @@ class RefPacking:
         q = np.array([[o[1], o[2], o[3]], [o[2], o[4], o[5]], [o[3], o[5], o[6]]])
         return {"p2": o[0], "q": q, "tau": o[7], "k": np.array(o[8:11]), "hkl": tuple(hkl)}
 
+    def pair_density(self, max_r, n_bins):
+        """(g, counts) of one PairDensityCorrelation / RadialEnumerator snapshot of the reference."""
+        g, counts = np.zeros(n_bins), np.zeros(n_bins)
+        self.lib.rpr_pair_density.restype = C.c_int
+        rc = self.lib.rpr_pair_density(self.ptr, self.traits.ptr, C.c_double(max_r),
+                                       C.c_uint64(n_bins), _dp(g), _dp(counts))
+        if rc != 0:
+            raise RuntimeError(f"rpr_pair_density failed ({rc})")
+        return g, counts
+
     def toggle_walls(self, walls):
         self.lib.rpr_toggle_walls(self.ptr, (C.c_int * 3)(*[int(w) for w in walls]))
 

@@ -119,7 +119,8 @@ SYMBOLS = ["rp_create", "rp_destroy", "rp_last_error", "rp_version", "rp_set_int
            "rp_revert_scaling", "rp_sweep", "rp_sweep_trace", "rp_toggle_overlap_counting", "rp_cached_overlaps",
            "rp_pair_test_batch", "rp_comm_unique_id", "rp_comm_init", "rp_comm_destroy", "rp_comm_stats", "rp_shard_plan",
            "rp_neighbour_stats", "rp_measure_fp64_peak", "rp_last_kernel_ms", "rp_launch_count", "rp_synchronize",
-           "rp_renormalize_orientations", "rp_toggle_walls", "rp_nematic_order", "rp_smectic_order", "rp_sim_create", "rp_sim_destroy", "rp_sim_run", "rp_sim_stats_get", "rp_sim_propose_box"]
+           "rp_renormalize_orientations", "rp_toggle_walls", "rp_nematic_order", "rp_smectic_order",
+           "rp_pair_density_correlation", "rp_sim_create", "rp_sim_destroy", "rp_sim_run", "rp_sim_stats_get", "rp_sim_propose_box"]
 
 _lib = None
 
@@ -148,6 +149,7 @@ def load():
     lib.rp_toggle_walls.argtypes = [H, C.POINTER(C.c_int32)]
     lib.rp_nematic_order.argtypes = [H, dp, dp, dp]
     lib.rp_smectic_order.argtypes = [H, C.POINTER(C.c_int32), dp, dp, C.POINTER(C.c_int32), dp]
+    lib.rp_pair_density_correlation.argtypes = [H, C.c_double, C.c_int32, dp, C.c_void_p, dp]
     lib.rp_renormalize_orientations.argtypes = [H, C.c_int, C.POINTER(C.c_uint64)]
     lib.rp_sim_create.argtypes = [H, C.POINTER(SimConfig), C.POINTER(H)]
     lib.rp_sim_destroy.argtypes = [H]
@@ -380,6 +382,14 @@ class Device:
         tau, hkl, k = C.c_double(), (C.c_int32 * 3)(), np.empty(3)
         self._check(self.lib.rp_smectic_order(self.h, rng, dptr(focal), C.byref(tau), hkl, dptr(k)))
         return tau.value, tuple(hkl), k
+
+    def pair_density_correlation(self, max_r, n_bins, focal_point=None):
+        """(counts, g) — one snapshot of PairDensityCorrelation / RadialEnumerator of the resident packing."""
+        focal = np.ascontiguousarray(focal_point if focal_point is not None else (0, 0, 0), dtype=np.float64)
+        counts, g = np.zeros(n_bins, dtype=np.uint64), np.zeros(n_bins)
+        self._check(self.lib.rp_pair_density_correlation(self.h, C.c_double(max_r), C.c_int32(n_bins), dptr(focal),
+                                                         counts.ctypes.data_as(C.c_void_p), dptr(g)))
+        return counts, g
 
     def toggle_walls(self, walls):
         self._check(self.lib.rp_toggle_walls(self.h, (C.c_int32 * 3)(*[int(w) for w in walls])))

@@ -391,6 +391,18 @@ rp_status rp_smectic_order(rp_handle *h, const int32_t hkl_range[3], const doubl
     RP_API_END(h)
 }
 
+rp_status rp_pair_density_correlation(rp_handle *h, double max_r, int32_t n_bins, const double focal_point[3],
+                                      uint64_t *counts_out, double *g_out) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(h->n > 0, "packing must be set");
+    // HistogramBuilder::HistogramBuilder (core/observables/HistogramBuilder.tpp): max > min, numBins > 0
+    RP_EXPECT(max_r > 0, "maxR > 0");
+    RP_EXPECT(n_bins > 0 && n_bins <= 4096, "0 < numBins <= 4096");
+    static_assert(sizeof(uint64_t) == sizeof(unsigned long long), "uint64_t");
+    pairDensityCorrelation(h, max_r, n_bins, focal_point, reinterpret_cast<unsigned long long *>(counts_out), g_out);
+    RP_API_END(h)
+}
+
 rp_status rp_toggle_walls(rp_handle *h, const int32_t walls[3]) {
     RP_API_BEGIN(h)
     RP_EXPECT(walls != nullptr, "walls != NULL");

@@ -232,6 +232,8 @@ void fp64Peak(Handle *h, double *dfmaGflops, double *dmulDaddGflops);
 // ---- rp_observe.cu ----
 void nematicOrder(Handle *h, const double axis[3], double qOut[9], double *p2Out);
 void smecticOrder(Handle *h, const int range[3], const double focal[3], double *tauAbs, int hklOut[3], double kOut[3]);
+void pairDensityCorrelation(Handle *h, double maxR, int numBins, const double focal[3], unsigned long long *countsOut,
+                            double *gOut);
 // ---- rp_sweep.cu ----
 void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out);
 void cullThresholds(const Handle *h, const double relCell[3], float *thr2, float *half);

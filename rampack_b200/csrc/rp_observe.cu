@@ -2,6 +2,8 @@
 // hundred cycles, evaluated where the packing lives instead of downloading 96 bytes per particle.
 //   rp_nematic_order  NematicOrder::calculate      (core/observables/NematicOrder.cpp:9-28, eigenvalues :30-55)
 //   rp_smectic_order  SmecticOrder::calculate      (core/observables/SmecticOrder.cpp:14-62), constant shape function
+//   rp_pair_density_correlation  PairDensityCorrelation::addSnapshot with RadialEnumerator
+//                     (core/observables/correlation/PairDensityCorrelation.cpp:8-41, RadialEnumerator.cpp:12-50)
 // Sums are formed per block in a fixed tree order and finished on the host in block order: results do not depend on
 // scheduling.  The reference adds particle by particle; agreement is to rounding (tests: 1e-12).
 #include "rp_internal.cuh"
@@ -166,6 +168,137 @@ void smecticOrder(Handle *h, const int range[3], const double focal[3], double *
     for (int i = 0; i < 3; i++) {
         if (hklOut) hklOut[i] = bestV >= 0 ? hkl[3 * bestV + i] : 0;
         if (kOut) kOut[i] = bestV >= 0 ? kvecs[3 * bestV + i] : 0;
+    }
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------
+// g(r): the reference visits ALL pairs i < j (RadialEnumerator.cpp:21-31) — so does this kernel, tile by tile, but a
+// pair reaches the reference's FP64 arithmetic (getTranslation, norm, bin = floor(d / step)) only if a conservative
+// FP32 minimum-image distance in relative coordinates says it may lie inside maxR.  Counts are integers: equal to the
+// reference's bin for bin.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int PD_TILE = 256, PD_MAXBINS = 4096;
+
+struct PdArgs {
+    float m[9];            // box matrix in FP32 (row-major)
+    float thr2;            // (maxR + FP32 error bound)^2
+    double maxR, step;
+    int numBins;
+    V3 focal;
+    int useFocal;
+};
+
+__device__ __forceinline__ V3 focalPoint(int p, size_t cap, const double *__restrict__ pos,
+                                         const double *__restrict__ orient, const PdArgs &A)
+{
+    V3 r = v3(pos[p], pos[cap + p], pos[2 * cap + p]);
+    if (A.useFocal) {
+        M33 o;
+        for (int q = 0; q < 9; q++) o.a[q] = orient[q * cap + p];
+        r = r + mul(o, A.focal);
+    }
+    return r;
+}
+
+__global__ void __launch_bounds__(PD_TILE) k_pair_density(int n, size_t cap, const double *__restrict__ pos,
+                                                          const double *__restrict__ orient, Box box, PdArgs A,
+                                                          unsigned long long *__restrict__ hist)
+{
+    if (blockIdx.x < blockIdx.y) return;                   // tile pairs (I <= J) only
+    __shared__ double sx[PD_TILE], sy[PD_TILE], sz[PD_TILE];
+    __shared__ float4 sRel[PD_TILE];
+    __shared__ unsigned int sHist[PD_MAXBINS];
+    const int t = threadIdx.x;
+    for (int b = t; b < A.numBins; b += PD_TILE) sHist[b] = 0u;
+    const int i = blockIdx.y * PD_TILE + t, jLoad = blockIdx.x * PD_TILE + t;
+    V3 pi = v3(0, 0, 0);
+    float rix = 0.f, riy = 0.f, riz = 0.f;
+    if (i < n) {
+        pi = focalPoint(i, cap, pos, orient, A);
+        const V3 r = absToRel(box, pi);
+        rix = static_cast<float>(r.x); riy = static_cast<float>(r.y); riz = static_cast<float>(r.z);
+    }
+    if (jLoad < n) {
+        const V3 pj = focalPoint(jLoad, cap, pos, orient, A);
+        const V3 r = absToRel(box, pj);
+        sx[t] = pj.x; sy[t] = pj.y; sz[t] = pj.z;
+        sRel[t] = make_float4(static_cast<float>(r.x), static_cast<float>(r.y), static_cast<float>(r.z), 0.f);
+    } else {
+        sRel[t] = make_float4(1e18f, 0.f, 0.f, 0.f);
+    }
+    __syncthreads();
+    const int jBase = blockIdx.x * PD_TILE;
+    if (i < n) {
+        #pragma unroll 4
+        for (int jj = 0; jj < PD_TILE; jj++) {
+            const float4 rj = sRel[jj];
+            float dx = rj.x - rix, dy = rj.y - riy, dz = rj.z - riz;
+            dx -= rintf(dx); dy -= rintf(dy); dz -= rintf(dz);
+            const float ax = fmaf(A.m[2], dz, fmaf(A.m[1], dy, A.m[0] * dx));
+            const float ay = fmaf(A.m[5], dz, fmaf(A.m[4], dy, A.m[3] * dx));
+            const float az = fmaf(A.m[8], dz, fmaf(A.m[7], dy, A.m[6] * dx));
+            const float d2 = fmaf(az, az, fmaf(ay, ay, ax * ax));
+            const int j = jBase + jj;
+            if (d2 < A.thr2 && j > i && j < n) {
+                // RadialEnumerator.cpp:24-29, PairDensityCorrelation.cpp:29-40, Histogram.tpp:61-69
+                const V3 pj = v3(sx[jj], sy[jj], sz[jj]);
+                const V3 p2 = pj + pbcTranslation(box, pi, pj);
+                const double distance = sqrt(norm2(p2 - pi));
+                if (!(distance > A.maxR)) {
+                    long long bin = static_cast<long long>(floor(distance / A.step));
+                    if (bin >= A.numBins) bin = A.numBins - 1;
+                    atomicAdd(&sHist[bin], 1u);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    for (int b = t; b < A.numBins; b += PD_TILE)
+        if (sHist[b]) atomicAdd(&hist[b], static_cast<unsigned long long>(sHist[b]));
+}
+
+void pairDensityCorrelation(Handle *h, double maxR, int numBins, const double focal[3], unsigned long long *countsOut,
+                            double *gOut) {
+    const int n = static_cast<int>(h->n);
+    ensureCellEnergyBuffer(h, static_cast<size_t>(numBins));
+    unsigned long long *dHist = reinterpret_cast<unsigned long long *>(h->dCellEnergy);
+    RP_CUDA(cudaMemsetAsync(dHist, 0, sizeof(unsigned long long) * numBins, h->stream));
+    PdArgs A;
+    double len = 0;
+    for (int q = 0; q < 9; q++) { A.m[q] = static_cast<float>(h->box.m.a[q]); len += std::abs(h->box.m.a[q]); }
+    // FP32 error of the minimum-image distance: relative coordinates carry 2^-24, the matrix product multiplies by at
+    // most the sum of the |entries|; ten times that, plus the same relative error on maxR
+    const double thr = maxR * (1 + 1e-5) + 1e-5 * len;
+    A.thr2 = std::nextafterf(static_cast<float>(thr * thr), INFINITY);
+    A.maxR = maxR;
+    A.step = (maxR - 0.0) / static_cast<double>(numBins);            // Histogram.tpp:91
+    A.numBins = numBins;
+    A.useFocal = focal && (focal[0] != 0 || focal[1] != 0 || focal[2] != 0);
+    A.focal = A.useFocal ? v3(focal[0], focal[1], focal[2]) : v3(0, 0, 0);
+    const int tiles = (n + PD_TILE - 1) / PD_TILE;
+    k_pair_density<<<dim3(tiles, tiles), PD_TILE, 0, h->stream>>>(n, h->cap, h->pos, h->orient, h->box, A, dHist);
+    h->launches++;
+    std::vector<unsigned long long> counts(numBins);
+    RP_CUDA(cudaMemcpyAsync(counts.data(), dHist, sizeof(unsigned long long) * numBins, cudaMemcpyDeviceToHost,
+                            h->stream));
+    RP_CUDA(cudaStreamSynchronize(h->stream));
+    RP_CUDA(cudaGetLastError());
+    // PairDensityCorrelation.cpp:12-16: bin *= 2 / (expected molecules in the shell) / N, expected from the number
+    // density (RadialEnumerator.cpp:34-50, in the reference's operation order)
+    const double numberDensity = static_cast<double>(h->n) / std::abs(boxVolume(h->box));
+    auto inBall = [numberDensity](double r) { return 4. / 3 * M_PI * r * r * r * numberDensity; };
+    for (int b = 0; b < numBins; b++) {
+        if (countsOut) countsOut[b] = counts[b];
+        if (gOut) {
+            // Histogram::getBinDividers (Histogram.tpp:141-151) with min = 0
+            const double nb = static_cast<double>(numBins);
+            const double lo = 0.0 * ((nb - b) / nb) + maxR * (static_cast<double>(b) / nb);
+            const double hi = 0.0 * ((nb - (b + 1)) / nb) + maxR * (static_cast<double>(b + 1) / nb);
+            double factor = inBall(hi) - inBall(lo);
+            factor = 2. / factor / static_cast<double>(h->n);
+            gOut[b] = static_cast<double>(counts[b]) * factor;
+        }
     }
 }
 

@@ -71,3 +71,45 @@ def test_observable_preconditions(device):
     device.upload(box, shapes)
     with pytest.raises(rp.PreconditionError):
         device.smectic_order((0, 0, 0))
+
+
+@pytest.mark.parametrize("name,max_r,n_bins", [("lattice", 4.0, 40), ("smectic", 6.0, 64),
+                                               ("isotropic_triclinic", 9.0, 90), ("aligned_random_positions", 3.0, 7)])
+def test_pair_density_correlation(device, name, max_r, n_bins):
+    """rp_pair_density_correlation against one snapshot of the reference's PairDensityCorrelation + RadialEnumerator
+    (PairDensityCorrelation.cpp:8-41, RadialEnumerator.cpp:12-50).  Pair counts per bin are integers: equal.  The
+    lattice puts thousands of pairs on bin boundaries (spacing 1.2 = 12 bins of 0.1): which side they fall on is decided
+    by the last bit of sqrt and of the division by the bin width — the device follows the reference's arithmetic."""
+    if name == "lattice":
+        box, shapes = H.sc_lattice((8, 8, 4))
+    else:
+        box, shapes = states()[name]
+    desc = H.desc_sc()
+    device.toggle_overlap_counting(False)
+    device.set_interaction(desc)
+    device.upload(box, shapes)
+    ref = R.RefPacking(R.RefTraits(desc), box, shapes)
+    want_g, want_counts = ref.pair_density(max_r, n_bins)
+    counts, g = device.pair_density_correlation(max_r, n_bins)
+    assert want_counts.sum() > 1000
+    assert np.array_equal(counts, want_counts.astype(np.uint64))
+    assert np.allclose(g, want_g, rtol=1e-12, atol=0)
+
+
+def test_pair_density_correlation_at_scale(device):
+    """N = 108 000: the reference's all-pairs loop would take minutes; hold the device to a cell-list count in numpy of
+    the pairs inside max_r and to the g -> 1 limit of an ideal gas of points."""
+    rng = np.random.default_rng(8)
+    box = np.diag([90.0, 80.0, 70.0])
+    n = 108_000
+    shapes = np.zeros((n, 12))
+    shapes[:, :3] = rng.uniform(0, 1, size=(n, 3)) * np.diag(box)
+    shapes[:, 3:] = np.eye(3).ravel()
+    device.toggle_overlap_counting(False)
+    device.set_interaction(H.desc_sphere(0.01))
+    device.upload(box, shapes)
+    counts, g = device.pair_density_correlation(5.0, 25)
+    from scipy.spatial import cKDTree
+    tree = cKDTree(shapes[:, :3], boxsize=np.diag(box))
+    assert int(counts.sum()) == (tree.count_neighbors(tree, 5.0) - n) // 2
+    assert np.all(np.abs(g[5:] - 1.0) < 0.05)

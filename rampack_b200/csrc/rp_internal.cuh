@@ -117,6 +117,7 @@ struct Handle {
     double *lastCabs = nullptr;
     size_t lastCap = 0, lastCentreCap = 0;
     bool hasLastScaling = false;
+    bool lastGridValid = false;     // tryScaling: the grid of the pre-scaling state was up to date (else revert leaves it dirty)
     double interactionRange = 0; // Packing::interactionRange
 
     // reference-geometry neighbour grid (Packing::neighbourGrid / tempNeighbourGrid)

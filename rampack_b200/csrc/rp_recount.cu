@@ -676,8 +676,11 @@ double tryScaling(Handle *h, const Box &newBox) {
         RP_CUDA(cudaMemcpyAsync(h->lastCabs, h->cabs, 3 * h->centreCap * sizeof(double), cudaMemcpyDeviceToDevice,
                                 st));
     }
-    double initialEnergy = totalEnergy(h);     // ensures the current grid is built
-    ensureGrid(h);
+    // The grid of the OLD state is only worth building if somebody reads it: the energy of a soft interaction now, or
+    // whoever comes after a revert.  After a sweep it is stale and the next sweep would discard it unread, so a hard-
+    // only run leaves it stale (revertScaling then marks the restored state "grid dirty": built lazily on first use).
+    double initialEnergy = totalEnergy(h);     // soft interactions: builds the current grid
+    h->lastGridValid = !h->gridDirty;
     h->lastScalingNumOverlaps = h->numOverlaps;
 
     h->box = newBox;
@@ -725,7 +728,7 @@ void revertScaling(Handle *h) {
     h->box = h->lastBox;
     std::swap(h->grid, h->tempGrid);
     std::swap(h->hasGrid, h->tempHasGrid);
-    h->gridDirty = false;      // the swapped-back grid describes the restored state
+    h->gridDirty = !h->lastGridValid;      // the swapped-back grid describes the restored state if it was built
     h->numOverlaps = h->lastScalingNumOverlaps;
     h->hasLastScaling = false;
 }

@@ -146,7 +146,7 @@ __device__ __forceinline__ bool segmentCullPass(const double *__restrict__ c, co
     const float cc = fmaf(h1z, dz, fmaf(h1y, dy, h1x * dx));
     const float f = fmaf(h2z, dz, fmaf(h2y, dy, h2x * dx));
     const float denom = fmaf(a, a, -b * b);
-    const float inva = __fdividef(1.0f, a);
+    const float inva = a > 0.f ? __fdividef(1.0f, a) : 0.f;      // length 0: both parameters stay 0
     float s = __fdividef(fmaf(b, f, -cc * a), fmaxf(denom, 1e-20f));    // nearly parallel: the SIGN still decides the end
     s = fminf(fmaxf(s, -1.0f), 1.0f);
     const float t0 = fmaf(b, s, f) * inva;

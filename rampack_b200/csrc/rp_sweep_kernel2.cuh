@@ -116,7 +116,8 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
         }
     }
 
-    const float invHalfF = HARD == RP_HARD_SPHEROCYLINDER ? __fdividef(1.0f, A.cullHalf) : 0.f;
+    // (a spherocylinder of length 0 is admissible, SpherocylinderTraits.cpp:15: its unit axis is irrelevant, not NaN)
+    const float invHalfF = (HARD == RP_HARD_SPHEROCYLINDER && A.cullHalf > 0.f) ? __fdividef(1.0f, A.cullHalf) : 0.f;
     const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION);
     const bool translated = (A.kind == RP_MOVE_TRANSLATION || A.kind == RP_MOVE_ROTOTRANSLATION);
 

@@ -97,6 +97,14 @@ def test_replay_spherocylinders_fast_path(device):
     run_replay(device, H.desc_sc(), box, shapes, rp.RP_MOVE_ROTOTRANSLATION, 0.3, 0.2, 4)
 
 
+def test_replay_spherocylinders_of_length_zero(device):
+    """SpherocylinderTraits admits length == 0 (SpherocylinderTraits.cpp:15): the FP32 culls must not turn the missing
+    axis into NaN distances (a NaN compares false and the pair would be dropped)."""
+    box, shapes = H.sc_lattice((10, 10, 10), cell=(1.15, 1.15, 1.15))
+    run_replay(device, H.desc_sc(l=0.0), box, shapes, rp.RP_MOVE_ROTOTRANSLATION, 0.3, 0.2, 3)
+    assert device.count_total_overlaps(False) == 0
+
+
 def test_replay_spherocylinders_generic_kernel(device, monkeypatch):
     monkeypatch.setenv("RP_SWEEP_GENERIC", "1")
     box, shapes = H.sc_lattice((12, 12, 4))

@@ -1,7 +1,7 @@
 #!/bin/bash
 # kernel parity after a k_sweep change (replay of every decision, cull-disabled bit identity, walls), then the bench
 mkdir -p gpurun_out
-timeout 1200 python -m pytest tests -m gpu -x -q -k "sweep_replay or cull_never or test_gpu_walls or test_gpu_parity or test_gpu_errors or test_gpu_observables or step_sizes or hs_degenerate" > gpurun_out/pytest_kernel.log 2>&1; echo "pytest(kernel) exit $?"
+timeout 1200 python -m pytest tests -m gpu -x -q -k "sweep_replay or cull_never or test_gpu_walls or test_gpu_parity or test_gpu_errors or test_gpu_observables" > gpurun_out/pytest_kernel.log 2>&1; echo "pytest(kernel) exit $?"
 tail -4 gpurun_out/pytest_kernel.log
 timeout 900 python bench.py --steps 20 --warmup 5 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit $?"
 python - <<'PY'

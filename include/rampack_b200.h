@@ -287,7 +287,9 @@ rp_status rp_nematic_order(rp_handle *h, const double primary_axis[3], double q_
  *   focal points (position + orientation * focal_point; NULL or zeros = the position) at the reference's minimum-image
  *   distance d <= max_r lands in bin floor(d / (max_r / n_bins)) (the last bin also takes d == max_r); counts_out[b] =
  *   pairs in bin b (equal to the reference's counts), g_out[b] = counts * 2 / (N * expected molecules in the shell at
- *   the packing's number density).  Either output may be NULL.  n_bins <= 4096. */
+ *   the packing's number density).  Either output may be NULL.  n_bins <= 4096; max_r <= half of the smallest box
+ *   height (RP_ERR_PRECONDITION otherwise: beyond it the reference's relative-coordinate minimum image is not the
+ *   nearest image and the caller keeps the host path). */
 rp_status rp_pair_density_correlation(rp_handle *h, double max_r, int32_t n_bins, const double focal_point[3],
                                       uint64_t *counts_out, double *g_out);
 rp_status rp_smectic_order(rp_handle *h, const int32_t hkl_range[3], const double focal_point[3], double *tau_out,

@@ -398,6 +398,15 @@ rp_status rp_pair_density_correlation(rp_handle *h, double max_r, int32_t n_bins
     // HistogramBuilder::HistogramBuilder (core/observables/HistogramBuilder.tpp): max > min, numBins > 0
     RP_EXPECT(max_r > 0, "maxR > 0");
     RP_EXPECT(n_bins > 0 && n_bins <= 4096, "0 < numBins <= 4096");
+    {
+        // Not a precondition of the reference, which applies its relative-coordinate minimum image at any distance;
+        // beyond half a box height that image is no longer the nearest one and, at a relative separation of exactly
+        // 1/2, depends on the last bit — the FP32 cull of the device kernel only promises the reference's counts below.
+        double heights[3];
+        boxHeights(h->box, heights);
+        const double minHeight = std::min(heights[0], std::min(heights[1], heights[2]));
+        RP_EXPECT(max_r <= 0.5 * minHeight * (1 - 1e-6), "maxR <= half of the smallest box height");
+    }
     static_assert(sizeof(uint64_t) == sizeof(unsigned long long), "uint64_t");
     pairDensityCorrelation(h, max_r, n_bins, focal_point, reinterpret_cast<unsigned long long *>(counts_out), g_out);
     RP_API_END(h)

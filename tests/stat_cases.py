@@ -118,6 +118,8 @@ def pair_density_in_shell(box, shapes, r_lo, r_hi):
         d -= np.round(d)
         r2 = ((d @ box.T) ** 2).sum(axis=2)
         count += int(((r2 >= r_lo * r_lo) & (r2 < r_hi * r_hi)).sum())
+    if r_lo <= 0:
+        count -= n          # the i == j terms (PairDensityCorrelation::consumePair skips them)
     shell = 4.0 / 3.0 * math.pi * (r_hi ** 3 - r_lo ** 3)
     rho = n / abs(np.linalg.det(box))
     return count / (n * rho * shell)

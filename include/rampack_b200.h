@@ -195,6 +195,8 @@ rp_status rp_set_interaction(rp_handle *h, const rp_interaction_desc *desc);
 rp_status rp_upload(rp_handle *h, const double box[9], const double *shapes /* N x 12 */, uint64_t n);
 rp_status rp_download(rp_handle *h, double box_out[9], double *shapes_out /* N x 12 */, uint64_t n);
 rp_status rp_size(const rp_handle *h, uint64_t *n_out);
+/* shapes [first, first + count) only — Packing::operator[] / front / back after a few explicit moves (Packing.h:193-215) */
+rp_status rp_download_range(rp_handle *h, uint64_t first, uint64_t count, double *shapes_out /* count x 12 */);
 
 /* ---- neighbour grid: Packing::rebuildNeighbourGrid (Packing.cpp:858-929), NeighbourGrid::positionToCellNo ---- */
 rp_status rp_rebuild_grid(rp_handle *h);
@@ -205,6 +207,10 @@ rp_status rp_cell_numbers(rp_handle *h, uint64_t *cell_no_out /* num_centres */)
 /* ---- full-system recount: Packing::countTotalOverlaps / getTotalEnergy (Packing.cpp:519-559, 690-709) ---- */
 rp_status rp_count_total_overlaps(rp_handle *h, int early_exit, uint64_t *count_out);
 rp_status rp_total_energy(rp_handle *h, double *energy_out);
+/* Packing::countWallOverlaps (Packing.cpp:561-580); early_exit != 0: 1 when any wall overlap exists */
+rp_status rp_count_wall_overlaps(rp_handle *h, int early_exit, uint64_t *count_out);
+/* Packing::getParticleEnergyFluctuations (Packing.cpp:841-856): sqrt(var(E_i)) / 2 over the per-particle energies */
+rp_status rp_particle_energy_fluctuations(rp_handle *h, double *fluctuations_out);
 
 /* ---- explicit moves (compatibility path): Packing::try* / accept* (Packing.cpp:84-164, 234-302) ---- */
 rp_status rp_try_move(rp_handle *h, const rp_move *move, double *dE_out);
@@ -240,7 +246,8 @@ rp_status rp_sweep_trace(rp_handle *h, rp_trial_trace *out, uint64_t n);
 
 /* ---- Packing::renormalizeOrientations / fixRotationMatrix (Packing.cpp:1178-1219), called by
  * Simulation::fixRotationMatrices every `rotation_matrix_fix_every` cycles.  allow_overlaps != 0 is the counting-mode
- * variant.  rejected_out: fixes not applied because they would create an overlap (all-or-nothing on the device). ---- */
+ * variant.  rejected_out: fixes not applied because they would create an overlap (per particle: every particle that
+ * takes part in an overlap after the bulk fix gets its old matrix back; the check is repeated). ---- */
 rp_status rp_renormalize_orientations(rp_handle *h, int allow_overlaps, uint64_t *rejected_out);
 
 /* ---- counting mode + walls: Packing::toggleOverlapCounting / getCachedNumberOfOverlaps (Packing.cpp:1049-1060) ---- */
@@ -339,6 +346,9 @@ typedef struct rp_sim_stats {
     double scaler_step;
     double box[9];
     double sweep_kernel_ms, sweep_grid_ms, scaling_ms;   /* device time inside the kernels, accumulated */
+    uint64_t cells_skipped;                   /* active cells a sweep left out because the shared-memory staging capacity
+                                                 (sized from the previous sweeps, no host round trip) was too small; the
+                                                 capacity grows at once, the moves of such a cell are simply not attempted */
 } rp_sim_stats;
 
 typedef struct rp_sim rp_sim;

@@ -98,7 +98,7 @@ class SimStats(C.Structure):
                 ("translation_step", C.c_double * RP_SIM_MAX_SAMPLERS),
                 ("rotation_step", C.c_double * RP_SIM_MAX_SAMPLERS), ("scaler_step", C.c_double),
                 ("box", C.c_double * 9), ("sweep_kernel_ms", C.c_double), ("sweep_grid_ms", C.c_double),
-                ("scaling_ms", C.c_double)]
+                ("scaling_ms", C.c_double), ("cells_skipped", C.c_uint64)]
 
 
 # rp_pair as a numpy structured dtype (same layout as the C struct: all members are 8 bytes wide)
@@ -120,7 +120,8 @@ SYMBOLS = ["rp_create", "rp_destroy", "rp_last_error", "rp_version", "rp_set_int
            "rp_pair_test_batch", "rp_comm_unique_id", "rp_comm_init", "rp_comm_destroy", "rp_comm_stats", "rp_shard_plan",
            "rp_neighbour_stats", "rp_measure_fp64_peak", "rp_last_kernel_ms", "rp_launch_count", "rp_synchronize",
            "rp_renormalize_orientations", "rp_toggle_walls", "rp_nematic_order", "rp_smectic_order",
-           "rp_pair_density_correlation", "rp_sim_create", "rp_sim_destroy", "rp_sim_run", "rp_sim_stats_get", "rp_sim_propose_box"]
+           "rp_pair_density_correlation", "rp_sim_create", "rp_sim_destroy", "rp_sim_run", "rp_sim_stats_get", "rp_sim_propose_box",
+           "rp_download_range", "rp_count_wall_overlaps", "rp_particle_energy_fluctuations"]
 
 _lib = None
 
@@ -161,6 +162,9 @@ def load():
     lib.rp_upload.argtypes = [H, dp, dp, C.c_uint64]
     lib.rp_download.argtypes = [H, dp, dp, C.c_uint64]
     lib.rp_size.argtypes = [H, C.POINTER(C.c_uint64)]
+    lib.rp_download_range.argtypes = [H, C.c_uint64, C.c_uint64, dp]
+    lib.rp_count_wall_overlaps.argtypes = [H, C.c_int, C.POINTER(C.c_uint64)]
+    lib.rp_particle_energy_fluctuations.argtypes = [H, dp]
     lib.rp_rebuild_grid.argtypes = [H]
     lib.rp_grid_info_get.argtypes = [H, C.POINTER(GridInfo)]
     lib.rp_cell_numbers.argtypes = [H, C.POINTER(C.c_uint64)]
@@ -281,6 +285,21 @@ class Device:
         shapes = out if out is not None else np.empty((self.n, 12))
         self._check(self.lib.rp_download(self.h, dptr(box), dptr(shapes), self.n))
         return box.reshape(3, 3), shapes
+
+    def download_range(self, first, count):
+        out = np.empty((count, 12), dtype=np.float64)
+        self._check(self.lib.rp_download_range(self.h, first, count, out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out
+
+    def count_wall_overlaps(self, early_exit=False):
+        c = C.c_uint64(0)
+        self._check(self.lib.rp_count_wall_overlaps(self.h, 1 if early_exit else 0, C.byref(c)))
+        return int(c.value)
+
+    def particle_energy_fluctuations(self):
+        v = C.c_double(0)
+        self._check(self.lib.rp_particle_energy_fluctuations(self.h, C.byref(v)))
+        return float(v.value)
 
     def rebuild_grid(self):
         self._check(self.lib.rp_rebuild_grid(self.h))

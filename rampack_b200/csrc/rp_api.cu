@@ -184,11 +184,15 @@ __global__ void k_fix_orientations(int n, size_t cap, double *__restrict__ orien
     }
     for (int q = 0; q < 9; q++) orient[q * cap + p] = R.a[q];
 }
+// withdraws the fix of every particle (flags == nullptr) or of the flagged ones; counts the withdrawals
 __global__ void k_restore_orientations(int n, size_t cap, double *__restrict__ orient,
-                                       const double *__restrict__ backup) {
+                                       const double *__restrict__ backup, const unsigned char *__restrict__ flags,
+                                       unsigned char *__restrict__ withdrawn, unsigned long long *__restrict__ count) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
+    if (flags && (!flags[p] || withdrawn[p])) return;
     for (int q = 0; q < 9; q++) orient[q * cap + p] = backup[9 * static_cast<size_t>(p) + q];
+    if (flags) { withdrawn[p] = 1; atomicAdd(count, 1ull); }
 }
 
 static void setupForInteraction(Handle *h) {
@@ -256,6 +260,10 @@ rp_status rp_create(const rp_config *config, rp_handle **out) {
         RP_CUDA(cudaMalloc(&h->dInter, sizeof(Inter)));
         RP_CUDA(cudaMalloc(&h->dCounters, 32 * sizeof(unsigned long long)));
         RP_CUDA(cudaMalloc(&h->dFlags, 16 * sizeof(int)));
+        RP_CUDA(cudaMemset(h->dFlags, 0, 16 * sizeof(int)));
+        RP_CUDA(cudaMallocHost(&h->sweepMaxPinned, 4 * 4 * sizeof(int)));
+        for (auto &ev : h->sweepMaxEvent) RP_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        for (auto &t : h->timing) for (auto &ev : t.e) RP_CUDA(cudaEventCreate(&ev));
         RP_CUDA(cudaMalloc(&h->dMoveOut, 8 * sizeof(double)));
         RP_CUDA(cudaMalloc(&h->tmpState, (12 + 6 * RP_MAX_CENTRES) * sizeof(double)));
         for (auto &ev : h->ev) RP_CUDA(cudaEventCreate(&ev));
@@ -275,7 +283,7 @@ void rp_destroy(rp_handle *h) {
     for (void *p : {(void *) h->dInter, (void *) h->pos, (void *) h->orient, (void *) h->crel, (void *) h->cabs,
                     (void *) h->lastPos, (void *) h->lastCabs, (void *) h->tmpState, (void *) h->dCounters,
                     (void *) h->dFlags, (void *) h->dCellEnergy, (void *) h->dMoveOut, h->dStage,
-                    (void *) h->sweepMoved, (void *) h->trialRec, (void *) h->trialOrient, h->trialMeta,
+                    (void *) h->sweepMoved, (void *) h->trialRec, (void *) h->trialOrient, h->trialMeta, h->trialRec32,
                     (void *) h->genRec, (void *) h->genTrialRec, (void *) h->genTrialCrel, (void *) h->genTrialU})
         if (p) cudaFree(p);
     shardDestroy(h);
@@ -286,6 +294,9 @@ void rp_destroy(rp_handle *h) {
     freeGrid(h->tempGrid);
     freeGrid(h->sgrid);
     for (auto &ev : h->ev) if (ev) cudaEventDestroy(ev);
+    for (auto &ev : h->sweepMaxEvent) if (ev) cudaEventDestroy(ev);
+    for (auto &t : h->timing) for (auto &ev : t.e) if (ev) cudaEventDestroy(ev);
+    if (h->sweepMaxPinned) cudaFreeHost(h->sweepMaxPinned);
     if (h->ownStream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -370,6 +381,38 @@ rp_status rp_download(rp_handle *h, double box_out[9], double *shapes_out, uint6
     RP_API_END(h)
 }
 
+rp_status rp_download_range(rp_handle *h, uint64_t first, uint64_t count, double *shapes_out) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(first <= h->n && count <= h->n - first, "first + count <= size()");
+    RP_EXPECT(shapes_out != nullptr || count == 0, "shapes_out != NULL");
+    if (count > 0) {
+        ensureStage(h, count * 12 * sizeof(double));
+        int total = static_cast<int>(count * 12);
+        k_pack_shapes<<<(total + 255) / 256, 256, 0, h->stream>>>(static_cast<int>(count), h->cap, h->pos + first,
+                                                                  h->orient + first, static_cast<double *>(h->dStage));
+        h->launches++;
+        RP_CUDA(cudaMemcpyAsync(shapes_out, h->dStage, count * 12 * sizeof(double), cudaMemcpyDeviceToHost,
+                                h->stream));
+        RP_CUDA(cudaStreamSynchronize(h->stream));
+        RP_CUDA(cudaGetLastError());
+    }
+    RP_API_END(h)
+}
+
+rp_status rp_count_wall_overlaps(rp_handle *h, int early_exit, uint64_t *count_out) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(h->hasInteraction && count_out != nullptr, "interaction must be set, count_out != NULL");
+    *count_out = h->n > 0 ? countWallOverlaps(h, early_exit != 0) : 0;
+    RP_API_END(h)
+}
+
+rp_status rp_particle_energy_fluctuations(rp_handle *h, double *fluctuations_out) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(h->hasInteraction && h->n > 0 && fluctuations_out != nullptr, "packing and interaction must be set");
+    *fluctuations_out = particleEnergyFluctuations(h);
+    RP_API_END(h)
+}
+
 rp_status rp_nematic_order(rp_handle *h, const double primary_axis[3], double q_out[9], double *p2_out) {
     RP_API_BEGIN(h)
     RP_EXPECT(h->n > 0 && primary_axis != nullptr, "packing must be set, primary_axis != NULL");
@@ -438,16 +481,45 @@ rp_status rp_renormalize_orientations(rp_handle *h, int allow_overlaps, uint64_t
         h->gridDirty = true;
         h->hasTrial = false;
         // the reference walks the particles one by one and rejects a fix that creates an overlap
-        // (core/Packing.cpp:1195-1211).  Here all fixes are applied at once and checked by one recount; if ANY overlap
-        // appears every fix is withdrawn and all N are reported rejected (the fixes are O(1e-15): never observed).
+        // (core/Packing.cpp:1195-1211).  Here all fixes are applied at once and checked by one early-exit recount (the
+        // fixes are O(1e-15): it practically always passes).  If it does not, the fix of every particle that takes
+        // part in an overlap is withdrawn — per-particle rejection like the reference's, except that of two
+        // neighbours whose fixes only collide with each other both are rejected where the reference would keep the
+        // first — and the check is repeated; after three rounds every fix is withdrawn.
+        unsigned long long rejected = 0;
         if (h->inter.hard != RP_HARD_NONE && countTotalOverlaps(h, true) > 0) {
-            k_restore_orientations<<<(n + 255) / 256, 256, 0, h->stream>>>(n, h->cap, h->orient, backup);
-            h->launches++;
-            initCentres(h);
-            recalcAbsoluteCentres(h);
-            h->gridDirty = true;
-            if (rejected_out) *rejected_out = h->n;
+            unsigned char *flags = nullptr, *withdrawn = nullptr;
+            RP_CUDA(cudaMalloc(&flags, 2 * h->n));
+            withdrawn = flags + h->n;
+            RP_CUDA(cudaMemsetAsync(withdrawn, 0, h->n, h->stream));
+            bool clean = false;
+            for (int round = 0; round < 3 && !clean; round++) {
+                particleScan(h, true, false, flags, nullptr);
+                RP_CUDA(cudaMemsetAsync(h->dCounters + 8, 0, sizeof(unsigned long long), h->stream));
+                k_restore_orientations<<<(n + 255) / 256, 256, 0, h->stream>>>(n, h->cap, h->orient, backup, flags,
+                                                                              withdrawn, h->dCounters + 8);
+                h->launches++;
+                unsigned long long now = 0;
+                RP_CUDA(cudaMemcpyAsync(&now, h->dCounters + 8, sizeof(now), cudaMemcpyDeviceToHost, h->stream));
+                RP_CUDA(cudaStreamSynchronize(h->stream));
+                rejected += now;
+                initCentres(h);
+                recalcAbsoluteCentres(h);
+                h->gridDirty = true;
+                clean = countTotalOverlaps(h, true) == 0;
+            }
+            cudaFree(flags);
+            if (!clean) {
+                k_restore_orientations<<<(n + 255) / 256, 256, 0, h->stream>>>(n, h->cap, h->orient, backup, nullptr,
+                                                                              nullptr, nullptr);
+                h->launches++;
+                initCentres(h);
+                recalcAbsoluteCentres(h);
+                h->gridDirty = true;
+                rejected = h->n;
+            }
         }
+        if (rejected_out) *rejected_out = rejected;
         RP_CUDA(cudaStreamSynchronize(h->stream));
     }
     RP_API_END(h)
@@ -623,6 +695,7 @@ rp_status rp_last_kernel_ms(rp_handle *h, double *sweep_ms, double *sweep_grid_m
                             double *scaling_ms)
 {
     RP_API_BEGIN(h)
+    sweepTimings(h, true);
     if (sweep_ms) *sweep_ms = h->lastSweepMs;
     if (sweep_grid_ms) *sweep_grid_ms = h->lastSweepGridMs;
     if (rebuild_ms) *rebuild_ms = h->lastRebuildMs;

@@ -183,7 +183,7 @@ void freeGrid(GridStore &g) {
     g.valid = false;
 }
 
-void ensureGridCapacity(GridStore &g, size_t numCells, size_t numItems) {
+void ensureGridCapacity(GridStore &g, size_t numCells, size_t numItems, size_t recDoublesPerItem) {
     RP_EXPECT(numCells < (1ull << 31) && numItems < (1ull << 31), "grid too large for 32-bit indices");
     if (numCells + 1 > g.cellCap || !g.cellStart) {
         if (g.cellStart) cudaFree(g.cellStart);
@@ -202,7 +202,7 @@ void ensureGridCapacity(GridStore &g, size_t numCells, size_t numItems) {
         RP_CUDA(cudaMalloc(&g.keys, newCap * sizeof(int)));
         RP_CUDA(cudaMalloc(&g.itemsTmp, newCap * sizeof(int)));
         RP_CUDA(cudaMalloc(&g.items, newCap * sizeof(int)));
-        RP_CUDA(cudaMalloc(&g.rec, 6 * newCap * sizeof(double)));
+        RP_CUDA(cudaMalloc(&g.rec, recDoublesPerItem * newCap * sizeof(double)));
         g.itemCap = newCap;
     }
     size_t numBlocks = (numCells + SCAN_BLOCK - 1) / SCAN_BLOCK;

@@ -87,6 +87,16 @@ struct GridStore {
     Box box;                      // box the grid was built for (translations)
 };
 
+// geometry of the sweep grid of one rp_sweep call (rp_sweep.cu)
+struct SweepGrid {
+    int n[3];
+    double relCell[3];     // 1 / n[i]
+    double shift[3];       // random relative origin s
+    V3 imageShift[8];      // M * f for f = (fx, fy, fz) in {0,1}^3, index fx + 2 fy + 4 fz
+    V3 trans[27];
+};
+
+constexpr int TIMING_RING = 16;
 struct SweepStats {
     unsigned long long attempted, accepted, rejDomain, rejOverlap;
 };
@@ -128,9 +138,24 @@ struct Handle {
     GridStore sgrid;
     int *sweepMoved = nullptr;    // (unused)
     size_t sweepMovedCap = 0;
-    // trials of one rp_sweep call, per sorted slot: record (6 doubles), new orientation (9 doubles), meta (uint2)
+    // trials of one rp_sweep call, per sorted slot: record (6 doubles), new orientation (9 doubles), meta (uint2),
+    // FP32 cull record of the new state (2 float4)
     double *trialRec = nullptr, *trialOrient = nullptr;
     void *trialMeta = nullptr;
+    void *trialRec32 = nullptr;
+    SweepGrid lastSg;             // sweep grid of the last rp_sweep call (sharded apply kernels, trace)
+    float lastInvHalf = 0.f;
+    // shared-memory staging capacities of k_sweep: taken from the maxima the previous calls observed (read back
+    // without blocking), so that a cycle needs no host synchronisation; 0 = unknown (first call synchronises)
+    int sweepCapOld = 0, sweepCapOwn = 0;
+    int *sweepMaxPinned = nullptr;        // pinned ring of {max cell population, max neighbourhood, cells skipped, -}
+    cudaEvent_t sweepMaxEvent[4] = {nullptr, nullptr, nullptr, nullptr};
+    bool sweepMaxPending[4] = {false, false, false, false};
+    int sweepMaxNext = 0;
+    unsigned long long sweepCellsSkipped = 0;   // cells a sweep left out because the staging capacity was too small
+    unsigned long long sweepSerial = 0;         // rp_sweep calls made on this handle (timing ring)
+    unsigned long long simCycles = 0;           // cycles run by rp_sim loops on this handle (Philox counter of their sweeps)
+    size_t smemConfigured[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // cudaFuncAttributeMaxDynamicSharedMemorySize set per kernel variant
     size_t trialCap = 0;
     // what rp_sweep_trace needs to know about the last rp_sweep call
     bool lastSweepValid = false, lastSweepGeneric = false, lastSweepRotated = false;
@@ -172,6 +197,10 @@ struct Handle {
     // timing of the last call
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     double lastSweepMs = 0, lastSweepGridMs = 0, lastRebuildMs = 0, lastScalingMs = 0;
+    // sweeps are queued without host synchronisation: their timing events live in a ring and are read back later
+    struct TimingSlot { cudaEvent_t e[4] = {nullptr, nullptr, nullptr, nullptr}; bool pending = false; };
+    TimingSlot timing[16];
+    double accSweepMs = 0, accSweepGridMs = 0;      // device time of all sweeps harvested so far
     unsigned long long launches = 0;
 };
 
@@ -206,7 +235,10 @@ inline void computeTranslations(const Box &box, V3 trans[27]) {
 }
 
 // ---- rp_grid.cu ----
-void ensureGridCapacity(GridStore &g, size_t numCells, size_t numItems);
+// rec holds recDoublesPerItem * itemCap doubles (6 = the FP64 records; the sweep grid asks for 10: its 32-byte FP32
+// cull records follow the FP64 records in the same allocation, see sweepRec32)
+void ensureGridCapacity(GridStore &g, size_t numCells, size_t numItems, size_t recDoublesPerItem = 6);
+inline float4 *sweepRec32(const GridStore &g) { return reinterpret_cast<float4 *>(g.rec + 6 * g.itemCap); }
 // histogram in g.cellFill -> g.cellStart (exclusive scan), g.cellFill zeroed, max population -> dMaxPop
 void scanCells(Handle *h, GridStore &g, int *dMaxPop);
 // keys -> items (cell order, ascending index inside a cell); needs scanCells() first
@@ -221,6 +253,9 @@ double totalEnergy(Handle *h);
 void initCentres(Handle *h);
 void recalcAbsoluteCentres(Handle *h);
 double tryMove(Handle *h, const rp_move &m);
+void particleScan(Handle *h, bool wantOverlaps, bool wantEnergy, unsigned char *dOverlapFlag, double *dEnergy);
+double particleEnergyFluctuations(Handle *h);
+unsigned long long countWallOverlaps(Handle *h, bool earlyExit);
 void acceptMove(Handle *h);
 double tryScaling(Handle *h, const Box &newBox);
 void revertScaling(Handle *h);
@@ -237,6 +272,14 @@ void pairDensityCorrelation(Handle *h, double maxR, int numBins, const double fo
                             double *gOut);
 // ---- rp_sweep.cu ----
 void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out);
+// the same without a host synchronisation when out == nullptr (fast path): the four counters {attempted, accepted,
+// rejected: left the cell, rejected: overlap} are ADDED to dAcc[0..3] on the device (dAcc may be nullptr)
+void sweepAsync(Handle *h, const rp_sweep_params &p, unsigned long long *dAcc, rp_sweep_counters *out);
+void sweepTimings(Handle *h, bool block);
+// staging-capacity reports of the queued sweeps (block: of all of them); throws on a peer timeout
+void sweepHarvest(Handle *h, bool block);
+// does a sweep with this sampler run without a host synchronisation (specialised kernel)?
+bool sweepIsQueued(const Handle *h, int kind);
 void cullThresholds(const Handle *h, const double relCell[3], float *thr2, float *half);
 void sweepTrace(Handle *h, rp_trial_trace *out, unsigned long long n);
 

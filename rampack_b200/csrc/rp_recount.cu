@@ -586,6 +586,109 @@ __global__ void k_accept_move(ParticleView P, double *pos, double *orient, doubl
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// bulk per-particle scan of the CURRENT state: overlaps / energy of every particle with the rest of the packing —
+// Packing::countParticleOverlaps(i, i, ...) / calculateParticleEnergy(i, i, ...) for all i (core/Packing.cpp:373-429,
+// 649-688).  Persistent CTAs of 64 threads walk the particles; used by getParticleEnergyFluctuations and by the
+// per-particle rejection of renormalizeOrientations (both rare: every 10^3..10^4 cycles).
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(64) k_particle_scan(ParticleView P, GridView g, int hasGrid, Box box,
+                                                      const Inter *__restrict__ interPtr, int wantOverlaps,
+                                                      int wantEnergy, unsigned char *__restrict__ overlapFlag,
+                                                      double *__restrict__ energyOut)
+{
+    __shared__ Inter I;
+    __shared__ Box sbox;
+    __shared__ TrialState S;
+    __shared__ double red[64];
+    __shared__ unsigned long long redc[64];
+    for (int i = threadIdx.x; i < static_cast<int>(sizeof(Inter) / sizeof(int)); i += blockDim.x)
+        reinterpret_cast<int *>(&I)[i] = reinterpret_cast<const int *>(interPtr)[i];
+    if (threadIdx.x == 0) sbox = box;
+    __syncthreads();
+    for (int particle = blockIdx.x; particle < P.n; particle += gridDim.x) {
+        if (threadIdx.x == 0) {
+            S.pos = loadPos(P, particle);
+            S.orient = loadOrient(P, particle);
+            for (int c = 0; c < I.k; c++) S.cabs[c] = loadCabs(P, particle * I.k + c);
+        }
+        __syncthreads();
+        unsigned long long ov = 0;
+        double en = 0;
+        scanParticle(S, particle, P, g, hasGrid, sbox, I, wantOverlaps != 0, wantEnergy != 0, ov, en);
+        red[threadIdx.x] = en;
+        redc[threadIdx.x] = ov;
+        __syncthreads();
+        for (int o = 32; o > 0; o >>= 1) {
+            if (threadIdx.x < o) { red[threadIdx.x] += red[threadIdx.x + o]; redc[threadIdx.x] += redc[threadIdx.x + o]; }
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) {
+            if (overlapFlag) overlapFlag[particle] = redc[0] ? 1 : 0;
+            if (energyOut) energyOut[particle] = red[0];
+        }
+        __syncthreads();
+    }
+}
+
+void particleScan(Handle *h, bool wantOverlaps, bool wantEnergy, unsigned char *dOverlapFlag, double *dEnergy) {
+    ensureGrid(h);
+    GridView g;
+    if (h->hasGrid) g = makeView(h->grid);
+    else std::memset(&g, 0, sizeof(g));
+    const int blocks = static_cast<int>(std::min<size_t>(h->n, 148 * 16));
+    k_particle_scan<<<blocks, 64, 0, h->stream>>>(particleView(h), g, h->hasGrid ? 1 : 0, h->box, h->dInter,
+                                                  wantOverlaps ? 1 : 0, wantEnergy ? 1 : 0, dOverlapFlag, dEnergy);
+    h->launches++;
+    RP_CUDA(cudaGetLastError());
+}
+
+// Packing::getParticleEnergyFluctuations (core/Packing.cpp:841-856): the per-particle energies come from the device,
+// the two running sums are accumulated on the host in the reference's order
+double particleEnergyFluctuations(Handle *h) {
+    if (!h->inter.soft) return 0;
+    const size_t n = h->n;
+    size_t need = n * sizeof(double);
+    if (need > h->dStageCap) {
+        if (h->dStage) cudaFree(h->dStage);
+        h->dStage = nullptr;
+        RP_CUDA(cudaMalloc(&h->dStage, need + 64));
+        h->dStageCap = need + 64;
+    }
+    double *dEnergy = static_cast<double *>(h->dStage);
+    particleScan(h, false, true, nullptr, dEnergy);
+    std::vector<double> e(n);
+    RP_CUDA(cudaMemcpyAsync(e.data(), dEnergy, need, cudaMemcpyDeviceToHost, h->stream));
+    RP_CUDA(cudaStreamSynchronize(h->stream));
+    double energySum = 0, energySum2 = 0;
+    for (size_t i = 0; i < n; i++) {
+        energySum += e[i];
+        energySum2 += e[i] * e[i];
+    }
+    double N = static_cast<double>(n);
+    double doubleEnergy = std::sqrt(energySum2 / (N - 1) - std::pow(energySum, 2) / N / (N - 1));
+    return doubleEnergy / 2;
+}
+
+// Packing::countWallOverlaps (core/Packing.cpp:561-580)
+unsigned long long countWallOverlaps(Handle *h, bool earlyExit) {
+    if (!h->wallMask || !h->inter.hard) return 0;
+    cudaStream_t st = h->stream;
+    RP_CUDA(cudaMemsetAsync(h->dCounters, 0, sizeof(unsigned long long), st));
+    const int n = static_cast<int>(h->n);
+    k_count_wall_overlaps<<<(n + 255) / 256, 256, 0, st>>>(n, particleView(h), h->crel, h->dInter,
+                                                           makeWalls(h->box, h->wallMask, h->inter.totalRange),
+                                                           h->dCounters);
+    h->launches++;
+    unsigned long long result = 0;
+    RP_CUDA(cudaMemcpyAsync(&result, h->dCounters, sizeof(result), cudaMemcpyDeviceToHost, st));
+    RP_CUDA(cudaStreamSynchronize(st));
+    RP_CUDA(cudaGetLastError());
+    // with early exit the reference returns the overlaps of the particles visited before the flag was seen: at
+    // least 1, at most the full count — callers only test for > 0
+    return (earlyExit && result) ? 1 : result;
+}
+
 // Packing::tryTranslation / tryRotation / tryMove (core/Packing.cpp:84-164) incl. calculateMoveOverlapEnergy
 // (Packing.cpp:304-323)
 double tryMove(Handle *h, const rp_move &m) {

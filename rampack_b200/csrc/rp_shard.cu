@@ -127,11 +127,12 @@ __global__ void k_layer_starts(int nz, int layerCells, const int *__restrict__ c
     if (z <= nz) out[z] = cellStart[z * layerCells];
 }
 
-void shardQueueLayerStarts(Handle *h, int nx, int ny, int nz) {
+void shardQueueLayerStarts(Handle *h, int nx, int ny, int nz, bool toHost) {
     Shard *s = h->shard;
     devEnsure(s->dLayerStart, s->layerCap, static_cast<size_t>(nz) + 1);
     k_layer_starts<<<(nz + 1 + 127) / 128, 128, 0, h->stream>>>(nz, nx * ny, h->sgrid.cellStart, s->dLayerStart);
     h->launches++;
+    if (!toHost) return;
     s->layerStart.resize(nz + 1);
     RP_CUDA(cudaMemcpyAsync(s->layerStart.data(), s->dLayerStart, (nz + 1) * sizeof(int), cudaMemcpyDeviceToHost,
                             h->stream));
@@ -160,8 +161,9 @@ __global__ void k_pack_moves(int s0, int s1, int xyColour, int nx, int ny, const
 
 // the receiving side of the sweep kernel's write-back (same arithmetic: Shape::translate, core/Shape.cpp:9-12)
 __global__ void k_apply_moves(const MoveMsg *__restrict__ in, int translated, int rotated, Box box, size_t cap,
-                              const int *__restrict__ items, double *__restrict__ rec, double *__restrict__ pos,
-                              double *__restrict__ orient, uint2 *__restrict__ meta)
+                              const int *__restrict__ items, const int *__restrict__ keys, SweepGrid sg,
+                              float invHalf, double *__restrict__ rec, float4 *__restrict__ rec32,
+                              double *__restrict__ pos, double *__restrict__ orient, uint2 *__restrict__ meta)
 {
     long long count = in[0].slot;
     long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -169,6 +171,13 @@ __global__ void k_apply_moves(const MoveMsg *__restrict__ in, int translated, in
     const MoveMsg &m = in[1 + i];
     const int slot = static_cast<int>(m.slot), id = items[slot];
     for (int q = 0; q < 6; q++) rec[6 * static_cast<size_t>(slot) + q] = m.rec[q];
+    {   // the FP32 cull record of the new state, by the expression its producer used (k_sweep_prepare)
+        const int cell = keys[id] & 0x0FFFFFFF;
+        const V3 centre = sweepCellCentre(sg, box, cell % sg.n[0], (cell / sg.n[0]) % sg.n[1],
+                                          cell / (sg.n[0] * sg.n[1]));
+        makeRec32(v3(m.rec[0], m.rec[1], m.rec[2]), v3(m.rec[3], m.rec[4], m.rec[5]), centre, invHalf,
+                  rec32 + 2 * static_cast<size_t>(slot));
+    }
     if (translated) {
         V3 np = v3(m.rec[0], m.rec[1], m.rec[2]);
         V3 p = np + pbcCorrection(box, np);
@@ -200,8 +209,8 @@ static void pack(Handle *h, int s0, int s1, int xyColour, int nx, int ny, bool r
 static void apply(Handle *h, const MoveMsg *in, size_t capacity, bool translated, bool rotated) {
     if (capacity == 0) return;
     k_apply_moves<<<static_cast<int>((capacity + 255) / 256), 256, 0, h->stream>>>(
-        in, translated ? 1 : 0, rotated ? 1 : 0, h->box, h->cap, h->sgrid.items, h->sgrid.rec, h->pos, h->orient,
-        static_cast<uint2 *>(h->trialMeta));
+        in, translated ? 1 : 0, rotated ? 1 : 0, h->box, h->cap, h->sgrid.items, h->sgrid.keys, h->lastSg,
+        h->lastInvHalf, h->sgrid.rec, sweepRec32(h->sgrid), h->pos, h->orient, static_cast<uint2 *>(h->trialMeta));
     h->launches++;
 }
 
@@ -345,18 +354,24 @@ PeerView shardPeerView(const Handle *h, int nLayersZ) {
     v.layerHi = 2 * aHi - 1;
     v.recLo = static_cast<double *>(s->peerBase[(r + P - 1) % P][0]);
     v.recHi = static_cast<double *>(s->peerBase[(r + 1) % P][0]);
+    // the cull records live behind the FP64 records of the same allocation (sweepRec32); every replica makes the
+    // same allocation decisions, so the offset is the local one
+    v.rec32Lo = reinterpret_cast<float4 *>(v.recLo + 6 * h->sgrid.itemCap);
+    v.rec32Hi = reinterpret_cast<float4 *>(v.recHi + 6 * h->sgrid.itemCap);
     return v;
 }
 
 // the write-back of k_sweep (rp_sweep_kernel2.cuh) for the accepted trials of the OTHER slabs, from this rank's own
 // copy of the trials
-__global__ void k_apply_accepts(int n, int slotBegin, int slotEnd, const unsigned char *__restrict__ acc,
+__global__ void k_apply_accepts(int n, const int *__restrict__ layerStart, int layerLo, int layerHi,
+                                const unsigned char *__restrict__ acc,
                                 int translated, int rotated, Box box, size_t cap, const int *__restrict__ items,
                                 const double *__restrict__ trialRec, const double *__restrict__ trialOrient,
                                 double *__restrict__ rec, double *__restrict__ pos, double *__restrict__ orient,
                                 uint2 *__restrict__ meta)
 {
     int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const int slotBegin = layerStart[layerLo], slotEnd = layerStart[layerHi];      // my own slab: already written
     if (slot >= n || (slot >= slotBegin && slot < slotEnd) || !acc[slot]) return;
     const int id = items[slot];
     const double *t = trialRec + 6 * static_cast<size_t>(slot);
@@ -370,8 +385,9 @@ __global__ void k_apply_accepts(int n, int slotBegin, int slotEnd, const unsigne
     meta[slot].x = 4u;
 }
 
-void shardApplyAccepts(Handle *h, int slotBegin, int slotEnd, int n, bool translated, bool rotated) {
-    k_apply_accepts<<<(n + 255) / 256, 256, 0, h->stream>>>(n, slotBegin, slotEnd, h->shard->acc, translated ? 1 : 0,
+void shardApplyAccepts(Handle *h, int aLo, int aHi, int n, bool translated, bool rotated) {
+    k_apply_accepts<<<(n + 255) / 256, 256, 0, h->stream>>>(n, h->shard->dLayerStart, 2 * aLo, 2 * aHi,
+                                                           h->shard->acc, translated ? 1 : 0,
                                                            rotated ? 1 : 0, h->box, h->cap, h->sgrid.items,
                                                            h->trialRec, h->trialOrient, h->sgrid.rec, h->pos,
                                                            h->orient, static_cast<uint2 *>(h->trialMeta));
@@ -388,14 +404,32 @@ struct FlagTargets {
 // One launch per synchronisation point: tell the peers "everything I queued before this kernel is done" (the peer
 // writes of earlier kernels are complete at their kernel end; the system-scope fence keeps the flag behind them),
 // then poll until every peer of the set said the same.
-__global__ void k_signal_wait(FlagTargets t, unsigned int value, const unsigned long long *__restrict__ counters) {
+// The poll is bounded (SHARD_WAIT_TIMEOUT_NS of wall clock, ~20 s): a peer that died or left the call sequence must
+// not leave this GPU spinning for ever.  A timeout raises *abortFlag, which the host checks at its next
+// synchronisation point (RP_ERR_STATE "peer timeout"); the sweep's results are then invalid.
+constexpr unsigned long long SHARD_WAIT_TIMEOUT_NS = 20ull * 1000ull * 1000ull * 1000ull;
+__global__ void k_signal_wait(FlagTargets t, unsigned int value, const unsigned long long *__restrict__ counters,
+                              int *__restrict__ abortFlag) {
     if (threadIdx.x < t.n) {
         if (counters)
             for (int j = 0; j < 4; j++) t.cntTo[threadIdx.x][j] = counters[j];
         __threadfence_system();
         *reinterpret_cast<volatile unsigned int *>(t.to[threadIdx.x]) = value;
         volatile unsigned int *f = t.from[threadIdx.x];
-        while (static_cast<int>(*f - value) < 0) __nanosleep(100);
+        unsigned long long t0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        unsigned int spins = 0;
+        while (static_cast<int>(*f - value) < 0) {
+            __nanosleep(100);
+            if ((++spins & 0x3ffu) == 0u) {
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                if (now - t0 > SHARD_WAIT_TIMEOUT_NS || *reinterpret_cast<volatile int *>(abortFlag)) {
+                    atomicExch(abortFlag, 1);
+                    break;
+                }
+            }
+        }
     }
     __threadfence_system();
 }
@@ -421,7 +455,9 @@ static int peerSet(const Shard *s, bool all, int out[SHARD_MAX_PEERS]) {
     return n;
 }
 
-void shardSignalWait(Handle *h, ShardFlag kind, unsigned int value, bool all, bool withCounters) {
+void shardSignalWait(Handle *h, ShardFlag kind, unsigned int value, bool all, bool withCounters,
+                     unsigned long long *dCounters) {
+    if (!dCounters) dCounters = h->dCounters;
     Shard *s = h->shard;
     int q[SHARD_MAX_PEERS];
     FlagTargets t;
@@ -431,10 +467,10 @@ void shardSignalWait(Handle *h, ShardFlag kind, unsigned int value, bool all, bo
         t.from[i] = s->flags + kind * 64 + q[i];
         t.cntTo[i] = counterBlock(s->peerFlags[q[i]]) + 4 * s->rank;
     }
-    k_signal_wait<<<1, 32, 0, h->stream>>>(t, value, withCounters ? h->dCounters : nullptr);
+    k_signal_wait<<<1, 32, 0, h->stream>>>(t, value, withCounters ? dCounters : nullptr, &h->dFlags[SHARD_ABORT_FLAG]);
     h->launches++;
     if (withCounters) {
-        k_sum_counters<<<1, 32, 0, h->stream>>>(s->nranks, s->rank, counterBlock(s->flags), h->dCounters);
+        k_sum_counters<<<1, 32, 0, h->stream>>>(s->nranks, s->rank, counterBlock(s->flags), dCounters);
         h->launches++;
     }
 }

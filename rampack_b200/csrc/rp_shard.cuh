@@ -64,7 +64,9 @@ void shardSlab(int nActiveZ, int nranks, int r, int *aLo, int *aHi);
 // who sends which cell layer to whom after a sub-sweep of `colour` (bit 2 = z parity); nz = cell layers along z
 struct HaloPlan { int aLo, aHi, sendLayer, recvLayer, peerSend, peerRecv; };
 HaloPlan shardHaloPlan(int nz, int nranks, int r, int colour);
-void shardQueueLayerStarts(Handle *h, int nx, int ny, int nz);
+// layer boundaries of the current sweep grid -> device array (always) and, toHost, the host copy (valid after the
+// next stream synchronisation; the NCCL path sizes its messages from it)
+void shardQueueLayerStarts(Handle *h, int nx, int ny, int nz, bool toHost);
 void shardHaloExchange(Handle *h, int colour, int nx, int ny, int nz, bool translated, bool rotated);
 void shardGatherCycle(Handle *h, int nz, bool translated, bool rotated);
 void shardAllReduceU64(Handle *h, unsigned long long *dValues, int count);
@@ -76,17 +78,21 @@ struct PeerView {                 // by-value kernel argument of k_sweep
     unsigned char *acc[SHARD_MAX_PEERS];      // their accept-byte arrays
     int layerLo = -1, layerHi = -1;           // my slab's bottom / top cell layer
     double *recLo = nullptr, *recHi = nullptr;    // sorted records of the rank below / above (read my boundary layers)
+    float4 *rec32Lo = nullptr, *rec32Hi = nullptr;    // ... and their FP32 cull records (same allocation, behind the FP64 records)
 };
 enum ShardFlag { SHARD_FLAG_GRID = 0, SHARD_FLAG_COLOUR = 1, SHARD_FLAG_DONE = 2 };
+constexpr int SHARD_ABORT_FLAG = 12;     // index into Handle::dFlags: a peer-flag wait timed out (never reset by a sweep)
 // (re)maps the peers' buffers when a local buffer moved since the last mapping; collective; returns whether the
 // peer-memory path is usable
 bool shardEnsurePeerMapping(Handle *h);
 PeerView shardPeerView(const Handle *h, int nLayersZ);
 // accepted trials of the slots outside [slotBegin, slotEnd) -> sorted records and canonical arrays
-void shardApplyAccepts(Handle *h, int slotBegin, int slotEnd, int n, bool translated, bool rotated);
+// (the slab's slot range is read from the device copy of the layer boundaries: layers [2 aLo, 2 aHi))
+void shardApplyAccepts(Handle *h, int aLo, int aHi, int n, bool translated, bool rotated);
 // One launch: flag[kind][my rank] = value on the peers (everyone, or the two z-neighbours), ordered after all prior
 // work of the stream, then poll the local flags of the same peers until they reach `value`.  withCounters (sweep
 // done): my four sweep counters travel with the signal and h->dCounters becomes the sum over ranks.
-void shardSignalWait(Handle *h, ShardFlag kind, unsigned int value, bool all, bool withCounters);
+void shardSignalWait(Handle *h, ShardFlag kind, unsigned int value, bool all, bool withCounters,
+                     unsigned long long *dCounters = nullptr);
 
 }  // namespace rp

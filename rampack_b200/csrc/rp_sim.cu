@@ -21,6 +21,13 @@ struct rp_sim {
     unsigned long long curMoves[RP_SIM_MAX_SAMPLERS] = {}, curAccepted[RP_SIM_MAX_SAMPLERS] = {};
     unsigned long long curScalings = 0, curScalingsAccepted = 0;
     std::string error;
+    // Sweeps of the specialised kernel are queued without a host synchronisation: their counters are accumulated on
+    // the device ({attempted, accepted, left the cell, overlap} per sampler) and read when somebody needs them —
+    // evaluateCounters once a window of 100 N moves is full, rp_sim_stats_get, the end of rp_sim_run.
+    unsigned long long *dAcc = nullptr;                         // 4 * RP_SIM_MAX_SAMPLERS
+    unsigned long long devSeen[4 * RP_SIM_MAX_SAMPLERS] = {};   // device accumulators at the last read
+    unsigned long long pendingMoves[RP_SIM_MAX_SAMPLERS] = {};  // attempted moves queued since the last read (estimate)
+    double accSweepBase = 0, accGridBase = 0;                   // h->accSweepMs / accSweepGridMs at creation
 };
 
 namespace {
@@ -134,9 +141,31 @@ bool tryScalingStep(rp_sim *s) {
     return false;
 }
 
+// device accumulators -> host counters (blocks until the queued sweeps are done)
+void readDeviceCounters(rp_sim *s) {
+    bool any = false;
+    for (int i = 0; i < s->cfg.n_samplers; i++) any = any || s->pendingMoves[i] > 0;
+    if (!any) return;
+    unsigned long long now[4 * RP_SIM_MAX_SAMPLERS];
+    RP_CUDA(cudaMemcpyAsync(now, s->dAcc, sizeof(now), cudaMemcpyDeviceToHost, s->h->stream));
+    RP_CUDA(cudaStreamSynchronize(s->h->stream));
+    RP_CUDA(cudaGetLastError());
+    for (int i = 0; i < s->cfg.n_samplers; i++) {
+        const unsigned long long att = now[4 * i] - s->devSeen[4 * i], acc = now[4 * i + 1] - s->devSeen[4 * i + 1];
+        s->st.moves_attempted[i] += att;
+        s->st.moves_accepted[i] += acc;
+        s->curMoves[i] += att;
+        s->curAccepted[i] += acc;
+        s->pendingMoves[i] = 0;
+    }
+    std::memcpy(s->devSeen, now, sizeof(now));
+}
+
 // Simulation::evaluateMoleculeMoveCounter / evaluateScalingMoveCounter (core/Simulation.cpp:533-607)
 void evaluateCounters(rp_sim *s) {
     const unsigned long long N = s->h->n;
+    for (int i = 0; i < s->cfg.n_samplers; i++)
+        if (s->curMoves[i] + s->pendingMoves[i] >= 100 * N) { readDeviceCounters(s); break; }
     double heights[3];
     boxHeights(s->h->box, heights);
     const double maxTranslation = std::min(heights[0], std::min(heights[1], heights[2])) / 2;
@@ -180,20 +209,26 @@ void performCycle(rp_sim *s, bool adjust) {
         p.translation_step = std::min(s->st.translation_step[i], maxTranslation);
         p.rotation_step = std::min(s->st.rotation_step[i], M_PI);
         p.temperature = s->cfg.temperature;
-        p.cycle = s->st.cycles;
+        // the Philox streams of a sweep are keyed by (handle seed, particle, cycle, pass): the cycle number is the
+        // handle's own count of cycles, so a second rp_sim on the same handle (thermalisation, then averaging)
+        // continues the streams instead of replaying them
+        p.cycle = h->simCycles;
         for (int q = 0; q < 3; q++) {
             p.flip_axis[q] = s->cfg.samplers[i].flip_axis[q];
             p.flip_origin[q] = s->cfg.samplers[i].flip_origin[q];
         }
         p.flip_every = s->cfg.samplers[i].flip_every;
-        rp_sweep_counters c;
-        check(s, rp_sweep(h, &p, &c));
-        s->st.moves_attempted[i] += c.attempted;
-        s->st.moves_accepted[i] += c.accepted;
-        s->curMoves[i] += c.attempted;
-        s->curAccepted[i] += c.accepted;
-        s->st.sweep_kernel_ms += h->lastSweepMs;
-        s->st.sweep_grid_ms += h->lastSweepGridMs;
+        if (sweepIsQueued(h, p.kind)) {
+            sweepAsync(h, p, s->dAcc + 4 * i, nullptr);
+            s->pendingMoves[i] += h->n;
+        } else {
+            rp_sweep_counters c;
+            sweepAsync(h, p, nullptr, &c);
+            s->st.moves_attempted[i] += c.attempted;
+            s->st.moves_accepted[i] += c.accepted;
+            s->curMoves[i] += c.attempted;
+            s->curAccepted[i] += c.accepted;
+        }
     }
     if (s->cfg.scaler_kind != RP_SCALER_NONE) {
         bool wasScaled = tryScalingStep(s);
@@ -203,6 +238,7 @@ void performCycle(rp_sim *s, bool adjust) {
     }
     if (adjust) evaluateCounters(s);
     s->st.cycles++;
+    h->simCycles++;
     // Simulation::fixRotationMatrices (core/Simulation.cpp:144-145, 750-769)
     if (s->cfg.rotation_matrix_fix_every > 0 && s->st.cycles % s->cfg.rotation_matrix_fix_every == 0)
         check(s, rp_renormalize_orientations(h, h->overlapCounting ? 1 : 0, nullptr));
@@ -239,17 +275,41 @@ rp_status rp_sim_create(rp_handle *h, const rp_sim_config *config, rp_sim **out)
         s->st.rotation_step[i] = c.samplers[i].rotation_step;
     }
     s->st.scaler_step = c.scaler_step;
+    if (h) {
+        cudaSetDevice(h->device);
+        if (cudaMalloc(&s->dAcc, 4 * RP_SIM_MAX_SAMPLERS * sizeof(unsigned long long)) != cudaSuccess
+            || cudaMemsetAsync(s->dAcc, 0, 4 * RP_SIM_MAX_SAMPLERS * sizeof(unsigned long long), h->stream) != cudaSuccess) {
+            rp::tlsError = "rp_sim_create: cannot allocate the device counters";
+            delete s;
+            return RP_ERR_CUDA;
+        }
+        s->accSweepBase = h->accSweepMs;
+        s->accGridBase = h->accSweepGridMs;
+    }
     *out = s;
     return RP_OK;
 }
 
-void rp_sim_destroy(rp_sim *s) { delete s; }
+void rp_sim_destroy(rp_sim *s) {
+    if (!s) return;
+    if (s->dAcc) {
+        cudaSetDevice(s->h->device);
+        cudaStreamSynchronize(s->h->stream);
+        cudaFree(s->dAcc);
+    }
+    delete s;
+}
 
 rp_status rp_sim_run(rp_sim *s, uint64_t cycles, int adjust_step_sizes) {
     if (!s || !s->h) { rp::tlsError = "rp_sim_run: needs an rp_sim bound to a handle"; return RP_ERR_PRECONDITION; }
     try {
         RP_EXPECT(s->h->hasInteraction && s->h->n > 0, "packing and interaction must be set");
         for (uint64_t c = 0; c < cycles; c++) performCycle(s, adjust_step_sizes != 0);
+        // one synchronisation per call: counters, device times, staging-capacity reports of the queued sweeps
+        readDeviceCounters(s);
+        RP_CUDA(cudaStreamSynchronize(s->h->stream));
+        sweepTimings(s->h, true);
+        sweepHarvest(s->h, true);
     } catch (const rp::rp_error &e) {
         s->h->error = e.what();
         return static_cast<rp_status>(e.status);
@@ -263,7 +323,12 @@ rp_status rp_sim_run(rp_sim *s, uint64_t cycles, int adjust_step_sizes) {
 rp_status rp_sim_stats_get(const rp_sim *s, rp_sim_stats *out) {
     if (!s || !out) return RP_ERR_PRECONDITION;
     *out = s->st;
-    if (s->h) for (int i = 0; i < 9; i++) out->box[i] = s->h->box.m.a[i];
+    if (s->h) {
+        for (int i = 0; i < 9; i++) out->box[i] = s->h->box.m.a[i];
+        out->sweep_kernel_ms = s->h->accSweepMs - s->accSweepBase;
+        out->sweep_grid_ms = s->h->accSweepGridMs - s->accGridBase;
+        out->cells_skipped = s->h->sweepCellsSkipped;
+    }
     return RP_OK;
 }
 

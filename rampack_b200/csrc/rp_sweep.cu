@@ -67,49 +67,14 @@ __global__ void k_sweep_scatter(int n, const int *__restrict__ keys, const int *
     itemsTmp[cellStart[c] + atomicAdd(&fill[c], 1)] = i;
 }
 
-// one warp per cell: order the items by ascending particle index and write the 48-byte AoS records
-// {P'x, P'y, P'z, aux x, aux y, aux z} in the image frame; also the 27-neighbourhood population maximum
-template <int HARD>
-__global__ void k_sweep_records(int numCells, size_t cap, const int *__restrict__ cellStart,
-                                const int *__restrict__ itemsTmp, const int *__restrict__ keys,
-                                const double *__restrict__ pos, const double *__restrict__ orient, SweepGrid sg,
-                                double halfLength, int *__restrict__ items, double *__restrict__ rec,
-                                int *__restrict__ maxNeigh)
-{
-    int cell = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    int lane = threadIdx.x & 31;
-    if (cell >= numCells) return;
-    int start = cellStart[cell], end = cellStart[cell + 1];
-    int cnt = end - start;
-    for (int i = lane; i < cnt; i += 32) {
-        int id = itemsTmp[start + i];
-        int rank = 0;
-        for (int j = 0; j < cnt; j++) rank += (itemsTmp[start + j] < id);
-        int slot = start + rank;
-        items[slot] = id;
-        int f = (keys[id] >> 28) & 7;
-        V3 p = v3(pos[id], pos[cap + id], pos[2 * cap + id]);
-        if (f) p = p + sg.imageShift[f];
-        double *r = rec + 6 * static_cast<size_t>(slot);
-        r[0] = p.x; r[1] = p.y; r[2] = p.z;
-        if (HARD == RP_HARD_SPHEROCYLINDER) {
-            // half axis h = orientation.column(2) * (0.5 * l): the cap centres are pos -+ h (SpherocylinderTraits.cpp:24-26)
-            r[3] = orient[2 * cap + id] * halfLength; r[4] = orient[5 * cap + id] * halfLength;
-            r[5] = orient[8 * cap + id] * halfLength;
-        } else {
-            r[3] = 0; r[4] = 0; r[5] = 0;
-        }
+// {max cell population, max neighbourhood population, cells skipped, peer timeout} -> mapped pinned memory
+// ... and the four counters of this sweep added to the caller's accumulators (the cycle loop reads them later)
+__global__ void k_sweep_report(const int *__restrict__ flags, int *__restrict__ out,
+                               const unsigned long long *__restrict__ counters, unsigned long long *__restrict__ acc) {
+    if (threadIdx.x == 0) {
+        out[0] = flags[1]; out[1] = flags[2]; out[2] = flags[3]; out[3] = flags[SHARD_ABORT_FLAG];
     }
-    // population of the 27-neighbourhood (smem sizing of the sweep kernel)
-    int cx = cell % sg.n[0], cy = (cell / sg.n[0]) % sg.n[1], cz = cell / (sg.n[0] * sg.n[1]);
-    int sum = 0;
-    if (lane < 27) {
-        int tIdx;
-        int c2 = neighbourCell(sg.n, cx, cy, cz, lane / 9 - 1, (lane / 3) % 3 - 1, lane % 3 - 1, &tIdx);
-        sum = cellStart[c2 + 1] - cellStart[c2];
-    }
-    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if (lane == 0) atomicMax(maxNeigh, sum);
+    if (acc && threadIdx.x < 4) acc[threadIdx.x] += counters[threadIdx.x];
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -135,22 +100,71 @@ void cullThresholds(const Handle *h, const double relCell[3], float *thr2, float
     *half = static_cast<float>(I.scHalfPlus);
 }
 
-constexpr int SW_THREADS = 128;
+// k_sweep variants: threads per CTA (= per active cell) and the minimum CTAs per SM the register allocation aims at.
+// The default is picked from the number of active cells (one wave or less: more threads per cell so that a launch
+// does not cost a full 4-warp CTA lifetime); RP_SWEEP_THREADS / RP_SWEEP_MINB override it (measurement hook).
+struct SweepVariant { int threads, minb, index; };
+static const SweepVariant SWEEP_VARIANTS[] = {{128, 4, 0}, {128, 5, 1}, {128, 6, 2}, {64, 8, 3}, {64, 10, 4},
+                                              {256, 2, 5}, {256, 3, 6}};
 
-template <int HARD>
-static void launchSweep(Handle *h, const SweepArgs &A0, const SweepGrid &sg, const int colourOrder[8], size_t smem,
-                        const TrialBuffers &T)
+static SweepVariant chooseVariant(int activeCells) {
+    int threads = activeCells <= 148 * 3 ? 256 : 128;
+    int minb = threads == 256 ? 3 : 5;
+    if (const char *e = std::getenv("RP_SWEEP_THREADS")) threads = std::atoi(e);
+    if (const char *e = std::getenv("RP_SWEEP_MINB")) minb = std::atoi(e);
+    for (const SweepVariant &v : SWEEP_VARIANTS)
+        if (v.threads == threads && v.minb == minb) return v;
+    for (const SweepVariant &v : SWEEP_VARIANTS)
+        if (v.threads == threads) return v;
+    return SWEEP_VARIANTS[1];
+}
+
+static size_t sweepSmemBytes(int capOld, int capOwn, int threads) {
+    return static_cast<size_t>(capOld + capOwn) * 32 + static_cast<size_t>(capOwn) * 48
+           + static_cast<size_t>(threads / 32) * SW_WQCAP * sizeof(unsigned int);
+}
+
+template <int HARD, int THREADS, int MINB>
+static void launchColour(Handle *h, int variantIndex, int blocks, size_t smem, const SweepArgs &A, const SweepGrid &sg,
+                         const SweepCellOffsets &off, const TrialBuffers &T, unsigned long long *dCounters,
+                         const PeerView &peers)
 {
-    static size_t configured = 0;
+    GridStore &g = h->sgrid;
+    // the attribute is per device and per kernel instantiation: kept per handle (a handle lives on one device)
+    size_t &configured = h->smemConfigured[variantIndex + (HARD == RP_HARD_SPHERE ? 8 : 0)];
     if (smem > configured) {
-        RP_CUDA(cudaFuncSetAttribute(k_sweep<HARD, SW_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        RP_CUDA(cudaFuncSetAttribute(k_sweep<HARD, THREADS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      static_cast<int>(std::max<size_t>(smem, 48 * 1024))));
         configured = std::max<size_t>(smem, 48 * 1024);
     }
-    GridStore &g = h->sgrid;
-    int n = static_cast<int>(h->n);
+    k_sweep<HARD, THREADS, MINB><<<blocks, THREADS, smem, h->stream>>>(A, sg, off, h->box, g.cellStart, g.items, g.rec,
+                                                                      sweepRec32(g), T, h->pos, h->orient, dCounters,
+                                                                      h->dFlags, peers);
+}
+
+template <int HARD>
+static void launchColourVariant(Handle *h, const SweepVariant &v, int blocks, size_t smem, const SweepArgs &A,
+                                const SweepGrid &sg, const SweepCellOffsets &off, const TrialBuffers &T,
+                                unsigned long long *dCounters, const PeerView &peers)
+{
+    switch (v.index) {
+        case 0: launchColour<HARD, 128, 4>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
+        case 1: launchColour<HARD, 128, 5>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
+        case 2: launchColour<HARD, 128, 6>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
+        case 3: launchColour<HARD, 64, 8>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
+        case 4: launchColour<HARD, 64, 10>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
+        case 5: launchColour<HARD, 256, 2>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
+        default: launchColour<HARD, 256, 3>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
+    }
+}
+
+template <int HARD>
+static void launchSweep(Handle *h, const SweepArgs &A0, const SweepGrid &sg, const SweepCellOffsets &off,
+                        const int colourOrder[8], const TrialBuffers &T, unsigned long long *dCounters)
+{
     const bool sharded = shardActive(h);
     const bool translated = A0.kind != RP_MOVE_ROTATION, rotated = A0.kind != RP_MOVE_TRANSLATION;
+    int n = static_cast<int>(h->n);
     int activeLayers = A0.nActive[2];
     if (sharded) {
         int aLo, aHi;
@@ -159,32 +173,23 @@ static void launchSweep(Handle *h, const SweepArgs &A0, const SweepGrid &sg, con
         h->shard->lastHaloBytes = h->shard->lastGatherBytes = 0;
     }
     // peer-memory path: accepted moves are written into all replicas by k_sweep itself, flags order the colours
-    const bool p2p = sharded && shardEnsurePeerMapping(h);
+    const bool p2p = sharded && h->shard->p2p;
     PeerView peers;
     unsigned int epoch = 0;
     if (p2p) {
         peers = shardPeerView(h, sg.n[2]);
         epoch = ++h->shard->sweepEpoch;
-    }
-    SweepArgs AT = A0;
-    if (p2p) { AT.slotBegin = 0; AT.slotEnd = n; }       // every rank holds the trials of all slots
-    int nTrials = AT.slotEnd - AT.slotBegin;
-    if (nTrials > 0)
-        k_sweep_trials<HARD><<<(nTrials + 127) / 128, 128, 0, h->stream>>>(
-            n, AT, sg, h->box, h->inter.scHalfPlus, g.items, g.keys, g.rec, h->orient, T,
-            makeWalls(h->box, h->wallMask, h->inter.totalRange), h->inter.radius);
-    h->launches++;
-    if (p2p) {      // nobody writes into a replica whose grid of this sweep is not built yet
+        // nobody writes into a replica whose grid of this sweep is not built yet
         shardSignalWait(h, SHARD_FLAG_GRID, epoch, true, false);
     }
+    const int blocks = A0.nActive[0] * A0.nActive[1] * activeLayers;
+    const SweepVariant v = chooseVariant(blocks);
+    const size_t smem = sweepSmemBytes(A0.capOld, A0.capOwn, v.threads);
     for (int c = 0; c < 8; c++) {
         SweepArgs A = A0;
         int col = colourOrder[c];
         A.colour[0] = col & 1; A.colour[1] = (col >> 1) & 1; A.colour[2] = (col >> 2) & 1;
-        int blocks = A.nActive[0] * A.nActive[1] * activeLayers;
-        k_sweep<HARD, SW_THREADS><<<blocks, SW_THREADS, smem, h->stream>>>(A, sg, h->box, g.cellStart,
-                                                                          g.items, g.rec, T, h->pos, h->orient,
-                                                                          h->dCounters, h->dFlags, peers);
+        launchColourVariant<HARD>(h, v, blocks, smem, A, sg, off, T, dCounters, peers);
         h->launches++;
         if (p2p) {
             if (c < 7) {        // the z-neighbours read my boundary layers in the next colour
@@ -193,23 +198,26 @@ static void launchSweep(Handle *h, const SweepArgs &A0, const SweepGrid &sg, con
         } else if (sharded) shardHaloExchange(h, col, sg.n[0], sg.n[1], sg.n[2], translated, rotated);
     }
     if (p2p) {                  // all replicas identical again before the next grid build / box move / download
-        shardSignalWait(h, SHARD_FLAG_DONE, epoch, true, true);
-        shardApplyAccepts(h, A0.slotBegin, A0.slotEnd, n, translated, rotated);
+        shardSignalWait(h, SHARD_FLAG_DONE, epoch, true, true, dCounters);
+        int aLo, aHi;
+        shardSlab(A0.nActive[2], h->shard->nranks, h->shard->rank, &aLo, &aHi);
+        shardApplyAccepts(h, aLo, aHi, n, translated, rotated);
     } else if (sharded) {
         shardGatherCycle(h, sg.n[2], translated, rotated);
-        shardAllReduceU64(h, h->dCounters, 4);
+        shardAllReduceU64(h, dCounters, 4);
     }
 }
 
 static void ensureTrialBuffers(Handle *h) {
     if (h->n > h->trialCap || !h->trialRec) {
-        for (void *q : {(void *) h->trialRec, (void *) h->trialOrient, h->trialMeta}) if (q) cudaFree(q);
+        for (void *q : {(void *) h->trialRec, (void *) h->trialOrient, h->trialMeta, h->trialRec32}) if (q) cudaFree(q);
         h->trialRec = h->trialOrient = nullptr;
-        h->trialMeta = nullptr;
+        h->trialMeta = h->trialRec32 = nullptr;
         size_t cap = h->n + h->n / 8 + 64;
         RP_CUDA(cudaMalloc(&h->trialRec, cap * 6 * sizeof(double)));
         RP_CUDA(cudaMalloc(&h->trialOrient, cap * 9 * sizeof(double)));
         RP_CUDA(cudaMalloc(&h->trialMeta, cap * sizeof(uint2)));
+        RP_CUDA(cudaMalloc(&h->trialRec32, cap * 2 * sizeof(float4)));
         h->trialCap = cap;
     }
 }
@@ -221,9 +229,27 @@ static bool fastPathEligible(const Handle *h) {
 }
 
 static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &sg, const int colourOrder[8],
-                         const int refN[3], rp_sweep_counters *out);
+                         const int refN[3], rp_sweep_counters *out, cudaEvent_t *ev);
 
-void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
+// the maxima the previous sweeps reported (pinned ring, non-blocking): grow the staging capacities of the next one
+static void harvestSweepMaxima(Handle *h, bool block) {
+    for (int i = 0; i < 4; i++) {
+        if (!h->sweepMaxPending[i]) continue;
+        if (block) RP_CUDA(cudaEventSynchronize(h->sweepMaxEvent[i]));
+        else if (cudaEventQuery(h->sweepMaxEvent[i]) != cudaSuccess) { cudaGetLastError(); continue; }
+        h->sweepMaxPending[i] = false;
+        const int *m = h->sweepMaxPinned + 4 * i;
+        // head room: the densest neighbourhood of the next cycles is a few particles away from this one's
+        h->sweepCapOwn = std::max(h->sweepCapOwn, m[0] + m[0] / 8 + 4);
+        h->sweepCapOld = std::max(h->sweepCapOld, m[1] + m[1] / 16 + 16);
+        h->sweepCellsSkipped += static_cast<unsigned long long>(m[2]);
+        if (m[3]) throw rp_error(RP_ERR_STATE, "rp_sweep: a peer rank did not reach a synchronisation point within "
+                                               "20 s (peer timeout); the state of this handle is undefined");
+    }
+}
+
+void sweepAsync(Handle *h, const rp_sweep_params &p, unsigned long long *dAcc, rp_sweep_counters *out) {
+    unsigned long long *dCounters = h->dCounters;
     const Inter &I = h->inter;
     const bool flip = p.kind == RP_MOVE_FLIP;
     const bool fast = fastPathEligible(h) && !flip;
@@ -277,9 +303,11 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
         sg.relCell[i] = 1 / static_cast<double>(n);
         numCells *= n;
     }
-    // random grid origin and colour order from the host side of the same Philox generator
+    // random grid origin and colour order from the host side of the same Philox generator.  The cycle number is a
+    // 64-bit quantity: its low word is a Philox counter word, its high word is folded into the key.
+    const unsigned long long sweepSeed = h->seed ^ ((p.cycle >> 32) * 0x9E3779B97F4A7C15ull);
     Rng rng;
-    rng.init(h->seed, 0xFFFFFFFFu, static_cast<unsigned int>(p.cycle), static_cast<unsigned int>(p.pass));
+    rng.init(sweepSeed, 0xFFFFFFFFu, static_cast<unsigned int>(p.cycle), static_cast<unsigned int>(p.pass));
     for (int i = 0; i < 3; i++) sg.shift[i] = rng.uniform();
     int colourOrder[8] = {0, 1, 2, 3, 4, 5, 6, 7};
     for (int i = 7; i > 0; i--) {
@@ -294,9 +322,11 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
     for (int c = 0; c < 8; c++) { h->lastColourOrder[c] = colourOrder[c]; h->lastImageShift[c] = sg.imageShift[c]; }
     for (int i = 0; i < 3; i++) h->lastSweepN[i] = sg.n[i];
     h->lastSweepRotated = rotated;
+    h->lastSg = sg;
+    h->sweepSerial++;
 
     GridStore &g = h->sgrid;
-    ensureGridCapacity(g, numCells, h->n);
+    ensureGridCapacity(g, numCells, h->n, 10);
     for (int i = 0; i < 3; i++) g.n[i] = sg.n[i];
     g.numCells = static_cast<int>(numCells);
     g.numItems = static_cast<int>(h->n);
@@ -305,7 +335,11 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
 
     cudaStream_t st = h->stream;
     int n = static_cast<int>(h->n);
-    RP_CUDA(cudaEventRecord(h->ev[0], st));
+    // timing events come from a ring: a sweep's device times are collected later without blocking (sweepTimings)
+    const int tslot = static_cast<int>(h->sweepSerial % TIMING_RING);
+    if (h->timing[tslot].pending) sweepTimings(h, true);
+    cudaEvent_t *ev = h->timing[tslot].e;
+    RP_CUDA(cudaEventRecord(ev[0], st));
     RP_CUDA(cudaMemsetAsync(g.cellFill, 0, (numCells + 1) * sizeof(int), st));
     RP_CUDA(cudaMemsetAsync(h->dFlags, 0, 8 * sizeof(int), st));
     RP_CUDA(cudaMemsetAsync(h->dCounters, 0, 8 * sizeof(unsigned long long), st));
@@ -317,51 +351,22 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
             throw rp_error(RP_ERR_UNSUPPORTED, "rp_sweep: the sharded sweep covers hard spheres / spherocylinders "
                                                "only (other interactions: run replicas)");
         h->launches += 2;
-        sweepGeneric(h, p, sg, colourOrder, refN, out);
+        sweepGeneric(h, p, sg, colourOrder, refN, out, ev);
         return;
     }
     if (shardActive(h) && sg.n[2] / 2 < h->shard->nranks)
         throw rp_error(RP_ERR_UNSUPPORTED, "rp_sweep: fewer active cell layers along z than ranks; use fewer GPUs "
                                            "or orient the longest box vector along z");
-    int recBlocks = static_cast<int>((numCells * 32 + 255) / 256);
-    if (I.hard == RP_HARD_SPHERE)
-        k_sweep_records<RP_HARD_SPHERE><<<recBlocks, 256, 0, st>>>(g.numCells, h->cap, g.cellStart, g.itemsTmp,
-                                                                    g.keys, h->pos, h->orient, sg, 0.0, g.items,
-                                                                    g.rec, &h->dFlags[2]);
-    else
-        k_sweep_records<RP_HARD_SPHEROCYLINDER><<<recBlocks, 256, 0, st>>>(g.numCells, h->cap, g.cellStart,
-                                                                            g.itemsTmp, g.keys, h->pos, h->orient,
-                                                                            sg, I.scHalfPlus, g.items, g.rec,
-                                                                            &h->dFlags[2]);
-    h->launches += 3;
-    if (shardActive(h)) shardQueueLayerStarts(h, sg.n[0], sg.n[1], sg.n[2]);
-    RP_CUDA(cudaEventRecord(h->ev[1], st));
-    int flags[4];
-    RP_CUDA(cudaMemcpyAsync(flags, h->dFlags, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    RP_CUDA(cudaStreamSynchronize(st));
-    RP_CUDA(cudaGetLastError());
-    g.maxPopulation = flags[1];
-    int maxNeigh = flags[2];
-    if (maxNeigh >= 65536)
-        throw rp_error(RP_ERR_CAPACITY, "rp_sweep: a cell neighbourhood holds more than 65535 particles");
-    // staging capacities: records are 48 bytes, so any count keeps the 16-byte alignment of the bulk copies
-    const int capOld = maxNeigh, capOwn = g.maxPopulation;
-    const int capCand = capOld + capOwn;
-    size_t smem = static_cast<size_t>(capCand) * 6 * sizeof(double)
-                  + (SW_THREADS / 32) * SW_WQCAP * sizeof(unsigned int);
-    if (smem > 200 * 1024)
-        throw rp_error(RP_ERR_CAPACITY, "rp_sweep: a cell neighbourhood does not fit into shared memory");
 
     SweepArgs A;
     A.kind = p.kind;
     A.transStep = p.translation_step;
     A.rotStep = p.rotation_step;
-    A.seed = h->seed;
+    A.seed = sweepSeed;
     A.cycle = static_cast<unsigned int>(p.cycle);
     A.pass = static_cast<unsigned int>(p.pass);
     for (int i = 0; i < 3; i++) { A.nActive[i] = sg.n[i] / 2; A.colour[i] = 0; }
-    A.capOld = capOld;
-    A.capOwn = capOwn;
+    A.capOld = A.capOwn = 0;
     {
         cullThresholds(h, sg.relCell, &A.cullThr2, &A.cullHalf);
         // test hook: with the cull disabled every pair takes the exact FP64 test; the results must be bit-identical
@@ -372,44 +377,113 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
     A.aOff2 = 0;
     A.slotBegin = 0;
     A.slotEnd = n;
-    if (shardActive(h)) {
-        int aLo, aHi;
-        shardSlab(sg.n[2] / 2, h->shard->nranks, h->shard->rank, &aLo, &aHi);
-        A.aOff2 = aLo;
-        A.slotBegin = h->shard->layerStart[2 * aLo];
-        A.slotEnd = h->shard->layerStart[2 * aHi];
-    }
     A.inter.sphereThr2 = I.sphereThr2;
     A.inter.scInner2 = I.scInner2;
     A.inter.scOuter2 = I.scOuter2;
     A.inter.scHalf = I.scHalfPlus;
+    h->lastInvHalf = (I.hard == RP_HARD_SPHEROCYLINDER && A.cullHalf > 0.f) ? 1.0f / A.cullHalf : 0.f;
     ensureTrialBuffers(h);
     TrialBuffers T;
     T.rec = h->trialRec;
     T.orient = h->trialOrient;
     T.meta = static_cast<uint2 *>(h->trialMeta);
-    RP_CUDA(cudaEventRecord(h->ev[2], st));
-    if (I.hard == RP_HARD_SPHERE) launchSweep<RP_HARD_SPHERE>(h, A, sg, colourOrder, smem, T);
-    else launchSweep<RP_HARD_SPHEROCYLINDER>(h, A, sg, colourOrder, smem, T);
-    RP_CUDA(cudaEventRecord(h->ev[3], st));
-    unsigned long long counters[4];
-    RP_CUDA(cudaMemcpyAsync(counters, h->dCounters, sizeof(counters), cudaMemcpyDeviceToHost, st));
-    RP_CUDA(cudaMemcpyAsync(flags, h->dFlags, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    RP_CUDA(cudaStreamSynchronize(st));
-    RP_CUDA(cudaGetLastError());
-    float msGrid = 0, msSweep = 0;
-    cudaEventElapsedTime(&msGrid, h->ev[0], h->ev[1]);
-    cudaEventElapsedTime(&msSweep, h->ev[2], h->ev[3]);
-    h->lastSweepMs = msSweep;
-    h->lastSweepGridMs = msGrid;
+    T.rec32 = static_cast<float4 *>(h->trialRec32);
+    // centre-to-centre vectors of the 27 neighbour cells in FP32 (the frame change of the staged cull records)
+    SweepCellOffsets off;
+    for (int code = 0; code < 27; code++) {
+        V3 o = relToAbs(h->box, v3((code % 3 - 1) * sg.relCell[0], ((code / 3) % 3 - 1) * sg.relCell[1],
+                                   (code / 9 - 1) * sg.relCell[2]));
+        off.o[code][0] = static_cast<float>(o.x); off.o[code][1] = static_cast<float>(o.y);
+        off.o[code][2] = static_cast<float>(o.z);
+    }
+
+    // sharded: the peer mapping (collective, may synchronise) and, over NCCL, the slab's slot range
+    bool p2p = false;
+    if (shardActive(h)) {
+        p2p = shardEnsurePeerMapping(h);
+        shardQueueLayerStarts(h, sg.n[0], sg.n[1], sg.n[2], !p2p);
+        if (!p2p) {
+            // NCCL path: a rank generates the trials of its own slab only -> needs the layer boundaries on the host
+            RP_CUDA(cudaStreamSynchronize(st));
+            int aLo, aHi;
+            shardSlab(sg.n[2] / 2, h->shard->nranks, h->shard->rank, &aLo, &aHi);
+            A.slotBegin = h->shard->layerStart[2 * aLo];
+            A.slotEnd = h->shard->layerStart[2 * aHi];
+        }
+        int aLo, aHi;
+        shardSlab(sg.n[2] / 2, h->shard->nranks, h->shard->rank, &aLo, &aHi);
+        A.aOff2 = aLo;
+    }
+    int prepBlocks = static_cast<int>((numCells * 32 + 255) / 256);
+    const Walls W = makeWalls(h->box, h->wallMask, I.totalRange);
+    if (I.hard == RP_HARD_SPHERE)
+        k_sweep_prepare<RP_HARD_SPHERE><<<prepBlocks, 256, 0, st>>>(g.numCells, A, sg, h->box, 0.0, g.cellStart,
+                                                                    g.itemsTmp, g.keys, h->pos, h->orient, g.items,
+                                                                    g.rec, sweepRec32(g), T, W, I.radius,
+                                                                    &h->dFlags[2]);
+    else
+        k_sweep_prepare<RP_HARD_SPHEROCYLINDER><<<prepBlocks, 256, 0, st>>>(g.numCells, A, sg, h->box, I.scHalfPlus,
+                                                                            g.cellStart, g.itemsTmp, g.keys, h->pos,
+                                                                            h->orient, g.items, g.rec,
+                                                                            sweepRec32(g), T, W, I.radius,
+                                                                            &h->dFlags[2]);
+    h->launches += 6;
+    RP_CUDA(cudaEventRecord(ev[1], st));
+
+    // staging capacities: from the maxima of the previous sweeps when there are any (no host synchronisation), else
+    // from this grid (one synchronisation, first call or after the packing changed)
+    harvestSweepMaxima(h, false);
+    if (h->sweepCapOld == 0 || std::getenv("RP_SWEEP_SYNC_CAPS")) {
+        int flags[4];
+        RP_CUDA(cudaMemcpyAsync(flags, h->dFlags, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+        RP_CUDA(cudaStreamSynchronize(st));
+        RP_CUDA(cudaGetLastError());
+        h->sweepCapOwn = std::max(h->sweepCapOwn, flags[1] + flags[1] / 8 + 4);
+        h->sweepCapOld = std::max(h->sweepCapOld, flags[2] + flags[2] / 16 + 16);
+    }
+    g.maxPopulation = h->sweepCapOwn;
+    if (h->sweepCapOld >= 65536)
+        throw rp_error(RP_ERR_CAPACITY, "rp_sweep: a cell neighbourhood holds more than 65535 particles");
+    A.capOld = h->sweepCapOld;
+    A.capOwn = h->sweepCapOwn;
+    if (sweepSmemBytes(A.capOld, A.capOwn, 256) > 200 * 1024)
+        throw rp_error(RP_ERR_CAPACITY, "rp_sweep: a cell neighbourhood does not fit into shared memory");
+
+    RP_CUDA(cudaEventRecord(ev[2], st));
+    if (I.hard == RP_HARD_SPHERE) launchSweep<RP_HARD_SPHERE>(h, A, sg, off, colourOrder, T, dCounters);
+    else launchSweep<RP_HARD_SPHEROCYLINDER>(h, A, sg, off, colourOrder, T, dCounters);
+    RP_CUDA(cudaEventRecord(ev[3], st));
+    h->timing[tslot].pending = true;
+    // {max population, max neighbourhood, cells skipped, peer timeout} of this sweep -> pinned ring, read by a later call
+    {
+        const int slot = h->sweepMaxNext;
+        if (h->sweepMaxPending[slot]) {       // ring full: wait for the oldest
+            RP_CUDA(cudaEventSynchronize(h->sweepMaxEvent[slot]));
+            harvestSweepMaxima(h, false);
+        }
+        k_sweep_report<<<1, 32, 0, st>>>(h->dFlags, h->sweepMaxPinned + 4 * slot, h->dCounters, dAcc);
+        RP_CUDA(cudaEventRecord(h->sweepMaxEvent[slot], st));
+        h->sweepMaxPending[slot] = true;
+        h->sweepMaxNext = (slot + 1) % 4;
+        h->launches++;
+    }
     h->gridDirty = true;       // particles moved: the reference-geometry grid is rebuilt before its next use
     h->hasTrial = false;
-    if (flags[3])
-        throw rp_error(RP_ERR_CAPACITY, "rp_sweep: shared-memory staging capacity exceeded (cells skipped)");
     h->lastSweepValid = true;
     h->lastSweepGeneric = false;
     h->lastRecw = 6;
     if (out) {
+        // the synchronous form: counters of THIS call
+        unsigned long long counters[4];
+        RP_CUDA(cudaMemcpyAsync(counters, dCounters, sizeof(counters), cudaMemcpyDeviceToHost, st));
+        RP_CUDA(cudaStreamSynchronize(st));
+        RP_CUDA(cudaGetLastError());
+        sweepTimings(h, true);
+        const unsigned long long skippedBefore = h->sweepCellsSkipped;
+        harvestSweepMaxima(h, true);
+        if (h->sweepCellsSkipped != skippedBefore)
+            throw rp_error(RP_ERR_CAPACITY, "rp_sweep: shared-memory staging capacity exceeded (cells skipped; the "
+                                            "capacity has been raised, the packing is valid)");
         out->attempted = counters[0];
         out->accepted = counters[1];
         out->rejected_domain = counters[2];
@@ -418,6 +492,37 @@ void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
         out->sub_sweeps = 8;
         out->kernel_launches = 8 + 7;
     }
+}
+
+// device times of the sweeps whose events have completed (block: of all sweeps queued so far) -> lastSweepMs /
+// lastSweepGridMs (the most recent one) and the accumulators the cycle loop reports
+void sweepTimings(Handle *h, bool block) {
+    for (int k = 0; k < TIMING_RING; k++) {
+        // oldest first: slot (sweepSerial + 1 + k) % TIMING_RING
+        Handle::TimingSlot &t = h->timing[(h->sweepSerial + 1 + k) % TIMING_RING];
+        if (!t.pending) continue;
+        if (block) RP_CUDA(cudaEventSynchronize(t.e[3]));
+        else if (cudaEventQuery(t.e[3]) != cudaSuccess) { cudaGetLastError(); continue; }
+        t.pending = false;
+        float msGrid = 0, msSweep = 0;
+        cudaEventElapsedTime(&msGrid, t.e[0], t.e[1]);
+        cudaEventElapsedTime(&msSweep, t.e[2], t.e[3]);
+        h->lastSweepMs = msSweep;
+        h->lastSweepGridMs = msGrid;
+        h->accSweepMs += msSweep;
+        h->accSweepGridMs += msGrid;
+    }
+}
+
+void sweepHarvest(Handle *h, bool block) { harvestSweepMaxima(h, block); }
+
+bool sweepIsQueued(const Handle *h, int kind) {
+    return fastPathEligible(h) && kind != RP_MOVE_FLIP;
+}
+
+void sweep(Handle *h, const rp_sweep_params &p, rp_sweep_counters *out) {
+    rp_sweep_counters local;
+    sweepAsync(h, p, nullptr, out ? out : &local);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -440,7 +545,7 @@ static GenLayout genLayout(const Inter &I) {
 }
 
 static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &sg, const int colourOrder[8],
-                         const int refN[3], rp_sweep_counters *out)
+                         const int refN[3], rp_sweep_counters *out, cudaEvent_t *ev)
 {
     const Inter &I = h->inter;
     GridStore &g = h->sgrid;
@@ -489,7 +594,7 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
     k_gen_records<<<recBlocks, 256, 0, st>>>(g.numCells, A, sg, h->box, h->dInter, g.cellStart, g.itemsTmp, g.keys,
                                              h->pos, h->orient, h->crel, g.items, h->genRec);
     h->launches++;
-    RP_CUDA(cudaEventRecord(h->ev[1], st));
+    RP_CUDA(cudaEventRecord(ev[1], st));
     int flags[4];
     RP_CUDA(cudaMemcpyAsync(flags, h->dFlags, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
     RP_CUDA(cudaStreamSynchronize(st));
@@ -505,7 +610,7 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
                                      static_cast<int>(std::max<size_t>(smem, 48 * 1024))));
         configured = std::max<size_t>(smem, 48 * 1024);
     }
-    RP_CUDA(cudaEventRecord(h->ev[2], st));
+    RP_CUDA(cudaEventRecord(ev[2], st));
     k_gen_trials<<<(n + 127) / 128, 128, 0, st>>>(n, A, sg, h->box, h->dInter, g.items, g.keys, h->genRec, h->orient,
                                                   h->crel, T, makeWalls(h->box, h->wallMask, I.totalRange), h->pos);
     h->launches++;
@@ -518,17 +623,19 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
                                                        h->pos, h->orient, h->crel, h->cabs, h->dCounters, h->dFlags);
         h->launches++;
     }
-    RP_CUDA(cudaEventRecord(h->ev[3], st));
+    RP_CUDA(cudaEventRecord(ev[3], st));
     unsigned long long counters[6];
     RP_CUDA(cudaMemcpyAsync(counters, h->dCounters, sizeof(counters), cudaMemcpyDeviceToHost, st));
     RP_CUDA(cudaMemcpyAsync(flags, h->dFlags, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
     RP_CUDA(cudaStreamSynchronize(st));
     RP_CUDA(cudaGetLastError());
     float msGrid = 0, msSweep = 0;
-    cudaEventElapsedTime(&msGrid, h->ev[0], h->ev[1]);
-    cudaEventElapsedTime(&msSweep, h->ev[2], h->ev[3]);
+    cudaEventElapsedTime(&msGrid, ev[0], ev[1]);
+    cudaEventElapsedTime(&msSweep, ev[2], ev[3]);
     h->lastSweepMs = msSweep;
     h->lastSweepGridMs = msGrid;
+    h->accSweepMs += msSweep;
+    h->accSweepGridMs += msGrid;
     h->gridDirty = true;
     h->hasTrial = false;
     if (flags[3])

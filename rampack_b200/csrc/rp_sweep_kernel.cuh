@@ -31,21 +31,13 @@
 
 namespace rp {
 
-struct SweepGrid {
-    int n[3];
-    double relCell[3];     // 1 / n[i]
-    double shift[3];       // random relative origin s
-    V3 imageShift[8];      // M * f for f = (fx, fy, fz) in {0,1}^3, index fx + 2 fy + 4 fz
-    V3 trans[27];
-};
-
 // staging order of the 27 neighbour cells (codes (dz+1)*9 + (dy+1)*3 + (dx+1)): own cell, faces, edges, corners
 __device__ const unsigned char SW_STAGE_ORDER[27] = {13, 4, 10, 12, 14, 16, 22, 1, 3, 5, 7, 9, 11, 15, 17, 19, 21, 23, 25,
                                                      0, 2, 6, 8, 18, 20, 24, 26};
 constexpr int SW_MAXOWN = 64;      // trials resolved together (bit matrices are 64 bits wide)
-constexpr int SW_PUSH = 4;         // queue entries a lane may push per round
-constexpr int SW_WQCAP1 = 32 * SW_PUSH + 64;    // per-warp queue of (trial, candidate) pairs that passed the first cull
-constexpr int SW_WQCAP = SW_WQCAP1 + 128;       // ... followed by the queue of pairs awaiting the exact test
+constexpr int SW_PUSH = 4;         // queue entries a lane may push per round when a chunk's survivors do not fit
+constexpr int SW_WQCAP1 = 32 * SW_PUSH + 96;    // per-warp queue of (trial, candidate) pairs that passed the first cull
+constexpr int SW_WQCAP = SW_WQCAP1 + 96;        // ... followed by the queue of pairs awaiting the exact test
 
 // the few interaction constants the sweep kernels need (rp::Inter thresholds, computed on the host with the
 // reference's expressions), passed by value
@@ -77,7 +69,28 @@ struct TrialBuffers {
     double *rec;                // 6 doubles per slot: new position (image frame), new half axis
     double *orient;             // 9 doubles per slot: new orientation (only written for rotating samplers)
     uint2 *meta;                // x: 0 alive / 2 left the cell, y: random key of the processing order
+    float4 *rec32;              // 2 float4 per slot: the FP32 cull record of the new state (Rec32 below)
 };
+
+// FP32 cull record of one particle state, 32 bytes (two float4): {x, y, z, ux} {uy, uz, 0, 0} — position relative to
+// the CENTRE OF THE PARTICLE'S OWN sweep cell (image frame) and the unit axis (spherocylinders).  Only the two
+// conservative culls read it; the exact test reads the FP64 record.  A CTA that stages a neighbour cell adds the
+// centre-to-centre vector of the two cells (SweepCellOffsets, the same for every active cell), which also carries
+// the lattice translation of a periodic image.
+struct SweepCellOffsets { float o[27][3]; };      // index = neighbour code (dz+1)*9 + (dy+1)*3 + (dx+1)
+
+// centre of sweep cell (cx, cy, cz) in the image frame of the shifted origin
+RP_HD V3 sweepCellCentre(const SweepGrid &sg, const Box &box, int cx, int cy, int cz) {
+    return relToAbs(box, v3((cx + 0.5) * sg.relCell[0] + sg.shift[0], (cy + 0.5) * sg.relCell[1] + sg.shift[1],
+                            (cz + 0.5) * sg.relCell[2] + sg.shift[2]));
+}
+// the one expression every producer of a cull record uses (prepare kernel, sharded apply kernels): identical inputs
+// give identical records on every rank
+__device__ __forceinline__ void makeRec32(const V3 &p, const V3 &h, const V3 &centre, float invHalf, float4 *out) {
+    out[0] = make_float4(static_cast<float>(p.x - centre.x), static_cast<float>(p.y - centre.y),
+                         static_cast<float>(p.z - centre.z), static_cast<float>(h.x) * invHalf);
+    out[1] = make_float4(static_cast<float>(h.y) * invHalf, static_cast<float>(h.z) * invHalf, 0.f, 0.f);
+}
 
 // ---- 1-D TMA bulk copy + mbarrier (PTX ISA: cp.async.bulk, mbarrier) ----
 __device__ __forceinline__ unsigned int smemAddr(const void *p) {
@@ -158,93 +171,161 @@ __device__ __forceinline__ bool segmentCullPass(const double *__restrict__ c, co
     return !(fmaf(pz, pz, fmaf(py, py, px * px)) >= thr2);        // NaN passes
 }
 
+// FP32 segment-segment cull on two cull records (same formula as segmentCullPass; d = trial - candidate)
+__device__ __forceinline__ bool segmentCullPass32(const float4 ca, const float4 cb, const float4 ta, const float4 tb,
+                                                  float half, float thr2)
+{
+    const float dx = ta.x - ca.x, dy = ta.y - ca.y, dz = ta.z - ca.z;
+    const float h1x = ta.w * half, h1y = tb.x * half, h1z = tb.y * half;
+    const float h2x = ca.w * half, h2y = cb.x * half, h2z = cb.y * half;
+    const float a = half * half;                                  // |h1|^2 = |h2|^2
+    const float b = fmaf(h1z, h2z, fmaf(h1y, h2y, h1x * h2x));
+    const float cc = fmaf(h1z, dz, fmaf(h1y, dy, h1x * dx));
+    const float f = fmaf(h2z, dz, fmaf(h2y, dy, h2x * dx));
+    const float denom = fmaf(a, a, -b * b);
+    const float inva = a > 0.f ? __fdividef(1.0f, a) : 0.f;      // length 0: both parameters stay 0
+    float s = __fdividef(fmaf(b, f, -cc * a), fmaxf(denom, 1e-20f));    // nearly parallel: the SIGN still decides the end
+    s = fminf(fmaxf(s, -1.0f), 1.0f);
+    const float t0 = fmaf(b, s, f) * inva;
+    const float t = fminf(fmaxf(t0, -1.0f), 1.0f);
+    const float s1 = fminf(fmaxf(fmaf(b, t, -cc) * inva, -1.0f), 1.0f);
+    s = (t != t0) ? s1 : s;
+    const float px = fmaf(-t, h2x, fmaf(s, h1x, dx)), py = fmaf(-t, h2y, fmaf(s, h1y, dy)),
+                pz = fmaf(-t, h2z, fmaf(s, h1z, dz));
+    return !(fmaf(pz, pz, fmaf(py, py, px * px)) >= thr2);        // NaN passes
+}
+
 // ---------------------------------------------------------------------------------------------------------------
-// trial moves of all particles: MoveSampler::sampleMove distributions (core/move_samplers/*.cpp), Shape::translate /
-// rotate (core/Shape.cpp:9-16), ActiveDomain::isInside with the checkerboard cell as the domain (Packing.cpp:95-96)
+// k_sweep_prepare — one warp per sweep-grid cell, once per rp_sweep call.  Fuses what used to be two gather passes
+// over the canonical arrays:
+//   records  order the cell's items by ascending particle index (deterministic whatever the scatter atomics did),
+//            write the 48-byte FP64 record {P', h} (image frame; h = orientation.column(2) * (l / 2)) and the 32-byte
+//            FP32 cull record;
+//   trials   MoveSampler::sampleMove distributions (core/move_samplers/*.cpp), Shape::translate / rotate
+//            (core/Shape.cpp:9-16), ActiveDomain::isInside with the checkerboard cell as the domain
+//            (Packing.cpp:95-96): trial FP64 record, trial cull record, new orientation, {reject flag, order key};
+//   sizing   the population of the cell's 27-neighbourhood (shared-memory capacity of k_sweep).
 // ---------------------------------------------------------------------------------------------------------------
 template <int HARD>
-__global__ void __launch_bounds__(128) k_sweep_trials(int n, SweepArgs A, SweepGrid sg, Box box, double halfLength,
-                                                      const int *__restrict__ items, const int *__restrict__ keys,
-                                                      const double *__restrict__ rec,
-                                                      const double *__restrict__ orient, TrialBuffers T, Walls W,
-                                                      double radius)
+__global__ void __launch_bounds__(256) k_sweep_prepare(int numCells, SweepArgs A, SweepGrid sg, Box box,
+                                                       double halfLength, const int *__restrict__ cellStart,
+                                                       const int *__restrict__ itemsTmp,
+                                                       const int *__restrict__ keys, const double *__restrict__ pos,
+                                                       const double *__restrict__ orient, int *__restrict__ items,
+                                                       double *__restrict__ rec, float4 *__restrict__ rec32,
+                                                       TrialBuffers T, Walls W, double radius,
+                                                       int *__restrict__ maxNeigh)
 {
-    const int slot = A.slotBegin + blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot >= A.slotEnd || slot >= n) return;
-    const int particleId = items[slot];
-    const int cell = keys[particleId] & 0x0FFFFFFF;
+    const int cell = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (cell >= numCells) return;
+    const int start = cellStart[cell], cnt = cellStart[cell + 1] - start;
     const int cc[3] = {cell % sg.n[0], (cell / sg.n[0]) % sg.n[1], cell / (sg.n[0] * sg.n[1])};
-    const double *r = rec + 6 * static_cast<size_t>(slot);
-    V3 p = v3(r[0], r[1], r[2]);
-    V3 h = v3(r[3], r[4], r[5]);
+    const V3 centre = sweepCellCentre(sg, box, cc[0], cc[1], cc[2]);
+    const float invHalfF = (HARD == RP_HARD_SPHEROCYLINDER && A.cullHalf > 0.f) ? __fdividef(1.0f, A.cullHalf) : 0.f;
     const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION);
     const bool translated = (A.kind == RP_MOVE_TRANSLATION || A.kind == RP_MOVE_ROTOTRANSLATION);
-    Rng rng;
-    rng.init(A.seed, static_cast<unsigned int>(particleId), A.cycle, A.pass);
-    unsigned int rej = 0;
-    if (translated) {
-        // TranslationSampler / RototranslationSampler: 3 x U(-step, step)  (RototranslationSampler.cpp:31-33)
-        double tx = rng.uniform(-A.transStep, A.transStep);
-        double ty = rng.uniform(-A.transStep, A.transStep);
-        double tz = rng.uniform(-A.transStep, A.transStep);
-        p = p + v3(tx, ty, tz);
-        // the new mass centre must stay in its cell (image frame of the shifted origin)
-        V3 rel = absToRel(box, p);
-        double q[3] = {rel.x - sg.shift[0], rel.y - sg.shift[1], rel.z - sg.shift[2]};
-        for (int d = 0; d < 3; d++) {
-            if (q[d] < 0 || q[d] >= 1) rej = 2;
-            else if (static_cast<int>(q[d] / sg.relCell[d]) != cc[d]) rej = 2;
-        }
-    }
-    if (rotated) {
-        // axis uniform in the unit ball by rejection, angle U(-a, a) (RototranslationSampler.cpp:35-43);
-        // Rodrigues: identity + K*sina + ((1 - cosa)*K)*K (geometry/Matrix.tpp:437-449)
-        V3 axis;
-        double n2;
-        do {
-            axis = v3(rng.uniform(-1, 1), rng.uniform(-1, 1), rng.uniform(-1, 1));
-            n2 = norm2(axis);
-        } while (n2 > 1 || n2 == 0);
-        double nrm = sqrt(n2);
-        axis = v3(axis.x / nrm, axis.y / nrm, axis.z / nrm);
-        double angle = rng.uniform(-A.rotStep, A.rotStep);
-        double sina = sin(angle), cosa = cos(angle);
-        M33 K = {{0, -axis.z, axis.y, axis.z, 0, -axis.x, -axis.y, axis.x, 0}};
-        M33 sK;
-        for (int q = 0; q < 9; q++) sK.a[q] = (1 - cosa) * K.a[q];
-        M33 KK = mul(sK, K);
-        M33 R;
-        for (int q = 0; q < 9; q++) R.a[q] = (((q % 4 == 0) ? 1.0 : 0.0) + K.a[q] * sina) + KK.a[q];
+    for (int i = lane; i < cnt; i += 32) {
+        const int particleId = itemsTmp[start + i];
+        int rank = 0;
+        for (int j = 0; j < cnt; j++) rank += (itemsTmp[start + j] < particleId);
+        const int slot = start + rank;
+        items[slot] = particleId;
+        const int f = (keys[particleId] >> 28) & 7;
+        V3 p = v3(pos[particleId], pos[A.cap + particleId], pos[2 * A.cap + particleId]);
+        if (f) p = p + sg.imageShift[f];
         M33 O;
-        for (int q = 0; q < 9; q++) O.a[q] = orient[q * A.cap + particleId];
-        M33 newOrient = mul(R, O);     // Shape::rotate (core/Shape.cpp:14-16)
-        if (HARD == RP_HARD_SPHEROCYLINDER) h = column(newOrient, 2) * halfLength;
-        double *o = T.orient + 9 * static_cast<size_t>(slot);
-        for (int q = 0; q < 9; q++) o[q] = newOrient.a[q];
-    }
-    if (W.mask && rej == 0) {
-        // hard walls (Packing::countParticleWallOverlaps, core/Packing.cpp:1086-1142, with the sphere / spherocylinder
-        // overlapWithWall): a trial touching a wall is rejected like an overlap with a frozen particle.  The test
-        // runs on the wrapped position the write-back would store.
-        V3 cp = p + pbcCorrection(box, p);
-        for (int i = 0; i < 3; i++) {
-            if (!((W.mask >> i) & 1)) continue;
-            V3 wv = W.normal[i], origin;
-            if (dot(cp, wv) < W.halfTotalRange) origin = v3(0, 0, 0);
-            else if (dot(W.furtherOrigin - cp, wv) < W.halfTotalRange) {
-                origin = W.furtherOrigin;
-                wv = v3(-wv.x, -wv.y, -wv.z);
-            } else continue;
-            bool hit;
-            if (HARD == RP_HARD_SPHERE) hit = dot(wv, cp - origin) < radius;
-            else hit = dot(wv, (cp + h) - origin) < radius || dot(wv, (cp - h) - origin) < radius;
-            if (hit) rej = 1;
+        V3 h = v3(0, 0, 0);
+        if (rotated) {
+            #pragma unroll
+            for (int q = 0; q < 9; q++) O.a[q] = orient[q * A.cap + particleId];
+            if (HARD == RP_HARD_SPHEROCYLINDER) h = column(O, 2) * halfLength;
+        } else if (HARD == RP_HARD_SPHEROCYLINDER) {
+            // half axis h = orientation.column(2) * (0.5 * l): the cap centres are pos -+ h (SpherocylinderTraits.cpp:24-26)
+            h = v3(orient[2 * A.cap + particleId], orient[5 * A.cap + particleId], orient[8 * A.cap + particleId])
+                * halfLength;
         }
+        double *r = rec + 6 * static_cast<size_t>(slot);
+        r[0] = p.x; r[1] = p.y; r[2] = p.z; r[3] = h.x; r[4] = h.y; r[5] = h.z;
+        makeRec32(p, h, centre, invHalfF, rec32 + 2 * static_cast<size_t>(slot));
+        if (slot < A.slotBegin || slot >= A.slotEnd) continue;       // sharded over NCCL: another rank's trial
+
+        // ---- the trial move of this particle ----
+        Rng rng;
+        rng.init(A.seed, static_cast<unsigned int>(particleId), A.cycle, A.pass);
+        unsigned int rej = 0;
+        if (translated) {
+            // TranslationSampler / RototranslationSampler: 3 x U(-step, step)  (RototranslationSampler.cpp:31-33)
+            double tx = rng.uniform(-A.transStep, A.transStep);
+            double ty = rng.uniform(-A.transStep, A.transStep);
+            double tz = rng.uniform(-A.transStep, A.transStep);
+            p = p + v3(tx, ty, tz);
+            // the new mass centre must stay in its cell (image frame of the shifted origin)
+            V3 rel = absToRel(box, p);
+            double q[3] = {rel.x - sg.shift[0], rel.y - sg.shift[1], rel.z - sg.shift[2]};
+            for (int d = 0; d < 3; d++) {
+                if (q[d] < 0 || q[d] >= 1) rej = 2;
+                else if (static_cast<int>(q[d] / sg.relCell[d]) != cc[d]) rej = 2;
+            }
+        }
+        if (rotated) {
+            // axis uniform in the unit ball by rejection, angle U(-a, a) (RototranslationSampler.cpp:35-43);
+            // Rodrigues: identity + K*sina + ((1 - cosa)*K)*K (geometry/Matrix.tpp:437-449)
+            V3 axis;
+            double n2;
+            do {
+                axis = v3(rng.uniform(-1, 1), rng.uniform(-1, 1), rng.uniform(-1, 1));
+                n2 = norm2(axis);
+            } while (n2 > 1 || n2 == 0);
+            double nrm = sqrt(n2);
+            axis = v3(axis.x / nrm, axis.y / nrm, axis.z / nrm);
+            double angle = rng.uniform(-A.rotStep, A.rotStep);
+            double sina = sin(angle), cosa = cos(angle);
+            M33 K = {{0, -axis.z, axis.y, axis.z, 0, -axis.x, -axis.y, axis.x, 0}};
+            M33 sK;
+            for (int q = 0; q < 9; q++) sK.a[q] = (1 - cosa) * K.a[q];
+            M33 KK = mul(sK, K);
+            M33 R;
+            for (int q = 0; q < 9; q++) R.a[q] = (((q % 4 == 0) ? 1.0 : 0.0) + K.a[q] * sina) + KK.a[q];
+            M33 newOrient = mul(R, O);     // Shape::rotate (core/Shape.cpp:14-16)
+            if (HARD == RP_HARD_SPHEROCYLINDER) h = column(newOrient, 2) * halfLength;
+            double *o = T.orient + 9 * static_cast<size_t>(slot);
+            for (int q = 0; q < 9; q++) o[q] = newOrient.a[q];
+        }
+        if (W.mask && rej == 0) {
+            // hard walls (Packing::countParticleWallOverlaps, core/Packing.cpp:1086-1142, with the sphere / spherocylinder
+            // overlapWithWall): a trial touching a wall is rejected like an overlap with a frozen particle.  The test
+            // runs on the wrapped position the write-back would store.
+            V3 cp = p + pbcCorrection(box, p);
+            for (int i2 = 0; i2 < 3; i2++) {
+                if (!((W.mask >> i2) & 1)) continue;
+                V3 wv = W.normal[i2], origin;
+                if (dot(cp, wv) < W.halfTotalRange) origin = v3(0, 0, 0);
+                else if (dot(W.furtherOrigin - cp, wv) < W.halfTotalRange) {
+                    origin = W.furtherOrigin;
+                    wv = v3(-wv.x, -wv.y, -wv.z);
+                } else continue;
+                bool hit;
+                if (HARD == RP_HARD_SPHERE) hit = dot(wv, cp - origin) < radius;
+                else hit = dot(wv, (cp + h) - origin) < radius || dot(wv, (cp - h) - origin) < radius;
+                if (hit) rej = 1;
+            }
+        }
+        double *t = T.rec + 6 * static_cast<size_t>(slot);
+        t[0] = p.x; t[1] = p.y; t[2] = p.z; t[3] = h.x; t[4] = h.y; t[5] = h.z;
+        makeRec32(p, h, centre, invHalfF, T.rec32 + 2 * static_cast<size_t>(slot));
+        rng.ctr.w = 0x40000000u;     // separate sub-stream for the processing order
+        T.meta[slot] = make_uint2(rej, philox4x32(rng.ctr, rng.k0, rng.k1).x);
     }
-    double *t = T.rec + 6 * static_cast<size_t>(slot);
-    t[0] = p.x; t[1] = p.y; t[2] = p.z; t[3] = h.x; t[4] = h.y; t[5] = h.z;
-    rng.ctr.w = 0x40000000u;     // separate sub-stream for the processing order
-    T.meta[slot] = make_uint2(rej, philox4x32(rng.ctr, rng.k0, rng.k1).x);
+    // population of the 27-neighbourhood (smem sizing of the sweep kernel)
+    int sum = 0;
+    if (lane < 27) {
+        int tIdx;
+        int c2 = neighbourCell(sg.n, cc[0], cc[1], cc[2], lane / 9 - 1, (lane / 3) % 3 - 1, lane % 3 - 1, &tIdx);
+        sum = cellStart[c2 + 1] - cellStart[c2];
+    }
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0) atomicMax(maxNeigh, sum);
 }
 
 }  // namespace rp

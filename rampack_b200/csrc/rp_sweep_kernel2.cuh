@@ -1,19 +1,26 @@
 // rp_sweep_kernel2.cuh — k_sweep, the per-colour sub-sweep kernel (see rp_sweep_kernel.cuh for the overview)
+//
+// Round-2 layout: the two conservative culls run on 32-byte FP32 cull records (position relative to the cell centre +
+// unit axis) that the prepare kernel wrote next to the FP64 records; only those are staged in shared memory (TMA bulk
+// copies, one per neighbour cell).  The exact FP64 test — the only stage that decides anything — fetches the FP64
+// records of the few surviving pairs (2-3 per trial) from global memory (L2).  Against staging the FP64 records this
+// takes a third off the staging traffic and the shared memory per CTA, removes every FP64 -> FP32 conversion from the
+// cull loops and lets 5-6 CTAs share an SM instead of 4, so that one CTA's serial sections (set-up, sequential
+// resolution, write-back) run under the other CTAs' culls.
 #pragma once
 
 namespace rp {
 
-template <int HARD, int THREADS>
-__global__ void __launch_bounds__(THREADS, THREADS == 256 ? 3 : 4)
-k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
-        const int *__restrict__ items, double *__restrict__ rec, TrialBuffers T, double *__restrict__ pos,
+template <int HARD, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
+k_sweep(SweepArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const int *__restrict__ cellStart,
+        const int *__restrict__ items, double *rec, float4 *rec32, TrialBuffers T, double *__restrict__ pos,
         double *__restrict__ orient, unsigned long long *__restrict__ counters, int *__restrict__ flags,
         PeerView peers)
 {
     constexpr int WARPS = THREADS / 32;
     extern __shared__ __align__(16) unsigned char smemRaw[];
-    __shared__ float4 trialF[SW_MAXOWN], trialU[SW_MAXOWN];
-    // the same FP32 trial data for the packed (f32x2) cull loop, two trials per entry: (-x0, -x1, -y0, -y1),
+    // FP32 trial data for the packed (f32x2) cull loop, two trials per entry: (-x0, -x1, -y0, -y1),
     // (-z0, -z1, ux0, ux1), (uy0, uy1, uz0, uz1)
     __shared__ float4 trialP[SW_MAXOWN / 2 + 1][3];
     __shared__ unsigned long long ownMask[SW_MAXOWN], newMask[SW_MAXOWN], seqOwn[SW_MAXOWN], seqNew[SW_MAXOWN];
@@ -22,14 +29,16 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
     __shared__ int rejected[SW_MAXOWN];     // 0 = alive, 1 = overlap with a frozen particle, 2 = left the cell
     __shared__ unsigned long long sAccepted, sRejMask, sBar;
     __shared__ int sDomain;
-    __shared__ int cellBegin[28], cellT[27];
+    __shared__ int cellBegin[28], cellT[27], cellSrc[27];
     __shared__ int sStats[3];
     __shared__ int qCount;
 
-    // dynamic shared memory: FP64 records (old states, then the trial = new states of the own cell), the warp queues
+    // dynamic shared memory: FP32 cull records (old states of the 27 cells, then the trial = new states of the own
+    // cell), the FP64 trial records of the own cell, the warp queues
     const int capCand = A.capOld + A.capOwn;
-    double *cand = reinterpret_cast<double *>(smemRaw);
-    unsigned int *queue = reinterpret_cast<unsigned int *>(cand + 6 * static_cast<size_t>(capCand));
+    float4 *cand32 = reinterpret_cast<float4 *>(smemRaw);
+    double *trial64 = reinterpret_cast<double *>(cand32 + 2 * static_cast<size_t>(capCand));
+    unsigned int *queue = reinterpret_cast<unsigned int *>(trial64 + 6 * static_cast<size_t>(A.capOwn));
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const SweepInter &I = A.inter;
@@ -60,7 +69,7 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
             mbarInit(&sBar, 1);
         }
         // exclusive scan of the 27 cell populations -> staging offsets; every lane then issues the 1-D TMA bulk copy
-        // of its own cell (lane 27: the trial records of the own cell)
+        // of its own cell (lanes 27 / 28: the FP32 / FP64 trial records of the own cell)
         int incl = cnt;
         #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -71,17 +80,22 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
         ownStartAll = __shfl_sync(0xffffffffu, src, 0);
         ownCountAll = __shfl_sync(0xffffffffu, cnt, 0);
         const bool ok = ownCountAll > 0 && total <= A.capOld && ownCountAll <= A.capOwn;
-        if (lane == 0 && ok) mbarExpectTx(&sBar, static_cast<unsigned int>((total + ownCountAll) * 48));
+        if (lane == 0 && ok)
+            mbarExpectTx(&sBar, static_cast<unsigned int>((total + ownCountAll) * 32 + ownCountAll * 48));
         __syncwarp();
         if (lane < 27) {
             cellBegin[lane] = incl - cnt;
             cellT[lane] = tIdx;
+            cellSrc[lane] = src;
             if (lane == 26) cellBegin[27] = incl;
             if (ok && cnt > 0)
-                bulkCopyG2S(cand + 6 * static_cast<size_t>(incl - cnt), rec + 6 * static_cast<size_t>(src),
-                            static_cast<unsigned int>(cnt * 48), &sBar);
+                bulkCopyG2S(cand32 + 2 * static_cast<size_t>(incl - cnt), rec32 + 2 * static_cast<size_t>(src),
+                            static_cast<unsigned int>(cnt * 32), &sBar);
         } else if (lane == 27 && ok) {
-            bulkCopyG2S(cand + 6 * static_cast<size_t>(total), T.rec + 6 * static_cast<size_t>(ownStartAll),
+            bulkCopyG2S(cand32 + 2 * static_cast<size_t>(total), T.rec32 + 2 * static_cast<size_t>(ownStartAll),
+                        static_cast<unsigned int>(ownCountAll * 32), &sBar);
+        } else if (lane == 28 && ok) {
+            bulkCopyG2S(trial64, T.rec + 6 * static_cast<size_t>(ownStartAll),
                         static_cast<unsigned int>(ownCountAll * 48), &sBar);
         }
     } else {
@@ -95,56 +109,77 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
     const int numOld = cellBegin[27], ownBeginAll = cellBegin[0], numOwnAll = cellBegin[1] - cellBegin[0];
     if (numOwnAll == 0) return;
     if (numOld > A.capOld || numOwnAll > A.capOwn) {
-        if (tid == 0) atomicOr(&flags[3], 1);
+        // the staging capacity (sized from the previous sweeps' maxima) is too small for this cell: its trials are not
+        // attempted in this sweep; the host learns the count and raises the capacity.  Sharded: the other ranks must
+        // not replay stale accept bytes for these slots.
+        if (tid == 0) atomicAdd(&flags[3], 1);
+        for (int i = tid; i < numOwnAll; i += THREADS) {
+            #pragma unroll
+            for (int pr = 0; pr < SHARD_MAX_PEERS; pr++)
+                if (pr < peers.n) peers.acc[pr][cellSrc[0] + i] = 0;
+        }
         return;
     }
 
-    // origin of the FP32 local frame: centre of the active cell (image frame)
-    const V3 origin = relToAbs(box, v3((cx + 0.5) * sg.relCell[0] + sg.shift[0], (cy + 0.5) * sg.relCell[1] + sg.shift[1],
-                                       (cz + 0.5) * sg.relCell[2] + sg.shift[2]));
     if (warp == 0) mbarWait(&sBar, 0);       // the other warps park at the CTA barrier instead of spinning
     __syncthreads();
 
-    // ---- second staging pass (shared memory only): pos2 + lattice translation (HardcodedTranslation) ----
-    for (int c = warp; c < 27; c += WARPS) {
-        if (cellT[c] == 13) continue;        // translation (0, 0, 0): pos2 + 0 == pos2
+    // ---- second staging pass (shared memory only): neighbour cells move from their own cell-centred frame into the
+    // frame of the active cell (FP32; the periodic image translation is part of the centre-to-centre vector) ----
+    for (int c = 1 + warp; c < 27; c += WARPS) {        // c = 0 is the own cell
         const int begin = cellBegin[c], cnt = cellBegin[c + 1] - begin;
-        const V3 t = sg.trans[cellT[c]];
+        const int code = SW_STAGE_ORDER[c];
+        const float ox = off.o[code][0], oy = off.o[code][1], oz = off.o[code][2];
         for (int j = begin + lane; j < begin + cnt; j += 32) {
-            double *r = cand + 6 * static_cast<size_t>(j);
-            r[0] += t.x; r[1] += t.y; r[2] += t.z;
+            float4 r = cand32[2 * j];
+            r.x += ox; r.y += oy; r.z += oz;
+            cand32[2 * j] = r;
         }
     }
 
-    // (a spherocylinder of length 0 is admissible, SpherocylinderTraits.cpp:15: its unit axis is irrelevant, not NaN)
-    const float invHalfF = (HARD == RP_HARD_SPHEROCYLINDER && A.cullHalf > 0.f) ? __fdividef(1.0f, A.cullHalf) : 0.f;
     const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION);
     const bool translated = (A.kind == RP_MOVE_TRANSLATION || A.kind == RP_MOVE_ROTOTRANSLATION);
 
+    // FP64 record of staged candidate c (old states: from the sorted records in global memory + the lattice
+    // translation of its cell, exactly the reference's pos2 + translation; new states: the staged trial records)
+    auto loadCandidate64 = [&](int c, double *out) {
+        if (c >= numOld) {
+            const double *s = trial64 + 6 * static_cast<size_t>(c - numOld);
+            #pragma unroll
+            for (int q = 0; q < 6; q++) out[q] = s[q];
+            return;
+        }
+        int ci = 0;      // staged cell of c: last ci with cellBegin[ci] <= c
+        #pragma unroll
+        for (int step = 16; step > 0; step >>= 1)
+            if (ci + step < 27 && cellBegin[ci + step] <= c) ci += step;
+        const double2 *s = reinterpret_cast<const double2 *>(rec + 6 * static_cast<size_t>(cellSrc[ci] + (c - cellBegin[ci])));
+        const double2 s0 = s[0], s1 = s[1], s2 = s[2];
+        out[0] = s0.x; out[1] = s0.y; out[2] = s1.x; out[3] = s1.y; out[4] = s2.x; out[5] = s2.y;
+        const int ti = cellT[ci];
+        if (ti != 13) {      // translation (0, 0, 0): pos2 + 0 == pos2
+            const V3 t = sg.trans[ti];
+            out[0] += t.x; out[1] += t.y; out[2] += t.z;
+        }
+    };
+
     // A cell with more than SW_MAXOWN particles is processed in batches of SW_MAXOWN trials; the particles of the
-    // other batches are frozen candidates meanwhile (their accepted states are patched into shared memory).
+    // other batches are frozen candidates meanwhile (accepted states go to the global records and to the staged cull
+    // records at the end of a batch).
     for (int batch0 = 0; batch0 < numOwnAll; batch0 += SW_MAXOWN) {
         const int numOwn = min(SW_MAXOWN, numOwnAll - batch0);
         const int ownBegin = ownBeginAll + batch0, ownStart = ownStartAll + batch0;
-        const int newBegin = numOld + batch0;          // new states of this batch's trials inside cand[]
+        const int newBegin = numOld + batch0;          // new states of this batch's trials inside cand32[]
         const int numCand = numOld + numOwn;
 
         if (tid == 0) { sAccepted = 0ull; sRejMask = 0ull; qCount = 0; sDomain = 0; }
         __syncthreads();       // staging passes done (first batch) / previous batch fully written back
         if (tid < numOwn) {
             const uint2 meta = batch0 == 0 ? metaFirst : T.meta[ownStart + tid];
-            const double *r = cand + 6 * static_cast<size_t>(newBegin + tid);
-            V3 p = v3(r[0], r[1], r[2]), h = v3(r[3], r[4], r[5]);
-            trialF[tid] = make_float4(static_cast<float>(p.x - origin.x), static_cast<float>(p.y - origin.y),
-                                      static_cast<float>(p.z - origin.z), 0.f);
-            if (HARD == RP_HARD_SPHEROCYLINDER)      // FP32 unit axis of the trial for the capsule cull
-                trialU[tid] = make_float4(static_cast<float>(h.x) * invHalfF, static_cast<float>(h.y) * invHalfF,
-                                          static_cast<float>(h.z) * invHalfF, 0.f);
-            {
-                float *tp = reinterpret_cast<float *>(&trialP[tid >> 1][0]) + (tid & 1);
-                tp[0] = -trialF[tid].x; tp[2] = -trialF[tid].y; tp[4] = -trialF[tid].z;
-                if (HARD == RP_HARD_SPHEROCYLINDER) { tp[6] = trialU[tid].x; tp[8] = trialU[tid].y; tp[10] = trialU[tid].z; }
-            }
+            const float4 ra = cand32[2 * (newBegin + tid)], rb = cand32[2 * (newBegin + tid) + 1];
+            float *tp = reinterpret_cast<float *>(&trialP[tid >> 1][0]) + (tid & 1);
+            tp[0] = -ra.x; tp[2] = -ra.y; tp[4] = -ra.z;
+            if (HARD == RP_HARD_SPHEROCYLINDER) { tp[6] = ra.w; tp[8] = rb.x; tp[10] = rb.y; }
             rejected[tid] = static_cast<int>(meta.x);
             orderKey[tid] = meta.y;
             ownMask[tid] = 0ull;
@@ -178,25 +213,15 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
                 else vrej[ti] = 1;
             }
         };
-        // two independent exact tests per lane: their FP64 dependency chains interleave (the pair arithmetic is
-        // straight-line code), which is what keeps the FP64 pipe fed at 3-4 warps per scheduler
-        auto exactTest2 = [&](unsigned int e0, unsigned int e1, bool v0, bool v1) {
-            const int t0 = e0 >> 16, c0 = e0 & 0xffff, t1 = e1 >> 16, c1 = e1 & 0xffff;
-            v0 = v0 && !vrej[t0];
-            v1 = v1 && !vrej[t1];
-            if (!__any_sync(0xffffffffu, v1)) {        // a short tail: one test per lane
-                if (v0 && exactOverlap<HARD>(I, cand + 6 * static_cast<size_t>(newBegin + t0),
-                                             cand + 6 * static_cast<size_t>(c0)))
-                    record(t0, c0);
-                return;
-            }
-            if (!(v0 || v1)) return;
-            const bool r0 = exactOverlap<HARD>(I, cand + 6 * static_cast<size_t>(newBegin + t0),
-                                               cand + 6 * static_cast<size_t>(c0));
-            const bool r1 = exactOverlap<HARD>(I, cand + 6 * static_cast<size_t>(newBegin + t1),
-                                               cand + 6 * static_cast<size_t>(c1));
-            if (v0 && r0) record(t0, c0);
-            if (v1 && r1) record(t1, c1);
+        // exact FP64 test, one pair per lane (after the two culls the exact stage is a few per cent of the kernel's
+        // instructions: register pressure matters more than the FP64 pipe's latency here)
+        auto exactTest = [&](unsigned int e, bool v) {
+            const int t = e >> 16, c = e & 0xffff;
+            v = v && !vrej[t];
+            if (!v) return;
+            double cr[6];
+            loadCandidate64(c, cr);
+            if (exactOverlap<HARD>(I, trial64 + 6 * static_cast<size_t>(batch0 + t), cr)) record(t, c);
         };
 
         // ---- phases A + B, warp-autonomous (no CTA barrier in between) ----
@@ -213,23 +238,25 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
             int qn = 0, q2n = 0;
             const unsigned int ltMask = (1u << lane) - 1u;
             // B1: conservative FP32 segment-segment cull of 64 queued pairs (two per lane), survivors compacted into
-            // q2 by ballot; B2: the exact FP64 test on every full batch of 64 survivors
+            // q2 by ballot; B2: the exact FP64 test on every full batch of 32 survivors
             auto segmentCull = [&](unsigned int e0, unsigned int e1, bool v0, bool v1) {
                 if (HARD == RP_HARD_SPHEROCYLINDER) {
                     const int t0 = e0 >> 16, c0 = e0 & 0xffff, t1 = e1 >> 16, c1 = e1 & 0xffff;
-                    v0 = v0 && !vrej[t0] && segmentCullPass(cand + 6 * static_cast<size_t>(c0), origin, trialF[t0],
-                                                            trialU[t0], halfF, A.cull2Thr2);
-                    v1 = v1 && !vrej[t1] && segmentCullPass(cand + 6 * static_cast<size_t>(c1), origin, trialF[t1],
-                                                            trialU[t1], halfF, A.cull2Thr2);
+                    v0 = v0 && !vrej[t0]
+                         && segmentCullPass32(cand32[2 * c0], cand32[2 * c0 + 1], cand32[2 * (newBegin + t0)],
+                                              cand32[2 * (newBegin + t0) + 1], halfF, A.cull2Thr2);
+                    v1 = v1 && !vrej[t1]
+                         && segmentCullPass32(cand32[2 * c1], cand32[2 * c1 + 1], cand32[2 * (newBegin + t1)],
+                                              cand32[2 * (newBegin + t1) + 1], halfF, A.cull2Thr2);
                 }
                 const unsigned int b0 = __ballot_sync(0xffffffffu, v0), b1 = __ballot_sync(0xffffffffu, v1);
                 if (v0) q2[q2n + __popc(b0 & ltMask)] = e0;
                 if (v1) q2[q2n + __popc(b0) + __popc(b1 & ltMask)] = e1;
                 q2n += __popc(b0) + __popc(b1);
                 __syncwarp();
-                while (q2n >= 64) {
-                    q2n -= 64;
-                    exactTest2(q2[q2n + lane], q2[q2n + 32 + lane], true, true);
+                while (q2n >= 32) {
+                    q2n -= 32;
+                    exactTest(q2[q2n + lane], true);
                 }
                 __syncwarp();
             };
@@ -244,11 +271,9 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
                 const int j = jj < numOwn ? newBegin + jj : jj - numOwn;      // the new states of the trials first
                 // a far-away dummy for the invalid slots keeps the loop branch-free
                 float cxf = 1e18f, cyf = 0.f, czf = 0.f;
-                if (valid) {         // FP32 copy of the position in cell-local coordinates
-                    const double *r = cand + 6 * static_cast<size_t>(j);
-                    cxf = static_cast<float>(r[0] - origin.x);
-                    cyf = static_cast<float>(r[1] - origin.y);
-                    czf = static_cast<float>(r[2] - origin.z);
+                if (valid) {
+                    const float4 r = cand32[2 * j];
+                    cxf = r.x; cyf = r.y; czf = r.z;
                 }
                 // two trials per iteration with the packed FP32 instructions of sm_100 (FADD2 / FMUL2 / FFMA2): the
                 // same operations in the same order as the scalar form, half the issue slots
@@ -294,36 +319,54 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
                 if (nw >= 0 && nw < numOwn) m &= ~(1ull << nw);
                 m &= ~dead;
 
-                // push: one entry per lane and round, queue slots from a ballot (no scan); whenever 64 entries are
-                // queued they go through the second cull
+                // push: every lane appends all its entries at the offset a warp scan of the counts gives it (one
+                // scan per chunk instead of one ballot round per entry).  A chunk whose survivors would not fit into
+                // the queue goes through in rounds of at most SW_PUSH entries per lane.
+                const unsigned int lowBits = static_cast<unsigned int>(j);
                 #pragma unroll 1
-                for (int half = 0; half < 2; half++) {
-                    unsigned int mm = half ? static_cast<unsigned int>(m >> 32) : static_cast<unsigned int>(m);
-                    unsigned int has;
-                    while ((has = __ballot_sync(0xffffffffu, mm != 0u)) != 0u) {
-                        if (mm != 0u) {
-                            const unsigned int i = static_cast<unsigned int>(__ffs(static_cast<int>(mm)) - 1 + 32 * half);
-                            mm &= mm - 1u;
-                            q[qn + __popc(has & ltMask)] = (i << 16) | static_cast<unsigned int>(j);
+                for (;;) {
+                    int cnt = __popcll(m);
+                    const int total = __reduce_add_sync(0xffffffffu, cnt);
+                    if (total == 0) break;
+                    unsigned long long take = m;
+                    if (qn + total > SW_WQCAP1) {
+                        take = 0ull;
+                        unsigned long long rest = m;
+                        #pragma unroll
+                        for (int e = 0; e < SW_PUSH; e++) {
+                            const unsigned long long low = rest & (~rest + 1ull);
+                            take |= low;
+                            rest ^= low;
                         }
-                        qn += __popc(has);
-                        __syncwarp();
-                        if (qn >= 64) {
-                            qn -= 64;
-                            segmentCull(q[qn + lane], q[qn + 32 + lane], true, true);
-                        }
-                        __syncwarp();
+                        cnt = __popcll(take);
                     }
+                    m ^= take;
+                    int incl = cnt;
+                    #pragma unroll
+                    for (int d = 1; d < 32; d <<= 1) {
+                        const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                        if (lane >= d) incl += v;
+                    }
+                    int at = qn + incl - cnt;
+                    while (take) {
+                        const int i = __ffsll(static_cast<long long>(take)) - 1;
+                        take &= take - 1ull;
+                        q[at++] = (static_cast<unsigned int>(i) << 16) | lowBits;
+                    }
+                    qn += __shfl_sync(0xffffffffu, incl, 31);
+                    __syncwarp();
+                    while (qn >= 64) {
+                        qn -= 64;
+                        segmentCull(q[qn + lane], q[qn + 32 + lane], true, true);
+                    }
+                    __syncwarp();
                 }
             }
             if (qn > 0) {
                 const bool v0 = lane < qn, v1 = lane + 32 < qn;
                 segmentCull(v0 ? q[lane] : 0u, v1 ? q[lane + 32] : 0u, v0, v1);
             }
-            if (q2n > 0) {
-                const bool v0 = lane < q2n, v1 = lane + 32 < q2n;
-                exactTest2(v0 ? q2[lane] : 0u, v1 ? q2[lane + 32] : 0u, v0, v1);
-            }
+            if (q2n > 0) exactTest(lane < q2n ? q2[lane] : 0u, lane < q2n);
         }
 
         // ---- phase C: sequential resolution inside the cell, random order, from the bit matrices ----
@@ -362,16 +405,20 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
         }
         __syncthreads();
 
-        // ---- write-back of the accepted moves: sorted record (image frame) and canonical arrays (wrapped) ----
+        // ---- write-back of the accepted moves: sorted records (image frame) and canonical arrays (wrapped) ----
         if (tid < numOwn && ((sAccepted >> tid) & 1ull)) {
-            const double *t = cand + 6 * static_cast<size_t>(newBegin + tid);
+            const double *t = trial64 + 6 * static_cast<size_t>(batch0 + tid);
+            const float4 ra = cand32[2 * (newBegin + tid)], rb = cand32[2 * (newBegin + tid) + 1];
             double *r = rec + 6 * static_cast<size_t>(ownStart + tid);
             for (int q = 0; q < 6; q++) r[q] = t[q];
+            rec32[2 * static_cast<size_t>(ownStart + tid)] = ra;
+            rec32[2 * static_cast<size_t>(ownStart + tid) + 1] = rb;
             T.meta[ownStart + tid].x = 4u;      // accepted (read back by rp_sweep_trace only)
             if (batch0 + SW_MAXOWN < numOwnAll) {
-                // later batches see this particle as a frozen candidate in its new state (own cell: no translation)
-                double *cs = cand + 6 * static_cast<size_t>(ownBegin + tid);
-                for (int q = 0; q < 6; q++) cs[q] = t[q];
+                // later batches see this particle as a frozen candidate in its new state (own cell: no offset); their
+                // exact tests read the global record written above (ordered by the barrier that ends the batch)
+                cand32[2 * (ownBegin + tid)] = ra;
+                cand32[2 * (ownBegin + tid) + 1] = rb;
             }
             if (translated) {
                 // Shape::translate (core/Shape.cpp:9-12): position += bc.getCorrection(position)
@@ -388,10 +435,14 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
                 if (cz == peers.layerLo) {
                     double *pr_ = peers.recLo + 6 * static_cast<size_t>(ownStart + tid);
                     for (int q = 0; q < 6; q++) pr_[q] = t[q];
+                    peers.rec32Lo[2 * static_cast<size_t>(ownStart + tid)] = ra;
+                    peers.rec32Lo[2 * static_cast<size_t>(ownStart + tid) + 1] = rb;
                 }
                 if (cz == peers.layerHi) {
                     double *pr_ = peers.recHi + 6 * static_cast<size_t>(ownStart + tid);
                     for (int q = 0; q < 6; q++) pr_[q] = t[q];
+                    peers.rec32Hi[2 * static_cast<size_t>(ownStart + tid)] = ra;
+                    peers.rec32Hi[2 * static_cast<size_t>(ownStart + tid) + 1] = rb;
                 }
             }
         }
@@ -402,6 +453,9 @@ k_sweep(SweepArgs A, SweepGrid sg, Box box, const int *__restrict__ cellStart,
             for (int pr = 0; pr < SHARD_MAX_PEERS; pr++)      // (unrolled: no dynamic indexing of the argument)
                 if (pr < peers.n) peers.acc[pr][ownStart + tid] = a;
         }
+        // every read of sAccepted (write-back, accept bytes) precedes the next batch's reset of it, and the records
+        // written above are visible to the next batch's exact tests
+        if (batch0 + SW_MAXOWN < numOwnAll) __syncthreads();
     }   // batches
 
     if (tid == 0) {

@@ -360,6 +360,7 @@ rp_status rp_upload(rp_handle *h, const double box[9], const double *shapes, uin
     h->gridDirty = true;
     h->hasTrial = false;
     h->hasLastScaling = false;
+    h->sweepCapOld = h->sweepCapOwn = 0;      // a new packing: the next queued sweep sizes its staging from its own grid
     if (h->hasInteraction) setupForInteraction(h);
     RP_API_END(h)
 }

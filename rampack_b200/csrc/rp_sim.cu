@@ -28,6 +28,7 @@ struct rp_sim {
     unsigned long long devSeen[4 * RP_SIM_MAX_SAMPLERS] = {};   // device accumulators at the last read
     unsigned long long pendingMoves[RP_SIM_MAX_SAMPLERS] = {};  // attempted moves queued since the last read (estimate)
     double accSweepBase = 0, accGridBase = 0;                   // h->accSweepMs / accSweepGridMs at creation
+    int device = 0;                                             // (the handle may be gone when the rp_sim is destroyed)
 };
 
 namespace {
@@ -283,6 +284,7 @@ rp_status rp_sim_create(rp_handle *h, const rp_sim_config *config, rp_sim **out)
             delete s;
             return RP_ERR_CUDA;
         }
+        s->device = h->device;
         s->accSweepBase = h->accSweepMs;
         s->accGridBase = h->accSweepGridMs;
     }
@@ -293,8 +295,9 @@ rp_status rp_sim_create(rp_handle *h, const rp_sim_config *config, rp_sim **out)
 void rp_sim_destroy(rp_sim *s) {
     if (!s) return;
     if (s->dAcc) {
-        cudaSetDevice(s->h->device);
-        cudaStreamSynchronize(s->h->stream);
+        // no access to the handle here: callers (garbage collectors) may destroy it first.  cudaFree waits for the
+        // device work that may still touch the buffer.
+        cudaSetDevice(s->device);
         cudaFree(s->dAcc);
     }
     delete s;

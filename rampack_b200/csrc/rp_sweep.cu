@@ -414,26 +414,27 @@ void sweepAsync(Handle *h, const rp_sweep_params &p, unsigned long long *dAcc, r
         shardSlab(sg.n[2] / 2, h->shard->nranks, h->shard->rank, &aLo, &aHi);
         A.aOff2 = aLo;
     }
-    int prepBlocks = static_cast<int>((numCells * 32 + 255) / 256);
+    const int prepBlocks = (n + 255) / 256;
     const Walls W = makeWalls(h->box, h->wallMask, I.totalRange);
+    k_sweep_neighbourhood<<<static_cast<int>((numCells + 255) / 256), 256, 0, st>>>(g.numCells, sg, g.cellStart,
+                                                                                    &h->dFlags[2]);
     if (I.hard == RP_HARD_SPHERE)
-        k_sweep_prepare<RP_HARD_SPHERE><<<prepBlocks, 256, 0, st>>>(g.numCells, A, sg, h->box, 0.0, g.cellStart,
-                                                                    g.itemsTmp, g.keys, h->pos, h->orient, g.items,
-                                                                    g.rec, sweepRec32(g), T, W, I.radius,
-                                                                    &h->dFlags[2]);
+        k_sweep_prepare<RP_HARD_SPHERE><<<prepBlocks, 256, 0, st>>>(n, A, sg, h->box, 0.0, g.cellStart, g.itemsTmp,
+                                                                    g.keys, h->pos, h->orient, g.items, g.rec,
+                                                                    sweepRec32(g), T, W, I.radius);
     else
-        k_sweep_prepare<RP_HARD_SPHEROCYLINDER><<<prepBlocks, 256, 0, st>>>(g.numCells, A, sg, h->box, I.scHalfPlus,
+        k_sweep_prepare<RP_HARD_SPHEROCYLINDER><<<prepBlocks, 256, 0, st>>>(n, A, sg, h->box, I.scHalfPlus,
                                                                             g.cellStart, g.itemsTmp, g.keys, h->pos,
                                                                             h->orient, g.items, g.rec,
-                                                                            sweepRec32(g), T, W, I.radius,
-                                                                            &h->dFlags[2]);
-    h->launches += 6;
+                                                                            sweepRec32(g), T, W, I.radius);
+    h->launches += 7;
     RP_CUDA(cudaEventRecord(ev[1], st));
 
     // staging capacities: from the maxima of the previous sweeps when there are any (no host synchronisation), else
     // from this grid (one synchronisation, first call or after the packing changed)
     harvestSweepMaxima(h, false);
-    if (h->sweepCapOld == 0 || std::getenv("RP_SWEEP_SYNC_CAPS")) {
+    // (the synchronous form — counters returned to the caller — always sizes from its own grid: it never skips a cell)
+    if (h->sweepCapOld == 0 || out != nullptr || std::getenv("RP_SWEEP_SYNC_CAPS")) {
         int flags[4];
         RP_CUDA(cudaMemcpyAsync(flags, h->dFlags, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
         RP_CUDA(cudaStreamSynchronize(st));

@@ -195,60 +195,80 @@ __device__ __forceinline__ bool segmentCullPass32(const float4 ca, const float4 
     return !(fmaf(pz, pz, fmaf(py, py, px * px)) >= thr2);        // NaN passes
 }
 
+// largest population of a cell's 27-neighbourhood: the shared-memory capacity k_sweep is launched with
+static __global__ void __launch_bounds__(256) k_sweep_neighbourhood(int numCells, SweepGrid sg,
+                                                             const int *__restrict__ cellStart,
+                                                             int *__restrict__ maxNeigh)
+{
+    const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+    int sum = 0;
+    if (cell < numCells) {
+        const int cx = cell % sg.n[0], cy = (cell / sg.n[0]) % sg.n[1], cz = cell / (sg.n[0] * sg.n[1]);
+        for (int c = 0; c < 27; c++) {
+            int tIdx;
+            const int c2 = neighbourCell(sg.n, cx, cy, cz, c / 9 - 1, (c / 3) % 3 - 1, c % 3 - 1, &tIdx);
+            sum += cellStart[c2 + 1] - cellStart[c2];
+        }
+    }
+    sum = __reduce_max_sync(0xffffffffu, sum);
+    if ((threadIdx.x & 31) == 0) atomicMax(maxNeigh, sum);
+}
+
 // ---------------------------------------------------------------------------------------------------------------
-// k_sweep_prepare — one warp per sweep-grid cell, once per rp_sweep call.  Fuses what used to be two gather passes
-// over the canonical arrays:
+// k_sweep_prepare — one thread per particle (per slot of the scattered item list), once per rp_sweep call.  Fuses what
+// used to be two gather passes over the canonical arrays:
 //   records  order the cell's items by ascending particle index (deterministic whatever the scatter atomics did),
 //            write the 48-byte FP64 record {P', h} (image frame; h = orientation.column(2) * (l / 2)) and the 32-byte
 //            FP32 cull record;
 //   trials   MoveSampler::sampleMove distributions (core/move_samplers/*.cpp), Shape::translate / rotate
 //            (core/Shape.cpp:9-16), ActiveDomain::isInside with the checkerboard cell as the domain
 //            (Packing.cpp:95-96): trial FP64 record, trial cull record, new orientation, {reject flag, order key};
-//   sizing   the population of the cell's 27-neighbourhood (shared-memory capacity of k_sweep).
+// (The shared-memory capacity of k_sweep — the largest population of a 27-neighbourhood — is k_sweep_neighbourhood's.)
+// The kernel is bound by the latency of its dependent chains (Philox rounds, FP64 Rodrigues formula, the gathers):
+// every lane carries a particle and the register allocation leaves room for 24 warps per SM.
 // ---------------------------------------------------------------------------------------------------------------
 template <int HARD>
-__global__ void __launch_bounds__(256) k_sweep_prepare(int numCells, SweepArgs A, SweepGrid sg, Box box,
-                                                       double halfLength, const int *__restrict__ cellStart,
-                                                       const int *__restrict__ itemsTmp,
-                                                       const int *__restrict__ keys, const double *__restrict__ pos,
-                                                       const double *__restrict__ orient, int *__restrict__ items,
-                                                       double *__restrict__ rec, float4 *__restrict__ rec32,
-                                                       TrialBuffers T, Walls W, double radius,
-                                                       int *__restrict__ maxNeigh)
+__global__ void __launch_bounds__(256, 3) k_sweep_prepare(int n, SweepArgs A, SweepGrid sg, Box box,
+                                                          double halfLength, const int *__restrict__ cellStart,
+                                                          const int *__restrict__ itemsTmp,
+                                                          const int *__restrict__ keys, const double *__restrict__ pos,
+                                                          const double *__restrict__ orient, int *__restrict__ items,
+                                                          double *__restrict__ rec, float4 *__restrict__ rec32,
+                                                          TrialBuffers T, Walls W, double radius)
 {
-    const int cell = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
-    if (cell >= numCells) return;
+    const int scattered = blockIdx.x * blockDim.x + threadIdx.x;
+    if (scattered >= n) return;
+    const int particleId = itemsTmp[scattered];
+    const int key = keys[particleId];
+    const int cell = key & 0x0FFFFFFF, f = (key >> 28) & 7;
+    // the canonical state: gathers issued before anything depends on them
+    V3 p = v3(pos[particleId], pos[A.cap + particleId], pos[2 * A.cap + particleId]);
+    const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION);
+    const bool translated = (A.kind == RP_MOVE_TRANSLATION || A.kind == RP_MOVE_ROTOTRANSLATION);
+    M33 O;
+    V3 h = v3(0, 0, 0);
+    if (rotated) {
+        #pragma unroll
+        for (int q = 0; q < 9; q++) O.a[q] = orient[q * A.cap + particleId];
+    } else if (HARD == RP_HARD_SPHEROCYLINDER) {
+        // half axis h = orientation.column(2) * (0.5 * l): the cap centres are pos -+ h (SpherocylinderTraits.cpp:24-26)
+        h = v3(orient[2 * A.cap + particleId], orient[5 * A.cap + particleId], orient[8 * A.cap + particleId]);
+    }
     const int start = cellStart[cell], cnt = cellStart[cell + 1] - start;
     const int cc[3] = {cell % sg.n[0], (cell / sg.n[0]) % sg.n[1], cell / (sg.n[0] * sg.n[1])};
     const V3 centre = sweepCellCentre(sg, box, cc[0], cc[1], cc[2]);
     const float invHalfF = (HARD == RP_HARD_SPHEROCYLINDER && A.cullHalf > 0.f) ? __fdividef(1.0f, A.cullHalf) : 0.f;
-    const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION);
-    const bool translated = (A.kind == RP_MOVE_TRANSLATION || A.kind == RP_MOVE_ROTOTRANSLATION);
-    for (int i = lane; i < cnt; i += 32) {
-        const int particleId = itemsTmp[start + i];
-        int rank = 0;
-        for (int j = 0; j < cnt; j++) rank += (itemsTmp[start + j] < particleId);
+    int rank = 0;
+    for (int j = 0; j < cnt; j++) rank += (itemsTmp[start + j] < particleId);
+    do {
         const int slot = start + rank;
         items[slot] = particleId;
-        const int f = (keys[particleId] >> 28) & 7;
-        V3 p = v3(pos[particleId], pos[A.cap + particleId], pos[2 * A.cap + particleId]);
         if (f) p = p + sg.imageShift[f];
-        M33 O;
-        V3 h = v3(0, 0, 0);
-        if (rotated) {
-            #pragma unroll
-            for (int q = 0; q < 9; q++) O.a[q] = orient[q * A.cap + particleId];
-            if (HARD == RP_HARD_SPHEROCYLINDER) h = column(O, 2) * halfLength;
-        } else if (HARD == RP_HARD_SPHEROCYLINDER) {
-            // half axis h = orientation.column(2) * (0.5 * l): the cap centres are pos -+ h (SpherocylinderTraits.cpp:24-26)
-            h = v3(orient[2 * A.cap + particleId], orient[5 * A.cap + particleId], orient[8 * A.cap + particleId])
-                * halfLength;
-        }
+        if (HARD == RP_HARD_SPHEROCYLINDER) h = (rotated ? column(O, 2) : h) * halfLength;
         double *r = rec + 6 * static_cast<size_t>(slot);
         r[0] = p.x; r[1] = p.y; r[2] = p.z; r[3] = h.x; r[4] = h.y; r[5] = h.z;
         makeRec32(p, h, centre, invHalfF, rec32 + 2 * static_cast<size_t>(slot));
-        if (slot < A.slotBegin || slot >= A.slotEnd) continue;       // sharded over NCCL: another rank's trial
+        if (slot < A.slotBegin || slot >= A.slotEnd) break;          // sharded over NCCL: another rank's trial
 
         // ---- the trial move of this particle ----
         Rng rng;
@@ -316,16 +336,7 @@ __global__ void __launch_bounds__(256) k_sweep_prepare(int numCells, SweepArgs A
         makeRec32(p, h, centre, invHalfF, T.rec32 + 2 * static_cast<size_t>(slot));
         rng.ctr.w = 0x40000000u;     // separate sub-stream for the processing order
         T.meta[slot] = make_uint2(rej, philox4x32(rng.ctr, rng.k0, rng.k1).x);
-    }
-    // population of the 27-neighbourhood (smem sizing of the sweep kernel)
-    int sum = 0;
-    if (lane < 27) {
-        int tIdx;
-        int c2 = neighbourCell(sg.n, cc[0], cc[1], cc[2], lane / 9 - 1, (lane / 3) % 3 - 1, lane % 3 - 1, &tIdx);
-        sum = cellStart[c2 + 1] - cellStart[c2];
-    }
-    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if (lane == 0) atomicMax(maxNeigh, sum);
+    } while (false);
 }
 
 }  // namespace rp

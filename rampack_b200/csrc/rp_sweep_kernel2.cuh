@@ -263,7 +263,8 @@ k_sweep(SweepArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const int *__r
             const int numChunks = (numCand + 31) >> 5;
             for (;;) {
                 int chunk = 0;
-                if (lane == 0) chunk = atomicAdd(&qCount, 1);
+                if (lane == 0)      // (plain atom.shared: the compiler's warp-aggregated atomicAdd costs 16 instructions)
+                    asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(chunk) : "r"(smemAddr(&qCount)) : "memory");
                 chunk = __shfl_sync(0xffffffffu, chunk, 0);
                 if (chunk >= numChunks) break;
                 const int jj = (chunk << 5) + lane;
@@ -279,18 +280,23 @@ k_sweep(SweepArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const int *__r
                 // same operations in the same order as the scalar form, half the issue slots
                 unsigned int mlo = 0, mhi = 0;
                 const float2 cx2 = make_float2(cxf, cxf), cy2 = make_float2(cyf, cyf), cz2 = make_float2(czf, czf);
+                const float2 negThr = make_float2(-thrF, -thrF);
                 const int numPairs = (numOwn + 1) >> 1;
                 #pragma unroll
                 for (int half = 0; half < 2; half++) {
                     const int k0 = half * 16, k1 = min(numPairs, k0 + 16);
-                    unsigned int bit = 1, mm = 0;
+                    // the verdict "squared distance < threshold" is the sign bit of (squared distance - threshold),
+                    // shifted into the mask by one funnel shift per trial (first trial ends up in the highest bit)
+                    unsigned int mm = 0;
                     #pragma unroll 4
                     for (int k = k0; k < k1; k++) {
                         const float4 pa = trialP[k][0], pb = trialP[k][1];
                         const float2 dx = __fadd2_rn(cx2, make_float2(pa.x, pa.y)),
                                      dy = __fadd2_rn(cy2, make_float2(pa.z, pa.w)),
                                      dz = __fadd2_rn(cz2, make_float2(pb.x, pb.y));
-                        float2 d2;
+                        // |d|^2 - threshold
+                        const float2 dd = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __ffma2_rn(dx, dx, negThr)));
+                        float2 e;
                         if (HARD == RP_HARD_SPHEROCYLINDER) {
                             const float4 pc = trialP[k][2];
                             const float2 ux = make_float2(pb.z, pb.w), uy = make_float2(pc.x, pc.y),
@@ -299,17 +305,18 @@ k_sweep(SweepArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const int *__r
                             // instructions fewer than forming d - s u; the rounding error (a few ulp of |d|^2 <= 36
                             // for a pair inside the threshold, ~1e-5) is inside the margin of cullThr2
                             const float2 t = __ffma2_rn(dz, uz, __ffma2_rn(dy, uy, __fmul2_rn(dx, ux)));
-                            const float2 dd = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
                             const float2 sc = make_float2(fminf(fmaxf(t.x, -halfF), halfF),
                                                           fminf(fmaxf(t.y, -halfF), halfF));
-                            d2 = __ffma2_rn(sc, __ffma2_rn(t, make_float2(-2.f, -2.f), sc), dd);
+                            e = __ffma2_rn(sc, __ffma2_rn(t, make_float2(-2.f, -2.f), sc), dd);
                         } else {
-                            d2 = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
+                            e = dd;
                         }
-                        if (d2.x < thrF) mm |= bit;
-                        if (d2.y < thrF) mm |= bit << 1;
-                        bit <<= 2;
+                        mm = __funnelshift_l(__float_as_uint(e.x), mm, 1);
+                        mm = __funnelshift_l(__float_as_uint(e.y), mm, 1);
                     }
+                    // trial 2 (k0 + i) sits at bit 2 (k1 - k0) - 1 - 2 i: reverse into ascending order
+                    const int nb = 2 * (k1 - k0);
+                    mm = nb > 0 ? __brev(mm) >> (32 - nb) : 0u;
                     if (half == 0) mlo = mm; else mhi = mm;
                 }
                 unsigned long long m = (static_cast<unsigned long long>(mhi) << 32) | mlo;
@@ -347,11 +354,17 @@ k_sweep(SweepArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const int *__r
                         const int v = __shfl_up_sync(0xffffffffu, incl, d);
                         if (lane >= d) incl += v;
                     }
-                    int at = qn + incl - cnt;
-                    while (take) {
-                        const int i = __ffsll(static_cast<long long>(take)) - 1;
-                        take &= take - 1ull;
-                        q[at++] = (static_cast<unsigned int>(i) << 16) | lowBits;
+                    // (the order of a lane's entries is immaterial: highest trial first, one 32-bit word at a time)
+                    unsigned int *dst = q + (qn + incl - cnt);
+                    #pragma unroll
+                    for (int w = 0; w < 2; w++) {
+                        unsigned int x = w == 0 ? static_cast<unsigned int>(take) : static_cast<unsigned int>(take >> 32);
+                        const unsigned int tag = lowBits | (static_cast<unsigned int>(32 * w) << 16);
+                        while (x) {
+                            const int i = 31 - __clz(x);
+                            x &= ~(1u << i);
+                            *dst++ = tag + (static_cast<unsigned int>(i) << 16);
+                        }
                     }
                     qn += __shfl_sync(0xffffffffu, incl, 31);
                     __syncwarp();

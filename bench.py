@@ -31,18 +31,21 @@ sys.path.insert(0, ROOT)
 
 METRIC = "mc_particle_moves_per_s_hard_sc"
 UNIT = "moves/s"
-TRANS_STEP, ROT_STEP = 0.05, 0.05      # rototranslation(trans_step=0.05, rot_step=0.05)
+TRANS_STEP, ROT_STEP = 0.05, 0.05      # rototranslation(trans_step=0.05, rot_step=0.05) before adaptation
 TEMPERATURE, PRESSURE = 1.0, 1.2
 SEED = 1234
+THERM_DEFAULT = 2000                   # thermalisation cycles with step-size adaptation (Simulation.cpp:128-135)
 # flops of one pair test in the reference arithmetic: centre-distance pre-filter, full segment test
 F_PRE, F_FULL = 14, 105
 B_MOVE = 200                           # algorithmic bytes per attempted move: state read + write-back + list entry
+CULL_INSTR_PER_PAIR = 10.0             # issue slots of the FP32 capsule cull per (trial, candidate) pair and lane (SASS)
 
 
 def box_step_for(n):
-    """delta_triclinic step at which N ln(V'/V) is O(1) — where the reference's step adaptation settles
-    (Simulation.cpp:533-607); 0.01 at N = 1e5 (Appendix C) scaled with the particle number."""
-    return 0.01 * 1.0e5 / max(n, 1.0e5) if n > 1.0e5 else 0.01
+    """Start value of the delta_triclinic step.  A uniform compression by eps brings every near-contact pair closer by
+    eps * r: with ~10 N pairs per unit gap an overlap-free proposal needs eps ~ 1 / (10 N), i.e. a step of a few 1 / N
+    for these boxes; the thermalisation adapts it from there (Simulation.cpp:598-607)."""
+    return min(0.01, 3.0 / n)
 
 
 def env_int(name, default):
@@ -125,23 +128,28 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def run_reference_cycles(box, shapes, cycles, seed, threads=None):
+def run_reference_cycles(box, shapes, cycles, seed, threads=None, steps=None, desc=None, pressure=PRESSURE,
+                         scaler=2, total_range=6.0):
     """`cycles` NpT cycles of the reference's own Simulation (oracle/_ref when built, else the single-thread port).
+    steps = (translation step, rotation step, box step) — frozen: the averaging phase does not adapt them.
     Returns (moves attempted, scalings attempted, seconds for moves + scaling + domain decomposition, info, state)."""
     from oracle import refwrap as R
     from rampack_b200 import workloads as W
     import rampack_b200 as rp
-    desc = rp.make_desc(hard=rp.RP_HARD_SPHEROCYLINDER, radius=W.SC_RADIUS, length=W.SC_LENGTH)
+    if desc is None:
+        desc = rp.make_desc(hard=rp.RP_HARD_SPHEROCYLINDER, radius=W.SC_RADIUS, length=W.SC_LENGTH)
     n = shapes.shape[0]
+    t_step, r_step, b_step = steps if steps is not None else (TRANS_STEP, ROT_STEP, box_step_for(n))
     if R.have_ref(native=True) or R.have_ref():
         native = R.have_ref(native=True)
         traits = R.RefTraits(desc, native=native)
         cores = threads or host_cores()
         heights = [box[0, 0], box[1, 1], box[2, 2]]
-        dom = choose_domains(cores, heights, 6.0, 6.2)
+        dom = choose_domains(cores, heights, total_range, total_range * 1.04)
         nthreads = dom[0] * dom[1] * dom[2]
-        res, box_out, shapes_out = R.ref_run_simulation(traits, box, shapes, seed, TEMPERATURE, PRESSURE, TRANS_STEP,
-                                                        ROT_STEP, 2, box_step_for(n), dom, nthreads, cycles, 0)
+        # the whole run is the "averaging" phase: the reference adapts step sizes in the thermalisation phase only
+        res, box_out, shapes_out = R.ref_run_simulation(traits, box, shapes, seed, TEMPERATURE, pressure, t_step,
+                                                        r_step, scaler, b_step, dom, nthreads, 0, cycles)
         seconds = res.move_seconds + res.scaling_seconds + res.domain_decomposition_seconds
         info = {"kind": "reference", "cores": nthreads, "domains": list(dom),
                 "flags": "-O3 -march=x86-64-v3 -fopenmp" if native else "-O3 -ffp-contract=off -fopenmp",
@@ -149,7 +157,7 @@ def run_reference_cycles(box, shapes, cycles, seed, threads=None):
                 "scalings_attempted": int(res.scalings_attempted)}
         return int(res.moves_attempted), int(res.scalings_attempted), seconds, info, (box_out, shapes_out)
     pk = R.PortPacking(R.PortTraits(desc), box, shapes)
-    res = pk.run_cycles(seed, cycles, TRANS_STEP, ROT_STEP, TEMPERATURE, PRESSURE, True, box_step_for(n))
+    res = pk.run_cycles(seed, cycles, t_step, r_step, TEMPERATURE, pressure, True, b_step)
     info = {"kind": "port", "cores": 1, "domains": [1, 1, 1], "flags": "-O2 -ffp-contract=off",
             "move_seconds": res.move_seconds, "scaling_seconds": res.scaling_seconds,
             "scalings_attempted": int(res.scalings_attempted)}
@@ -157,38 +165,72 @@ def run_reference_cycles(box, shapes, cycles, seed, threads=None):
     return int(res.moves_attempted), int(res.scalings_attempted), res.move_seconds + res.scaling_seconds, info, (b, s)
 
 
-def reference_workload(args):
-    """The reference arm runs the metric's configuration when K + W cycles of it fit a few minutes on this host,
-    otherwise the same lattice at N = 100 352 (same density, same per-move work)."""
+def workload_string(name, n, therm, steps3, sharded=False, per_gpu=False):
+    """The one description both arms print (`config.workload`): same lattice, same thermalisation, same frozen steps."""
+    where = " in ONE packing sharded over all GPUs" if sharded else (" per GPU" if per_gpu else "")
+    return (f"{name}: hard spherocylinders l=5 r=0.5, N={n}{where}, sc lattice eta=0.475 + {therm} thermalisation "
+            f"cycles on the device with the reference's step adaptation, then frozen steps: NpT T=1 p={PRESSURE}, "
+            f"rototranslation({steps3[0]:.6g}, {steps3[1]:.6g}), delta_triclinic({steps3[2]:.6g})")
+
+
+def thermalised_state(workload, therm, local=0, seed=SEED, pressure=PRESSURE, stream=None, comm=None):
+    """Lattice -> `therm` NpT cycles on the device with step-size adaptation (Simulation.cpp:128-135, 533-607).
+    Deterministic for a given (workload, therm, seed): both arms call it and start from the same state with the same
+    frozen step sizes.  Returns (device, simulation, (translation, rotation, box) steps)."""
+    import rampack_b200 as rp
     from rampack_b200 import workloads as W
-    cores = host_cores()
-    name = args.workload
-    box, shapes = W.sc_config(name)
-    est = shapes.shape[0] / (3.0e4 * max(1, min(cores, 512))) * (args.steps + args.warmup)
-    if est > 150 and name != "sc_100k":
-        name = "sc_100k"
-        box, shapes = W.sc_config(name)
-    return name, box, shapes
+    from rampack_b200 import NativeSimulation
+    dev = rp.Device(device=local, seed=seed, cuda_stream=stream)
+    if comm is not None:
+        dev.comm_init(*comm)
+    desc = rp.make_desc(hard=rp.RP_HARD_SPHEROCYLINDER, radius=W.SC_RADIUS, length=W.SC_LENGTH)
+    box, shapes = W.sc_config(workload)
+    dev.set_interaction(desc)
+    dev.upload(box, shapes)
+    sim = NativeSimulation(dev, [(rp.RP_MOVE_ROTOTRANSLATION, TRANS_STEP, ROT_STEP)], TEMPERATURE, pressure,
+                           ("delta_triclinic", box_step_for(shapes.shape[0]), False), seed=seed)
+    sim.run(therm, adjust_step_sizes=True)
+    st = sim.stats()
+    return dev, sim, (st.translation_step[0], st.rotation_step[0], st.scaler_step)
 
 
 def main_reference(args):
+    """The reference's own OpenMP Simulation on the host cores, from the state and with the step sizes the GPU arm is
+    timed on (prepared, untimed, by the same deterministic device thermalisation; without a GPU: from the lattice)."""
     rank = env_int("RANK", 0)
     if rank != 0:
         return 0
-    name, box, shapes = reference_workload(args)
-    n = shapes.shape[0]
+    from rampack_b200 import workloads as W
+    name = args.workload
+    box, shapes = W.sc_config(name)
+    est = shapes.shape[0] / (3.0e4 * max(1, min(host_cores(), 512))) * (args.steps + args.warmup)
+    if est > 150 and name != "sc_100k":        # K + W cycles of the metric's configuration must fit a few minutes
+        name = "sc_100k"
+    n = W.sc_config(name)[1].shape[0]
+    steps3, same_state = (TRANS_STEP, ROT_STEP, box_step_for(n)), False
+    box, shapes = W.sc_config(name)
+    try:
+        import torch
+        if torch.cuda.is_available():
+            dev, sim, steps3 = thermalised_state(name, args.therm)
+            box, shapes = dev.download()
+            sim.close()
+            dev.close()
+            same_state = True
+    except Exception as ex:        # no device / no library: the reference arm still runs, from the lattice
+        print(f"bench.py --impl reference: device thermalisation unavailable ({ex}); starting from the lattice",
+              file=sys.stderr)
     state = (box, shapes)
     if args.warmup > 0:
-        _, _, _, _, state = run_reference_cycles(box, shapes, args.warmup, SEED)
-    moves, scalings, seconds, info, _ = run_reference_cycles(state[0], state[1], args.steps, SEED + 1)
+        _, _, _, _, state = run_reference_cycles(box, shapes, args.warmup, SEED, steps=steps3)
+    moves, scalings, seconds, info, _ = run_reference_cycles(state[0], state[1], args.steps, SEED + 1, steps=steps3)
     value = moves / seconds
     sample = f"{args.steps} NpT cycles of {name} (N={n}) after {args.warmup} warm-up cycles, all particles"
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": seconds / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"{name}: hard spherocylinders l=5 r=0.5, N={n}, sc lattice eta=0.475, NpT "
-                                   f"T=1 p=1.2, rototranslation(0.05, 0.05), delta_triclinic({box_step_for(n):g})",
-                       "parallelism": f"OpenMP domains {info['domains']}"},
+            "config": {"workload": workload_string(name, n, args.therm if same_state else 0, steps3),
+                       "parallelism": f"OpenMP domains {info['domains']}", "same_state_as_gpu_arm": same_state},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": info["cores"], "kind": info["kind"],
                              "sample": sample, "flags": info["flags"]},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -198,6 +240,129 @@ def main_reference(args):
     return 0
 
 
+def sweep_cells(box, n, total_range):
+    """Cells of the checkerboard grid rp_sweep builds (rampack_b200/csrc/rp_sweep.cu): width >= totalRange and wide
+    enough for ~16 particles, even counts."""
+    heights = [np.linalg.det(box) / np.linalg.norm(np.cross(box[:, (i + 1) % 3], box[:, (i + 2) % 3]))
+               for i in range(3)]
+    width = max(total_range * (1 + 1e-9), (16.0 * abs(np.linalg.det(box)) / n) ** (1.0 / 3.0))
+    return [max(2, int(h / width)) & ~1 for h in heights]
+
+
+def measure_extra(name, cfg, local, stream, peak_gflops, steps, budget_s=6.0, cpu=True):
+    """One of the other BASELINE configurations (rampack_b200/workloads.py EXTRA_CONFIGS): thermalise with step
+    adaptation, time `steps` cycles with CUDA events, and put the reference's CPU figure for a bounded sample of the
+    same lattice (same density, same step sizes) beside it."""
+    import torch
+    import rampack_b200 as rp
+    from rampack_b200 import workloads as W
+    from rampack_b200 import NativeSimulation
+    out = {}
+    desc = cfg["desc"]()
+    box, shapes = W.extra_lattice(cfg)
+    n = shapes.shape[0]
+    dev = rp.Device(device=local, seed=SEED, cuda_stream=stream.cuda_stream)
+    dev.set_interaction(desc)
+    dev.upload(box, shapes)
+    sim = NativeSimulation(dev, [(rp.RP_MOVE_ROTOTRANSLATION,) + tuple(cfg["moves"])], TEMPERATURE, cfg["p"],
+                           cfg["scaler"], seed=SEED)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def timed(cycles, adjust=False):
+        s0 = sim.stats()
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            sim.run(cycles, adjust_step_sizes=adjust)
+            e1.record(stream)
+        torch.cuda.synchronize()
+        s1 = sim.stats()
+        return e0.elapsed_time(e1), s0, s1
+
+    if cfg.get("relax"):
+        # overlap_relaxation run (Simulation::relaxOverlaps, Simulation.cpp:218-323): overlap counting on, cycles until
+        # the cached count reaches zero
+        dev.toggle_overlap_counting(True)
+        start = dev.cached_overlaps()
+        ms_total, cycles, moves = 0.0, 0, 0
+        while dev.cached_overlaps() > 0 and ms_total < budget_s * 1e3 and cycles < 2000:
+            ms, s0, s1 = timed(5, adjust=True)
+            ms_total += ms
+            cycles += 5
+            moves += s1.moves_attempted[0] - s0.moves_attempted[0]
+        left = dev.cached_overlaps()
+        out["overlap_relaxation"] = {"overlaps_start": int(start), "overlaps_end": int(left), "cycles": cycles,
+                                     "value": moves / (ms_total * 1e-3) if ms_total > 0 else None, "unit": UNIT,
+                                     "ms_per_cycle": ms_total / max(1, cycles)}
+        if left == 0:
+            dev.toggle_overlap_counting(False)
+    # thermalisation with the reference's step adaptation, bounded by the time budget
+    timed(2, adjust=True)             # (first calls: allocations)
+    ms, _, _ = timed(3, adjust=True)
+    therm = int(max(10, min(cfg.get("therm", 200), budget_s * 1e3 / max(ms / 3, 1e-3))))
+    timed(therm, adjust=True)
+    timed(3)
+    launches0 = dev.launch_count()
+    ms, s0, s1 = timed(steps)
+    attempted = s1.moves_attempted[0] - s0.moves_attempted[0]
+    accepted = s1.moves_accepted[0] - s0.moves_accepted[0]
+    evaluated = s1.scalings_evaluated - s0.scalings_evaluated
+    scaling_ms = s1.scaling_ms - s0.scaling_ms
+    sweep_ms = (s1.sweep_kernel_ms - s0.sweep_kernel_ms) + (s1.sweep_grid_ms - s0.sweep_grid_ms)
+    steps3 = (s1.translation_step[0], s1.rotation_step[0], s1.scaler_step)
+    k_cand, k_full = dev.neighbour_stats()
+    n_centres = max(1, desc.n_centres)
+    f_pre, f_full = cfg["flops"]
+    w_move = n_centres * (k_cand * f_pre + k_full * f_full)
+    value = attempted / (ms * 1e-3)
+    achieved = attempted * w_move / (max(sweep_ms, 1e-9) * 1e-3) * 1e-12
+    box_now = np.array(list(s1.box)).reshape(3, 3)
+    out.update({"value": value, "unit": UNIT, "n": n, "interaction_centres": n * n_centres, "steps": steps,
+                "thermalisation_cycles": therm, "ms_per_step": ms / steps,
+                "acceptance": accepted / max(1, attempted),
+                "step_sizes": {"translation": steps3[0], "rotation": steps3[1], "box": steps3[2]},
+                "number_density": n / abs(np.linalg.det(box_now)),
+                "box_moves_per_s": (evaluated / (scaling_ms * 1e-3)) if scaling_ms > 0 and evaluated else None,
+                "box_moves": {"attempted": steps, "evaluated": int(evaluated),
+                              "accepted": int(s1.scalings_accepted - s0.scalings_accepted)},
+                "gpu_launches": int(dev.launch_count() - launches0),
+                "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak_gflops * 1e-3, "unit": "TFLOP/s",
+                             "frac": achieved / (peak_gflops * 1e-3), "flop_per_move": w_move, "k_cand": k_cand,
+                             "k_within_range": k_full, "flops_per_pair": [f_pre, f_full],
+                             "sweep_ms_per_step": sweep_ms / steps,
+                             "hbm_frac": attempted * B_MOVE / (max(sweep_ms, 1e-9) * 1e-3) * 1e-9 / 6540.0}})
+    if "nematic" in cfg.get("observe", ()):
+        out["nematic_p2"] = float(dev.nematic_order()[1])
+    if cpu:
+        try:
+            from oracle import refwrap as R
+            cbox, cshapes = W.extra_lattice(dict(cfg, relax=None), cells=cfg["cpu_cells"])
+            # the CPU sample runs at the density the device run has reached (same per-move work)
+            scale = (n / abs(np.linalg.det(box_now)) / (cshapes.shape[0] / abs(np.linalg.det(cbox)))) ** (-1.0 / 3.0)
+            cbox, cshapes = cbox * scale, cshapes.copy()
+            cshapes[:, :3] *= scale
+            native = R.have_ref(native=True)
+            tr = R.RefTraits(desc, native=native)
+            total_range = 2 * tr.total_range_radius
+            scaler_kind = 1 if cfg["scaler"][0] == "delta_v" else 2
+            t0 = time.perf_counter()
+            m1, _, sec1, info, state = run_reference_cycles(cbox, cshapes, 1, SEED, steps=steps3, desc=desc,
+                                                            pressure=cfg["p"], scaler=scaler_kind,
+                                                            total_range=total_range)
+            cycles = int(max(1, min(50, (budget_s - (time.perf_counter() - t0)) / max(sec1, 1e-4))))
+            m, sc, sec, info, _ = run_reference_cycles(state[0], state[1], cycles, SEED + 1, steps=steps3, desc=desc,
+                                                       pressure=cfg["p"], scaler=scaler_kind, total_range=total_range)
+            out["cpu_baseline"] = {"value": m / sec, "unit": UNIT, "cores": info["cores"], "kind": info["kind"],
+                                   "sample": f"{cycles} NpT cycles of the same lattice at N={cshapes.shape[0]} "
+                                             f"(same density and step sizes), domains {info['domains']}",
+                                   "box_moves_per_s": (sc / info["scaling_seconds"]) if info["scaling_seconds"] > 0
+                                   else None}
+        except Exception as ex:
+            out["cpu_baseline"] = {"value": None, "kind": "unavailable", "sample": str(ex)}
+    sim.close()
+    dev.close()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -205,9 +370,13 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="sc_1m", choices=["sc_12k", "sc_100k", "sc_1m", "sc_4m"])
-    ap.add_argument("--therm", type=int, default=20, help="untimed equilibration cycles before the warm-up")
+    ap.add_argument("--therm", type=int, default=THERM_DEFAULT,
+                    help="untimed thermalisation cycles (with step-size adaptation) before the warm-up")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-cycles", type=int, default=1)
+    ap.add_argument("--configs", default="all",
+                    help="other BASELINE configurations measured after the metric's (N = 1 only): all, none, or a "
+                         "comma-separated list of names from rampack_b200/workloads.py EXTRA_CONFIGS")
     ap.add_argument("--parallelism", default="sharded", choices=["sharded", "replicas"],
                     help="what N > 1 ranks do (ignored at N = 1)")
     args = ap.parse_args()
@@ -217,7 +386,6 @@ def main():
     import torch
     import rampack_b200 as rp
     from rampack_b200 import workloads as W
-    from rampack_b200 import NativeSimulation
 
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if not torch.cuda.is_available():
@@ -250,32 +418,27 @@ def main():
     sharded = world > 1 and args.parallelism == "sharded"
     rseed = SEED if sharded else SEED + rank          # sharded ranks are one simulation: same Philox key everywhere
     stream = torch.cuda.Stream()
-    dev = rp.Device(device=local, seed=rseed, cuda_stream=stream.cuda_stream)
+    comm = None
     if sharded:
         ident = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
             ident.copy_(torch.frombuffer(bytearray(rp.Device.comm_unique_id()), dtype=torch.uint8))
         dist.broadcast(ident, 0)
-        dev.comm_init(bytes(ident.cpu().numpy().tobytes()), rank, world)
-    desc = rp.make_desc(hard=rp.RP_HARD_SPHEROCYLINDER, radius=W.SC_RADIUS, length=W.SC_LENGTH)
-    box, shapes = W.sc_config(args.workload)
-    n = shapes.shape[0]
-    dev.set_interaction(desc)
-    dev.upload(box, shapes)
-    # each replica is one pressure point of a scan (north_star): rank r runs p = 1.2 + 0.1 r
-    # the reference's Simulation cycle loop, in C++ inside the library (rp_sim, rampack_b200/csrc/rp_sim.cu); step
-    # sizes stay frozen (adjust_step_sizes = 0) so that both arms do the same work
-    sim = NativeSimulation(dev, [(rp.RP_MOVE_ROTOTRANSLATION, TRANS_STEP, ROT_STEP)], TEMPERATURE,
-                           PRESSURE if sharded else PRESSURE + 0.1 * rank,
-                           ("delta_triclinic", box_step_for(n), False), seed=rseed)
-    sim.run(args.therm)
+        comm = (bytes(ident.cpu().numpy().tobytes()), rank, world)
+    # each replica is one pressure point of a scan (north_star): rank r runs p = 1.2 + 0.1 r.  The cycle loop is the
+    # reference's Simulation::performCycle in C++ inside the library (rp_sim, rampack_b200/csrc/rp_sim.cu); the
+    # thermalisation adapts the step sizes like the reference's, the timed cycles run with them frozen
+    dev, sim, steps3 = thermalised_state(args.workload, args.therm, local, rseed,
+                                         PRESSURE if sharded or world == 1 else PRESSURE + 0.1 * rank,
+                                         stream.cuda_stream, comm)
     therm_box, therm_shapes = dev.download()
+    n = therm_shapes.shape[0]
 
     # ---- device-resident timing: W warm-up + exactly K timed steps ----
-    sim.run(args.warmup)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    sim.run(args.warmup)
     launches0 = dev.launch_count()
     s0 = sim.stats()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -286,9 +449,14 @@ def main():
         e1.record(stream)
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1))
-    clocks = sampler.stop() if rank == 0 else None
     launches = dev.launch_count() - launches0
     s1 = sim.stats()
+    # the timed region is a few tens of milliseconds: the clock sampler (100 ms period) keeps running over the warm-up
+    # before it and the same cycles repeated after it
+    if ms < 600:
+        sim.run(max(1, int((600 - ms) / max(ms / args.steps, 1e-3))))
+        torch.cuda.synchronize()
+    clocks = sampler.stop() if rank == 0 else None
     sweep_ms = s1.sweep_kernel_ms - s0.sweep_kernel_ms
     grid_ms = s1.sweep_grid_ms - s0.sweep_grid_ms
     scaling_ms = s1.scaling_ms - s0.scaling_ms
@@ -315,7 +483,7 @@ def main():
     barrier()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
     e2e_value = (float(n * e2e_steps) if sharded else sum_over_ranks(float(n * e2e_steps))) / (e2e_ms * 1e-3)
-    comm = dev.comm_stats() if sharded else None
+    comm_stats = dev.comm_stats() if sharded else None
 
     # ---- roofline of the dominant kernel (k_sweep, 8 launches per step) ----
     k_cand, k_full = dev.neighbour_stats()
@@ -336,6 +504,14 @@ def main():
         traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("k_sweep_bytes_per_launch")
     except (OSError, ValueError):
         pass
+    # the physical ceiling of the kernel as built: the FP32 capsule cull visits every (trial, staged candidate) pair of
+    # a cell; its inner loop is CULL_INSTR_PER_PAIR issue slots per pair and lane
+    cells = sweep_cells(np.array(b_now), n, 6.0)
+    per_cell = n / float(cells[0] * cells[1] * cells[2])
+    cull_pairs_per_move = 28.0 * per_cell
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    cull_peak = 148 * 4 * 32 * sm_mhz * 1e6 / CULL_INSTR_PER_PAIR
+    cull_rate = units_per_launch * cull_pairs_per_move / (avg_launch_ms * 1e-3)
     roofline = {"bound": "fp64", "kernel": "k_sweep<spherocylinder>", "achieved": achieved_tflops,
                 "peak": peak["dmul_dadd_gflops"] * 1e-3, "unit": "TFLOP/s",
                 "frac": achieved_tflops / (peak["dmul_dadd_gflops"] * 1e-3),
@@ -344,6 +520,12 @@ def main():
                 "flop_per_move": w_move, "k_cand": k_cand, "k_full": k_full, "avg_launch_ms": avg_launch_ms,
                 "kernel_share_of_step": sweep_ms / ms if world == 1 else None,
                 "traffic": traffic,
+                "physical": {"what": "FP32 capsule-cull pairs (every trial of an active cell against every particle "
+                                     "staged for it) against the issue-slot ceiling of that loop",
+                             "cull_pairs_per_move": cull_pairs_per_move, "achieved": cull_rate,
+                             "peak": cull_peak, "unit": "pairs/s", "frac": cull_rate / cull_peak,
+                             "peak_source": f"148 SMs x 4 schedulers x 32 lanes x {sm_mhz:.0f} MHz / "
+                                            f"{CULL_INSTR_PER_PAIR:g} issue slots per pair (SASS of the inner loop)"},
                 "hbm": {"achieved": units_per_launch * B_MOVE / (avg_launch_ms * 1e-3) * 1e-9, "peak": hbm_peak,
                         "unit": "GB/s", "frac": units_per_launch * B_MOVE / (avg_launch_ms * 1e-3) * 1e-9 / hbm_peak,
                         "bytes_per_move": B_MOVE,
@@ -352,7 +534,7 @@ def main():
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
-            cm, cs, csec, info, _ = run_reference_cycles(therm_box, therm_shapes, args.cpu_cycles, SEED)
+            cm, cs, csec, info, _ = run_reference_cycles(therm_box, therm_shapes, args.cpu_cycles, SEED, steps=steps3)
             cpu_baseline = {"value": cm / csec, "unit": UNIT, "cores": info["cores"], "kind": info["kind"],
                             "sample": f"{args.cpu_cycles} NpT cycle(s) of the same {args.workload} state the GPU "
                                       f"timing starts from (N={n}, all particles), domains {info['domains']}",
@@ -360,23 +542,34 @@ def main():
                             "scaling_seconds": info["scaling_seconds"]}
         except Exception as ex:      # the baseline is a reported figure; its absence must not hide the GPU number
             cpu_baseline = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": str(ex)}
+    sim.close()
+    dev.close()
+
+    # ---- the other BASELINE configurations (C1 - C4), N = 1 only: extra keys of the same line ----
+    configs = None
+    if rank == 0 and world == 1 and args.configs != "none":
+        names = list(W.EXTRA_CONFIGS) if args.configs == "all" else [x for x in args.configs.split(",") if x]
+        configs = {}
+        for name in names:
+            try:
+                configs[name] = measure_extra(name, W.EXTRA_CONFIGS[name], local, stream, peak["dmul_dadd_gflops"],
+                                              args.steps, cpu=not args.no_cpu_baseline)
+            except Exception as ex:
+                configs[name] = {"value": None, "error": str(ex)}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": "strong" if sharded else "weak",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": f"{args.workload}: hard spherocylinders l=5 r=0.5, N={n} "
-                                       f"{'in ONE packing sharded over all GPUs' if sharded else 'per GPU'}, sc lattice "
-                                       f"eta=0.475 + {args.therm} equilibration cycles, NpT T=1 p=1.2, "
-                                       f"rototranslation(0.05, 0.05), delta_triclinic({box_step_for(n):g})",
+                "config": {"workload": workload_string(args.workload, n, args.therm, steps3, sharded, world > 1),
                            "parallelism": ("1 GPU" if world == 1 else
                                            f"spatially sharded sweep: {world} z-slabs of cell layers; accepted moves "
                                            "travel as accept bytes + boundary-layer records written by k_sweep into "
                                            "the peers' memory over NVLink, flag kernels order the colours; box-move "
                                            "recount split + NCCL all-reduce; state replicated"
                                            if sharded else "replicas (pressure-scan points), one per GPU"),
-                           "l2_policy": f"state {n * 96 / 1e6:.0f} MB + sorted records {n * 48 / 1e6:.0f} MB per "
+                           "l2_policy": f"state {n * 96 / 1e6:.0f} MB + sorted records {n * 80 / 1e6:.0f} MB per "
                                         "step; every step rebuilds the sweep grid from all particles "
                                         "(inputs not flushed: working set is re-read each step by design)"},
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(n * 96 + 72),
@@ -386,15 +579,16 @@ def main():
                 "roofline": roofline,
                 "cpu_baseline": cpu_baseline,
                 "acceptance": accepted / max(1, attempted),
+                "step_sizes": {"translation": steps3[0], "rotation": steps3[1], "box": steps3[2]},
                 "volume_moves": {"attempted": args.steps, "evaluated": int(evaluated),
                                  "accepted": int(scalings_accepted),
                                  "evaluated_per_s": (evaluated / (scaling_ms * 1e-3)) if scaling_ms > 0 else None,
                                  "ms_per_evaluated": (scaling_ms / evaluated) if evaluated else None},
-                "comm_bytes_last_sweep": comm,
+                "comm_bytes_last_sweep": comm_stats,
                 "breakdown_ms_per_step": {"sweep_kernels": sweep_ms / args.steps, "sweep_grid": grid_ms / args.steps,
-                                          "box_move": scaling_ms / args.steps}}
+                                          "box_move": scaling_ms / args.steps},
+                "configs": configs}
         print(json.dumps(line))
-    dev.close()
     if world > 1:
         dist.destroy_process_group()
     return 0

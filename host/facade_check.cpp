@@ -136,6 +136,12 @@ void spherocylinders() {
     // store / restore round trip
     std::stringstream stream;
     packing.store(stream, {{"cycles", "17"}});
+    {   // RAMSNAP text (io/RamsnapWriter.cpp:8-48): byte-identical files for identical state
+        std::uint64_t hash = 1469598103934665603ull;
+        for (unsigned char ch : stream.str()) hash = (hash ^ ch) * 1099511628211ull;
+        std::printf("sc.ramsnap_bytes %zu\nsc.ramsnap_fnv1a %016llx\n", stream.str().size(),
+                    static_cast<unsigned long long>(hash));
+    }
     Packing restored(std::make_unique<PeriodicBoundaryConditions>());
     auto aux = restored.restore(stream, interaction);
     std::printf("sc.aux_cycles %s\n", aux["cycles"].c_str());

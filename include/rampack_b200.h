@@ -197,6 +197,15 @@ rp_status rp_download(rp_handle *h, double box_out[9], double *shapes_out /* N x
 rp_status rp_size(const rp_handle *h, uint64_t *n_out);
 /* shapes [first, first + count) only — Packing::operator[] / front / back after a few explicit moves (Packing.h:193-215) */
 rp_status rp_download_range(rp_handle *h, uint64_t first, uint64_t count, double *shapes_out /* count x 12 */);
+/* Snapshot without stalling the sweep — the producer side of SimulationRecorder / SnapshotWriter
+ * (src/core/Simulation.cpp:141-152, src/core/io/RamsnapWriter.cpp:35-47, RamtrjIO.cpp writeShape): the state of this
+ * moment is copied on the device (ordered with the work queued so far), then moved to `shapes_out` (pinned host
+ * memory for a truly asynchronous copy) on a second stream while later cycles run.  `box_out` is valid on return;
+ * `shapes_out` after rp_snapshot_wait, or once rp_snapshot_done reports 1.  One snapshot in flight per handle: a
+ * second request waits (on the device) for the first copy to finish. */
+rp_status rp_snapshot_async(rp_handle *h, double box_out[9], double *shapes_out /* N x 12 */, uint64_t n);
+rp_status rp_snapshot_wait(rp_handle *h);
+rp_status rp_snapshot_done(rp_handle *h, int32_t *done_out);
 
 /* ---- neighbour grid: Packing::rebuildNeighbourGrid (Packing.cpp:858-929), NeighbourGrid::positionToCellNo ---- */
 rp_status rp_rebuild_grid(rp_handle *h);

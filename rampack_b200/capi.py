@@ -121,7 +121,8 @@ SYMBOLS = ["rp_create", "rp_destroy", "rp_last_error", "rp_version", "rp_set_int
            "rp_neighbour_stats", "rp_measure_fp64_peak", "rp_last_kernel_ms", "rp_launch_count", "rp_synchronize",
            "rp_renormalize_orientations", "rp_toggle_walls", "rp_nematic_order", "rp_smectic_order",
            "rp_pair_density_correlation", "rp_sim_create", "rp_sim_destroy", "rp_sim_run", "rp_sim_stats_get", "rp_sim_propose_box",
-           "rp_download_range", "rp_count_wall_overlaps", "rp_particle_energy_fluctuations"]
+           "rp_download_range", "rp_count_wall_overlaps", "rp_particle_energy_fluctuations", "rp_snapshot_async",
+           "rp_snapshot_wait", "rp_snapshot_done"]
 
 _lib = None
 
@@ -163,6 +164,9 @@ def load():
     lib.rp_download.argtypes = [H, dp, dp, C.c_uint64]
     lib.rp_size.argtypes = [H, C.POINTER(C.c_uint64)]
     lib.rp_download_range.argtypes = [H, C.c_uint64, C.c_uint64, dp]
+    lib.rp_snapshot_async.argtypes = [H, dp, dp, C.c_uint64]
+    lib.rp_snapshot_wait.argtypes = [H]
+    lib.rp_snapshot_done.argtypes = [H, C.POINTER(C.c_int32)]
     lib.rp_count_wall_overlaps.argtypes = [H, C.c_int, C.POINTER(C.c_uint64)]
     lib.rp_particle_energy_fluctuations.argtypes = [H, dp]
     lib.rp_rebuild_grid.argtypes = [H]
@@ -290,6 +294,22 @@ class Device:
         out = np.empty((count, 12), dtype=np.float64)
         self._check(self.lib.rp_download_range(self.h, first, count, out.ctypes.data_as(C.POINTER(C.c_double))))
         return out
+
+    def snapshot_async(self, out):
+        """Start an asynchronous snapshot into `out` (N x 12 float64, ideally pinned host memory); returns the box.
+        `out` is valid after snapshot_wait() (or once snapshot_done() is True); later cycles may be queued meanwhile."""
+        assert out.dtype == np.float64 and out.flags["C_CONTIGUOUS"] and out.size == self.n * 12
+        box = np.empty(9)
+        self._check(self.lib.rp_snapshot_async(self.h, dptr(box), dptr(out), self.n))
+        return box.reshape(3, 3)
+
+    def snapshot_wait(self):
+        self._check(self.lib.rp_snapshot_wait(self.h))
+
+    def snapshot_done(self):
+        v = C.c_int32()
+        self._check(self.lib.rp_snapshot_done(self.h, C.byref(v)))
+        return bool(v.value)
 
     def count_wall_overlaps(self, early_exit=False):
         c = C.c_uint64(0)

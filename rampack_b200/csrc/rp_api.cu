@@ -297,6 +297,13 @@ void rp_destroy(rp_handle *h) {
     for (auto &ev : h->sweepMaxEvent) if (ev) cudaEventDestroy(ev);
     for (auto &t : h->timing) for (auto &ev : t.e) if (ev) cudaEventDestroy(ev);
     if (h->sweepMaxPinned) cudaFreeHost(h->sweepMaxPinned);
+    if (h->snapStream) {
+        cudaStreamSynchronize(h->snapStream);
+        cudaStreamDestroy(h->snapStream);
+        cudaEventDestroy(h->snapReady);
+        cudaEventDestroy(h->snapDone);
+    }
+    if (h->dSnap) cudaFree(h->dSnap);
     if (h->ownStream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -396,6 +403,64 @@ rp_status rp_download_range(rp_handle *h, uint64_t first, uint64_t count, double
                                 h->stream));
         RP_CUDA(cudaStreamSynchronize(h->stream));
         RP_CUDA(cudaGetLastError());
+    }
+    RP_API_END(h)
+}
+
+rp_status rp_snapshot_async(rp_handle *h, double box_out[9], double *shapes_out, uint64_t n) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(n == h->n, "n == size()");
+    RP_EXPECT(shapes_out != nullptr || n == 0, "shapes_out != NULL");
+    if (box_out) for (int i = 0; i < 9; i++) box_out[i] = h->box.m.a[i];
+    if (n > 0) {
+        if (!h->snapStream) {
+            RP_CUDA(cudaStreamCreateWithFlags(&h->snapStream, cudaStreamNonBlocking));
+            RP_CUDA(cudaEventCreateWithFlags(&h->snapReady, cudaEventDisableTiming));
+            RP_CUDA(cudaEventCreateWithFlags(&h->snapDone, cudaEventDisableTiming));
+        }
+        const size_t bytes = n * 12 * sizeof(double);
+        // the previous snapshot still reads the device-side copy: the pack below must come after it
+        if (h->snapPending) RP_CUDA(cudaStreamWaitEvent(h->stream, h->snapDone, 0));
+        if (bytes > h->dSnapCap) {
+            if (h->snapPending) RP_CUDA(cudaEventSynchronize(h->snapDone));
+            if (h->dSnap) cudaFree(h->dSnap);
+            h->dSnap = nullptr;
+            RP_CUDA(cudaMalloc(&h->dSnap, bytes + 64));
+            h->dSnapCap = bytes + 64;
+        }
+        const int total = static_cast<int>(n * 12);
+        k_pack_shapes<<<(total + 255) / 256, 256, 0, h->stream>>>(static_cast<int>(n), h->cap, h->pos, h->orient,
+                                                                  static_cast<double *>(h->dSnap));
+        h->launches++;
+        RP_CUDA(cudaEventRecord(h->snapReady, h->stream));
+        RP_CUDA(cudaStreamWaitEvent(h->snapStream, h->snapReady, 0));
+        RP_CUDA(cudaMemcpyAsync(shapes_out, h->dSnap, bytes, cudaMemcpyDeviceToHost, h->snapStream));
+        RP_CUDA(cudaEventRecord(h->snapDone, h->snapStream));
+        h->snapPending = true;
+    }
+    RP_API_END(h)
+}
+
+rp_status rp_snapshot_wait(rp_handle *h) {
+    RP_API_BEGIN(h)
+    if (h->snapPending) {
+        RP_CUDA(cudaEventSynchronize(h->snapDone));
+        h->snapPending = false;
+    }
+    RP_API_END(h)
+}
+
+rp_status rp_snapshot_done(rp_handle *h, int32_t *done_out) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(done_out != nullptr, "done_out != NULL");
+    *done_out = 1;
+    if (h->snapPending) {
+        cudaError_t e = cudaEventQuery(h->snapDone);
+        if (e == cudaErrorNotReady) *done_out = 0;
+        else {
+            RP_CUDA(e);
+            h->snapPending = false;
+        }
     }
     RP_API_END(h)
 }

@@ -190,6 +190,12 @@ struct Handle {
     size_t stageCap = 0;
     void *dStage = nullptr;       // device staging for AoS <-> SoA transposes
     size_t dStageCap = 0;
+    // asynchronous snapshot (rp_snapshot_async): device-side copy + second stream
+    void *dSnap = nullptr;
+    size_t dSnapCap = 0;
+    cudaStream_t snapStream = nullptr;
+    cudaEvent_t snapReady = nullptr, snapDone = nullptr;
+    bool snapPending = false;
 
     // spatial sharding over the GPUs of one node (rp_shard.cuh); nullptr = single GPU
     struct Shard *shard = nullptr;

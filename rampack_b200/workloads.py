@@ -85,23 +85,23 @@ EXTRA_CONFIGS = {
     "hs_1k_gas": dict(desc=_desc_sphere, lattice=((10, 10, 10), (10.0, 10.0, 10.0), False), cpu_cells=(10, 10, 10),
                       p=0.1, moves=(10.0, 0.1), scaler=("delta_v", 1000.0), flops=(12, 0), therm=2000),
     "hs_1m_liquid": dict(desc=_desc_sphere, lattice=((100, 100, 100), (1.1, 1.1, 1.1), False), cpu_cells=(30, 30, 30),
-                         p=5.0, moves=(0.1, 0.1), scaler=("delta_v", 50.0), flops=(12, 0), therm=1000),
+                         p=5.0, moves=(0.1, 0.1), scaler=("delta_v", 0.5), flops=(12, 0), therm=2000),
     # C2: hard spherocylinders L/D = 5, N = 100 352, pressure scan (isotropic / nematic / smectic side of the scan)
     "sc_100k_p0.8": dict(desc=_desc_sc, lattice=((56, 56, 32), (1.2, 1.2, 6.5), False), cpu_cells=(28, 28, 16),
-                         p=0.8, moves=(0.05, 0.05), scaler=("delta_triclinic", 0.01, False), flops=(14, 105),
-                         therm=3000),
+                         p=0.8, moves=(0.05, 0.05), scaler=("delta_triclinic", 3e-5, False), flops=(14, 105),
+                         therm=15000, observe=("nematic",)),
     "sc_100k_p1.4": dict(desc=_desc_sc, lattice=((56, 56, 32), (1.2, 1.2, 6.5), False), cpu_cells=(28, 28, 16),
-                         p=1.4, moves=(0.05, 0.05), scaler=("delta_triclinic", 0.01, False), flops=(14, 105),
-                         therm=3000),
+                         p=1.4, moves=(0.05, 0.05), scaler=("delta_triclinic", 3e-5, False), flops=(14, 105),
+                         therm=5000, observe=("nematic",)),
     "sc_100k_p2.0": dict(desc=_desc_sc, lattice=((56, 56, 32), (1.2, 1.2, 6.5), False), cpu_cells=(28, 28, 16),
-                         p=2.0, moves=(0.05, 0.05), scaler=("delta_triclinic", 0.01, False), flops=(14, 105),
-                         therm=3000),
+                         p=2.0, moves=(0.05, 0.05), scaler=("delta_triclinic", 3e-5, False), flops=(14, 105),
+                         therm=5000, observe=("nematic",)),
     # C3: 4-mers and a XenoCollide convex body, N = 2 * 10^5, started 10 % (linear) too dense with overlap counting
     "kmer4_200k": dict(desc=lambda: kmer_desc(4), lattice=((58, 58, 60), (1.25, 1.25, 4.3), False),
-                       cpu_cells=(14, 14, 15), p=20.0, moves=(0.1, 0.1), scaler=("delta_v", 50.0), flops=(13, 0),
+                       cpu_cells=(20, 20, 20), p=20.0, moves=(0.1, 0.1), scaler=("delta_v", 1.5), flops=(13, 0),
                        relax=0.9, therm=200),
-    "convex_200k": dict(desc=convex_desc, lattice=((58, 58, 60), (1.5, 1.5, 2.3), False), cpu_cells=(14, 14, 15),
-                        p=4.0, moves=(0.1, 0.1), scaler=("delta_v", 50.0), flops=(20, 400), relax=0.9, therm=200),
+    "convex_200k": dict(desc=convex_desc, lattice=((58, 58, 60), (1.5, 1.5, 2.3), False), cpu_cells=(20, 20, 20),
+                        p=4.0, moves=(0.1, 0.1), scaler=("delta_v", 1.0), flops=(20, 400), relax=0.9, therm=200),
     # C4: soft 3-mers (energy path), N = 5 * 10^5 (1.5 * 10^6 interaction centres)
     "kmer3_wca_500k": dict(desc=lambda: kmer_desc(3, soft=capi.RP_SOFT_WCA, hard=False),
                            lattice=((80, 80, 79), (1.35, 1.35, 3.3), True), cpu_cells=(20, 20, 20), p=1.0,

@@ -284,7 +284,8 @@ void rp_destroy(rp_handle *h) {
                     (void *) h->lastPos, (void *) h->lastCabs, (void *) h->tmpState, (void *) h->dCounters,
                     (void *) h->dFlags, (void *) h->dCellEnergy, (void *) h->dMoveOut, h->dStage,
                     (void *) h->sweepMoved, (void *) h->trialRec, (void *) h->trialOrient, h->trialMeta, h->trialRec32,
-                    (void *) h->genRec, (void *) h->genTrialRec, (void *) h->genTrialCrel, (void *) h->genTrialU})
+                    (void *) h->genRec, (void *) h->genTrialRec, (void *) h->genTrialCrel, (void *) h->genTrialU,
+                    (void *) h->genCull, (void *) h->genTrialCull})
         if (p) cudaFree(p);
     shardDestroy(h);
     if (h->dXc) cudaFree(h->dXc);

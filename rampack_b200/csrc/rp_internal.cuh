@@ -155,6 +155,7 @@ struct Handle {
     unsigned long long sweepCellsSkipped = 0;   // cells a sweep left out because the staging capacity was too small
     unsigned long long sweepSerial = 0;         // rp_sweep calls made on this handle (timing ring)
     unsigned long long simCycles = 0;           // cycles run by rp_sim loops on this handle (Philox counter of their sweeps)
+    size_t genSmemConfigured[16] = {};     // ... of the k_gen_sweep instantiations (hard kind * 2 + soft)
     size_t smemConfigured[16] = {};   // cudaFuncAttributeMaxDynamicSharedMemorySize set per kernel variant
     size_t trialCap = 0;
     // what rp_sweep_trace needs to know about the last rp_sweep call
@@ -165,6 +166,8 @@ struct Handle {
     V3 lastImageShift[8];
     // generic sweep (rp_sweep_generic.cuh): whole-particle records in cell order and the trial buffers
     double *genRec = nullptr, *genTrialRec = nullptr, *genTrialCrel = nullptr, *genTrialU = nullptr;
+    double *genCull = nullptr, *genTrialCull = nullptr;      // float4 per slot: FP32 cull points (rp_sweep_generic.cuh)
+    size_t genCullCap = 0, genTrialCullCap = 0;
     size_t genRecCap = 0, genTrialRecCap = 0, genTrialCrelCap = 0, genTrialUCap = 0;
 
     // explicit trial move (Packing's temp slot): pos[3] orient[9] crel[16][3] cabs[16][3]

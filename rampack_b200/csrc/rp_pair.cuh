@@ -62,9 +62,10 @@ RP_HD bool scFull(const Inter &I, V3 pos1, V3 axis1, V3 pos2bc, V3 axis2) {
 }
 
 // Interaction::overlapBetween for (centre c1 at pos1 with aux1) vs (centre c2 at pos2 with aux2)
-template <typename BC>
+// (HARDK >= 0: the hard kind is a compile-time constant of the calling kernel and the switch folds away)
+template <int HARDK = -1, typename BC>
 RP_HD bool overlapBetween(const Inter &I, V3 pos1, V3 aux1, int c1, V3 pos2, V3 aux2, int c2, const BC &bc) {
-    switch (I.hard) {
+    switch (HARDK >= 0 ? HARDK : I.hard) {
         case RP_HARD_SPHERE:
             return bc.distance2(pos1, pos2) < I.sphereThr2;
         case RP_HARD_SPHEROCYLINDER: {

@@ -591,10 +591,30 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
     T.wall = h->wallMask ? reinterpret_cast<int2 *>(h->genTrialU + 2 * h->n) : nullptr;
     T.meta = static_cast<uint2 *>(h->trialMeta);
 
+    devEnsure(h->genCull, h->genCullCap, 2 * h->n);          // float4 per slot
+    devEnsure(h->genTrialCull, h->genTrialCullCap, 2 * h->n);
+    float4 *cull = reinterpret_cast<float4 *>(h->genCull);
+    T.cull = reinterpret_cast<float4 *>(h->genTrialCull);
+    {
+        // FP32 cull of mass-centre distances: the FP64 test inside pairTerms (cullRange2) stays the deciding one; the
+        // margin covers the rounding of cell-relative coordinates (|x| < a few cell widths, ulp ~ 1e-6)
+        const double t32 = tr * (1 + 1e-4) + 1e-3;
+        A.cull32Thr2 = I.soft == RP_SOFT_LJ ? std::numeric_limits<float>::infinity()
+                                            : std::nextafterf(static_cast<float>(t32 * t32), INFINITY);
+    }
+    SweepCellOffsets off;
+    for (int code = 0; code < 27; code++) {
+        V3 o = relToAbs(h->box, v3((code % 3 - 1) * sg.relCell[0], ((code / 3) % 3 - 1) * sg.relCell[1],
+                                   (code / 9 - 1) * sg.relCell[2]));
+        off.o[code][0] = static_cast<float>(o.x); off.o[code][1] = static_cast<float>(o.y);
+        off.o[code][2] = static_cast<float>(o.z);
+    }
+
     int recBlocks = static_cast<int>((static_cast<size_t>(g.numCells) * 32 + 255) / 256);
     k_gen_records<<<recBlocks, 256, 0, st>>>(g.numCells, A, sg, h->box, h->dInter, g.cellStart, g.itemsTmp, g.keys,
-                                             h->pos, h->orient, h->crel, g.items, h->genRec);
-    h->launches++;
+                                             h->pos, h->orient, h->crel, g.items, h->genRec, cull);
+    k_sweep_neighbourhood<<<(g.numCells + 255) / 256, 256, 0, st>>>(g.numCells, sg, g.cellStart, &h->dFlags[2]);
+    h->launches += 2;
     RP_CUDA(cudaEventRecord(ev[1], st));
     int flags[4];
     RP_CUDA(cudaMemcpyAsync(flags, h->dFlags, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -602,26 +622,63 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
     RP_CUDA(cudaGetLastError());
     g.maxPopulation = flags[1];
     A.capOwn = std::max(g.maxPopulation, 1);
-    size_t smem = static_cast<size_t>(A.capOwn) * (16 * recw + 48) + 64;
+    A.capOld = std::max(flags[2], 1);
+    A.matrices = (h->overlapCounting && I.hard != RP_HARD_NONE) || I.soft != RP_SOFT_NONE || A.capOwn > GEN_MAXOWN;
+    if (A.capOwn > 2 * GEN_MAXOWN)
+        throw rp_error(RP_ERR_CAPACITY, "rp_sweep: more than 128 particles in one cell of the sweep grid");
+    const size_t smem = genSmemBytes(A.capOld, A.capOwn, static_cast<int>(recw), A.matrices != 0);
     if (smem > 200 * 1024)
         throw rp_error(RP_ERR_CAPACITY, "rp_sweep: a cell does not fit into shared memory");
-    static size_t configured = 0;
-    if (smem > configured) {
-        RP_CUDA(cudaFuncSetAttribute(k_gen_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     static_cast<int>(std::max<size_t>(smem, 48 * 1024))));
-        configured = std::max<size_t>(smem, 48 * 1024);
-    }
     RP_CUDA(cudaEventRecord(ev[2], st));
     k_gen_trials<<<(n + 127) / 128, 128, 0, st>>>(n, A, sg, h->box, h->dInter, g.items, g.keys, h->genRec, h->orient,
                                                   h->crel, T, makeWalls(h->box, h->wallMask, I.totalRange), h->pos);
     h->launches++;
+    const int blocks = A.nActive[0] * A.nActive[1] * A.nActive[2];
+    const bool softOn = I.soft != RP_SOFT_NONE;
     for (int c = 0; c < 8; c++) {
         GenArgs Ac = A;
         int col = colourOrder[c];
         Ac.colour[0] = col & 1; Ac.colour[1] = (col >> 1) & 1; Ac.colour[2] = (col >> 2) & 1;
-        int blocks = A.nActive[0] * A.nActive[1] * A.nActive[2];
-        k_gen_sweep<<<blocks, GEN_THREADS, smem, st>>>(Ac, sg, h->box, h->dInter, g.cellStart, g.items, h->genRec, T,
-                                                       h->pos, h->orient, h->crel, h->cabs, h->dCounters, h->dFlags);
+        // one instantiation per (hard kind, soft potential present): the pair function is a compile-time constant
+        auto launch = [&](auto kernel, int slotIndex) {
+            size_t &configured = h->genSmemConfigured[slotIndex];
+            if (smem > configured) {
+                const size_t want = std::max<size_t>(smem, 48 * 1024);
+                RP_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             static_cast<int>(want)));
+                configured = want;
+            }
+            kernel<<<blocks, GEN_THREADS, smem, st>>>(Ac, sg, off, h->box, h->dInter, g.cellStart, g.items, h->genRec,
+                                                      cull, T, h->pos, h->orient, h->crel, h->cabs, h->dCounters,
+                                                      h->dFlags);
+        };
+        const int slotIndex = I.hard * 2 + (softOn ? 1 : 0);
+        switch (I.hard) {
+            case RP_HARD_NONE:
+                launch(k_gen_sweep<RP_HARD_NONE, true>, slotIndex); break;
+            case RP_HARD_SPHERE:
+                if (softOn) launch(k_gen_sweep<RP_HARD_SPHERE, true>, slotIndex);
+                else launch(k_gen_sweep<RP_HARD_SPHERE, false>, slotIndex);
+                break;
+            case RP_HARD_SPHEROCYLINDER:
+                if (softOn) launch(k_gen_sweep<RP_HARD_SPHEROCYLINDER, true>, slotIndex);
+                else launch(k_gen_sweep<RP_HARD_SPHEROCYLINDER, false>, slotIndex);
+                break;
+            case RP_HARD_POLYSPHERE:
+                if (softOn) launch(k_gen_sweep<RP_HARD_POLYSPHERE, true>, slotIndex);
+                else launch(k_gen_sweep<RP_HARD_POLYSPHERE, false>, slotIndex);
+                break;
+            case RP_HARD_POLYSPHEROCYLINDER:
+                if (softOn) launch(k_gen_sweep<RP_HARD_POLYSPHEROCYLINDER, true>, slotIndex);
+                else launch(k_gen_sweep<RP_HARD_POLYSPHEROCYLINDER, false>, slotIndex);
+                break;
+            case RP_HARD_XENOCOLLIDE:
+                if (softOn) launch(k_gen_sweep<RP_HARD_XENOCOLLIDE, true>, slotIndex);
+                else launch(k_gen_sweep<RP_HARD_XENOCOLLIDE, false>, slotIndex);
+                break;
+            default:
+                throw rp_error(RP_ERR_UNSUPPORTED, "rp_sweep: unknown hard interaction kind");
+        }
         h->launches++;
     }
     RP_CUDA(cudaEventRecord(ev[3], st));

@@ -43,8 +43,10 @@ struct GenArgs {
     unsigned long long seed;
     unsigned int cycle, pass;
     int colour[3], nActive[3];
-    int capOwn;
+    int capOwn, capOld;      // shared-memory capacities: particles of the active cell / frozen candidates around it
+    float cull32Thr2;        // FP32 cull of mass-centre distances (conservative: cull range + rounding); LJ: +inf
     int counting;            // Packing::overlapCounting
+    int matrices;            // in-cell pair terms as matrices (counting / soft / > 64 particles per cell) or bit masks
     // RP_MOVE_FLIP (FlipSampler.cpp:18-41): body-frame flip axis, geometric origin, attempt probability 1 / flipEvery
     double flipAxis[3], flipOrigin[3], flipProb;
     int flipOriginZero;
@@ -63,6 +65,7 @@ struct GenTrialBuffers {
     double *dE;        // written by k_gen_sweep: the value Packing::tryMove would have returned (rp_sweep_trace)
     uint2 *meta;       // x: 0 alive / 2 left the cell, y: order key
     int2 *wall;        // wall overlaps of the {old, new} state (Packing::countParticleWallOverlaps); nullptr: no walls
+    float4 *cull;      // FP32 cull point of the trial state (mass centre relative to the centre of the own cell)
 };
 
 __device__ __forceinline__ V3 ld3(const double *p) { return v3(p[0], p[1], p[2]); }
@@ -99,12 +102,18 @@ __device__ __forceinline__ void fillRecord(const Inter &I, const GenArgs &A, con
             reinterpret_cast<long long *>(r)[L.offCell + c] = packRefCell(box, A.refRelCell, ld3(r + L.offCentre + 3 * c));
 }
 
-// one warp per cell: items by ascending particle index + the generic records (image frame)
+// FP32 cull point of a particle state: mass centre relative to the centre of the particle's own sweep cell
+__device__ __forceinline__ float4 genCullPoint(const V3 &p, const V3 &centre) {
+    return make_float4(static_cast<float>(p.x - centre.x), static_cast<float>(p.y - centre.y),
+                       static_cast<float>(p.z - centre.z), 0.f);
+}
+
+// one warp per cell: items by ascending particle index + the generic records (image frame) + the FP32 cull points
 __global__ void k_gen_records(int numCells, GenArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr,
                               const int *__restrict__ cellStart, const int *__restrict__ itemsTmp,
                               const int *__restrict__ keys, const double *__restrict__ pos,
                               const double *__restrict__ orient, const double *__restrict__ crelAll,
-                              int *__restrict__ items, double *__restrict__ rec)
+                              int *__restrict__ items, double *__restrict__ rec, float4 *__restrict__ cull)
 {
     __shared__ Inter I;
     for (int i = threadIdx.x; i < static_cast<int>(sizeof(Inter) / sizeof(int)); i += blockDim.x)
@@ -114,6 +123,7 @@ __global__ void k_gen_records(int numCells, GenArgs A, SweepGrid sg, Box box, co
     int lane = threadIdx.x & 31;
     if (cell >= numCells) return;
     int start = cellStart[cell], cnt = cellStart[cell + 1] - start;
+    const V3 centre = sweepCellCentre(sg, box, cell % sg.n[0], (cell / sg.n[0]) % sg.n[1], cell / (sg.n[0] * sg.n[1]));
     for (int i = lane; i < cnt; i += 32) {
         int id = itemsTmp[start + i];
         int rank = 0;
@@ -131,6 +141,7 @@ __global__ void k_gen_records(int numCells, GenArgs A, SweepGrid sg, Box box, co
             crel[c] = v3(crelAll[idx], crelAll[A.ccap + idx], crelAll[2 * A.ccap + idx]);
         }
         fillRecord(I, A, box, rec + static_cast<size_t>(slot) * A.L.recw, p, o, crel);
+        cull[slot] = genCullPoint(p, centre);
     }
 }
 
@@ -247,6 +258,7 @@ __global__ void __launch_bounds__(128) k_gen_trials(int n, GenArgs A, SweepGrid 
         T.wall[slot] = make_int2(wallOld, wallNew);
     }
     fillRecord(I, A, box, T.rec + static_cast<size_t>(slot) * A.L.recw, p, O, crel);
+    T.cull[slot] = genCullPoint(p, sweepCellCentre(sg, box, cc[0], cc[1], cc[2]));
     double *o = T.orient + 9 * static_cast<size_t>(slot);
     for (int q = 0; q < 9; q++) o[q] = O.a[q];
     for (int c = 0; c < I.k; c++) st3(T.crel + (static_cast<size_t>(slot) * I.k + c) * 3, crel[c]);
@@ -260,6 +272,8 @@ __global__ void __launch_bounds__(128) k_gen_trials(int n, GenArgs A, SweepGrid 
 // Pair terms between two particles given as records: `a` (own, untranslated) and `b` (+ lattice translation t with
 // integer lattice coordinates g).  Adds the number of overlapping centre pairs to *ov (stops at the first one when
 // firstOnly) and the pair energies to *en.  Loops like Packing::countParticleOverlaps / calculateParticleEnergy.
+// HARD / SOFT are compile-time constants of the calling kernel: one instantiation carries one pair function.
+template <int HARD, bool SOFT>
 __device__ __forceinline__ void pairTerms(const Inter &I, const GenArgs &A, const double *a, const double *b, V3 t,
                                           int gx, int gy, int gz, bool wantOv, bool wantEn, bool firstOnly,
                                           int *ov, double *en)
@@ -268,25 +282,28 @@ __device__ __forceinline__ void pairTerms(const Inter &I, const GenArgs &A, cons
     V3 pa = ld3(a), pb = ld3(b) + t;
     if (!(norm2(pb - pa) < A.cullRange2)) return;
     BcFixed bc{t};
+    constexpr bool HAS_AUX = HARD == RP_HARD_SPHEROCYLINDER || HARD == RP_HARD_POLYSPHEROCYLINDER;
     for (int c1 = 0; c1 < L.kk; c1++) {
         V3 pos1 = ld3(a + L.offCentre + 3 * c1);
-        V3 aux1 = L.offAux >= 0 ? ld3(a + L.offAux + 3 * c1) : v3(0, 0, 0);
+        V3 aux1 = HAS_AUX ? ld3(a + L.offAux + 3 * c1) : v3(0, 0, 0);
         for (int c2 = 0; c2 < L.kk; c2++) {
             V3 pos2 = ld3(b + L.offCentre + 3 * c2);
-            if (wantOv) {
-                V3 aux2 = L.offAux >= 0 ? ld3(b + L.offAux + 3 * c2) : v3(0, 0, 0);
-                const bool hit = needsOrientation(I)
-                    ? overlapBetweenOriented(I, pos1, [&] { M33 o; for (int q = 0; q < 9; q++) o.a[q] = a[L.offOrient + q]; return o; },
-                                             c1, pos2,
-                                             [&] { M33 o; for (int q = 0; q < 9; q++) o.a[q] = b[L.offOrient + q]; return o; },
-                                             c2, bc)
-                    : overlapBetween(I, pos1, aux1, c1, pos2, aux2, c2, bc);
+            if (HARD != RP_HARD_NONE && wantOv) {
+                bool hit;
+                if (HARD == RP_HARD_XENOCOLLIDE) {
+                    hit = overlapBetweenOriented(
+                        I, pos1, [&] { M33 o; for (int q = 0; q < 9; q++) o.a[q] = a[L.offOrient + q]; return o; }, c1,
+                        pos2, [&] { M33 o; for (int q = 0; q < 9; q++) o.a[q] = b[L.offOrient + q]; return o; }, c2, bc);
+                } else {
+                    V3 aux2 = HAS_AUX ? ld3(b + L.offAux + 3 * c2) : v3(0, 0, 0);
+                    hit = overlapBetween<HARD>(I, pos1, aux1, c1, pos2, aux2, c2, bc);
+                }
                 if (hit) {
                     (*ov)++;
                     if (firstOnly) return;
                 }
             }
-            if (wantEn) {
+            if (SOFT && wantEn) {
                 if (L.offCell >= 0) {
                     long long ca = reinterpret_cast<const long long *>(a)[L.offCell + c1];
                     long long cb = reinterpret_cast<const long long *>(b)[L.offCell + c2];
@@ -299,19 +316,53 @@ __device__ __forceinline__ void pairTerms(const Inter &I, const GenArgs &A, cons
 }
 
 constexpr int GEN_THREADS = 128;
+constexpr int GEN_MAXOWN = 64;       // trials per cell the bit masks of the hard-only resolution cover
 
+// shared memory of k_gen_sweep beyond its static part, for (capOld frozen candidates, capOwn particles in the cell)
+__host__ __device__ inline size_t genSmemBytes(int capOld, int capOwn, int recw, bool matrices) {
+    size_t b = 16 * static_cast<size_t>(capOld + 2 * capOwn);               // FP32 cull points: candidates, trial + current states
+    b += 2 * static_cast<size_t>(capOwn) * recw * 8;                        // cur, tri
+    b += 3 * static_cast<size_t>(capOwn) * 8;                               // eOld, eNew, uMet
+    b += 2 * static_cast<size_t>(capOwn) * 4;                               // ovOld, ovNew
+    b += (GEN_THREADS / 32) * 64 * 4;                                       // per-warp survivor queues
+    if (matrices) b += 4 * static_cast<size_t>(capOwn) * capOwn * (8 + 2);  // in-cell pair matrices
+    return b + 64;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// k_gen_sweep<HARD, SOFT> — one CTA per active cell.
+//   staging   the FP32 cull points (mass centre relative to the own cell's centre, 16 B) of the 26 frozen cells land
+//             in shared memory by 1-D TMA bulk copies; the FP64 records stay in global memory (L2) and are fetched
+//             for survivors only; the own cell's records (current and trial states) are copied to shared memory
+//   phase 1   one warp per trial: FP32 distance cull of all staged candidates (32 per iteration), survivors are
+//             compacted (ballot) into the warp's queue and take the exact pair terms 32 at a time — every lane busy;
+//             per-trial sums reduce in a fixed order (deterministic)
+//   phase 2a  pair terms inside the cell for every ordered pair (i, j): trial / current state of i against the
+//             current and the trial state of j, all threads in parallel
+//             hard-only: two bit masks per trial; otherwise small matrices of counts and energies
+//   phase 2b  sequential pass in the cell's random order: what used to evaluate pair functions one trial after the
+//             other is now a walk over the precomputed tables (the state of j a term is taken from follows `moved`)
+// The decisions are those of a sequential Monte Carlo pass through the cell, as before.
+// ---------------------------------------------------------------------------------------------------------------
+template <int HARD, bool SOFT>
 __global__ void __launch_bounds__(GEN_THREADS)
-k_gen_sweep(GenArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr, const int *__restrict__ cellStart,
-            const int *__restrict__ items, double *__restrict__ rec, GenTrialBuffers T, double *__restrict__ pos,
-            double *__restrict__ orient, double *__restrict__ crelAll, double *__restrict__ cabsAll,
-            unsigned long long *__restrict__ counters, int *__restrict__ flags)
+k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter *__restrict__ interPtr,
+            const int *__restrict__ cellStart, const int *__restrict__ items, double *__restrict__ rec,
+            float4 *__restrict__ cull, GenTrialBuffers T, double *__restrict__ pos, double *__restrict__ orient,
+            double *__restrict__ crelAll, double *__restrict__ cabsAll, unsigned long long *__restrict__ counters,
+            int *__restrict__ flags)
 {
     constexpr int WARPS = GEN_THREADS / 32;
+    constexpr bool hard = HARD != RP_HARD_NONE, soft = SOFT;
     extern __shared__ __align__(16) unsigned char smemRaw[];
     __shared__ Inter I;
     __shared__ int cellBegin[28], cellSrc[27], cellT[27];
     __shared__ int sStats[5];
     __shared__ long long sOverlapDelta;
+    __shared__ unsigned long long sBar;
+    __shared__ unsigned long long ownMask[GEN_MAXOWN], newMask[GEN_MAXOWN];
+    __shared__ int rejected[GEN_MAXOWN * 2], seq[GEN_MAXOWN * 2];
+    __shared__ unsigned int orderKey[GEN_MAXOWN * 2];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const GenLayout &L = A.L;
@@ -319,46 +370,78 @@ k_gen_sweep(GenArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr
     for (int i = tid; i < static_cast<int>(sizeof(Inter) / sizeof(int)); i += GEN_THREADS)
         reinterpret_cast<int *>(&I)[i] = reinterpret_cast<const int *>(interPtr)[i];
 
+    const bool counting = A.counting != 0 && hard;
+    const bool needOld = counting || soft;
+    const bool matrices = A.matrices != 0;      // counting, soft, or a cell too crowded for the 64-bit masks
+
     const int b = blockIdx.x;
     const int a0 = b % A.nActive[0], a1 = (b / A.nActive[0]) % A.nActive[1], a2 = b / (A.nActive[0] * A.nActive[1]);
     const int cx = 2 * a0 + A.colour[0], cy = 2 * a1 + A.colour[1], cz = 2 * a2 + A.colour[2];
-    if (tid < 27) {
-        int tIdx;
-        int c2 = neighbourCell(sg.n, cx, cy, cz, tid % 3 - 1, (tid / 3) % 3 - 1, tid / 9 - 1, &tIdx);
-        cellSrc[tid] = cellStart[c2];
-        cellBegin[tid] = (tid == 13) ? 0 : cellStart[c2 + 1] - cellStart[c2];   // the own cell is not frozen
-        cellT[tid] = tIdx;
-    }
-    if (tid == 0) { sStats[0] = sStats[1] = sStats[2] = sStats[3] = sStats[4] = 0; sOverlapDelta = 0; }
-    __syncthreads();
-    if (tid == 0) {
-        int acc = 0;
-        for (int c = 0; c < 27; c++) { int n = cellBegin[c]; cellBegin[c] = acc; acc += n; }
-        cellBegin[27] = acc;
-    }
     const int ownCell = (cz * sg.n[1] + cy) * sg.n[0] + cx;
     const int ownStart = cellStart[ownCell], numOwn = cellStart[ownCell + 1] - ownStart;
     if (numOwn == 0) return;
-    if (numOwn > A.capOwn) {
-        if (tid == 0) atomicOr(&flags[3], 1);
-        return;
-    }
-    __syncthreads();
-    const int numFrozen = cellBegin[27];
 
-    // shared memory: current states and trial states of the own cell, per-trial accumulators
-    double *cur = reinterpret_cast<double *>(smemRaw);
+    // dynamic shared memory
+    float4 *cand = reinterpret_cast<float4 *>(smemRaw);
+    float4 *trialPt = cand + A.capOld;
+    float4 *curPt = trialPt + A.capOwn;
+    double *cur = reinterpret_cast<double *>(curPt + A.capOwn);
     double *tri = cur + static_cast<size_t>(A.capOwn) * recw;
     double *eOld = tri + static_cast<size_t>(A.capOwn) * recw;
     double *eNew = eOld + A.capOwn;
     double *uMet = eNew + A.capOwn;
     int *ovOld = reinterpret_cast<int *>(uMet + A.capOwn);
     int *ovNew = ovOld + A.capOwn;
-    int *rejected = ovNew + A.capOwn;
-    int *seq = rejected + A.capOwn;
-    int *accepted = seq + A.capOwn;
-    unsigned int *orderKey = reinterpret_cast<unsigned int *>(accepted + A.capOwn);
+    int *queue = ovNew + A.capOwn;
+    // in-cell matrices, row i = trial, column j = other particle: [0] new_i/old_j [1] old_i/old_j [2] new_i/new_j
+    // [3] old_i/new_j
+    double *eMat = reinterpret_cast<double *>(queue + WARPS * 64);
+    short *cMat = reinterpret_cast<short *>(eMat + 4 * static_cast<size_t>(A.capOwn) * A.capOwn);
+    const size_t matStride = static_cast<size_t>(A.capOwn) * A.capOwn;
 
+    // ---- cell table + staging (warp 0) ----
+    if (warp == 0) {
+        int cnt = 0, src = 0, tIdx = 13;
+        if (lane < 27) {
+            const int c2 = neighbourCell(sg.n, cx, cy, cz, lane % 3 - 1, (lane / 3) % 3 - 1, lane / 9 - 1, &tIdx);
+            src = cellStart[c2];
+            cnt = lane == 13 ? 0 : cellStart[c2 + 1] - src;      // the own cell is not frozen
+        }
+        if (lane == 0) {
+            sStats[0] = sStats[1] = sStats[2] = sStats[3] = sStats[4] = 0;
+            sOverlapDelta = 0;
+            mbarInit(&sBar, 1);
+        }
+        int incl = cnt;
+        #pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int v = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += v;
+        }
+        const int total = __shfl_sync(0xffffffffu, incl, 26);
+        const bool ok = total <= A.capOld && numOwn <= A.capOwn;
+        if (lane == 0 && ok) mbarExpectTx(&sBar, static_cast<unsigned int>((total + 2 * numOwn) * 16));
+        __syncwarp();
+        if (lane < 27) {
+            cellBegin[lane] = incl - cnt;
+            cellT[lane] = tIdx;
+            cellSrc[lane] = src;
+            if (lane == 26) cellBegin[27] = incl;
+            if (ok && cnt > 0)
+                bulkCopyG2S(cand + (incl - cnt), cull + src, static_cast<unsigned int>(cnt * 16), &sBar);
+        } else if (lane == 27 && ok) {
+            bulkCopyG2S(trialPt, T.cull + ownStart, static_cast<unsigned int>(numOwn * 16), &sBar);
+        } else if (lane == 28 && ok) {
+            bulkCopyG2S(curPt, cull + ownStart, static_cast<unsigned int>(numOwn * 16), &sBar);
+        }
+    }
+    __syncthreads();
+    const int numFrozen = cellBegin[27];
+    if (numFrozen > A.capOld || numOwn > A.capOwn) {
+        if (tid == 0) atomicOr(&flags[3], 1);
+        return;
+    }
+    // own cell: current and trial records, trial meta
     for (int i = tid; i < numOwn * recw; i += GEN_THREADS) {
         cur[i] = rec[static_cast<size_t>(ownStart) * recw + i];
         tri[i] = T.rec[static_cast<size_t>(ownStart) * recw + i];
@@ -368,51 +451,97 @@ k_gen_sweep(GenArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr
         rejected[i] = static_cast<int>(meta.x);
         orderKey[i] = meta.y;
         uMet[i] = T.u[ownStart + i];
-        accepted[i] = 0;
+        if (i < GEN_MAXOWN) { ownMask[i] = 0ull; newMask[i] = 0ull; }
+    }
+    if (warp == 0) mbarWait(&sBar, 0);
+    __syncthreads();
+    // frozen cull points move into the frame of the active cell (centre-to-centre vector incl. the periodic image)
+    for (int c = warp; c < 27; c += WARPS) {
+        const int begin = cellBegin[c], cnt = cellBegin[c + 1] - begin;
+        const float ox = off.o[c][0], oy = off.o[c][1], oz = off.o[c][2];
+        for (int j = begin + lane; j < begin + cnt; j += 32) {
+            float4 r = cand[j];
+            r.x += ox; r.y += oy; r.z += oz;
+            cand[j] = r;
+        }
     }
     __syncthreads();
 
-    const bool hard = I.hard != RP_HARD_NONE, soft = I.soft != RP_SOFT_NONE;
-    const bool counting = A.counting != 0 && hard;
-    const bool needOld = counting || soft;
-
     // ---- phase 1: frozen neighbours, one warp per trial ----
-    for (int i = warp; i < numOwn; i += WARPS) {
-        int oO = 0, oN = 0;
-        double enO = 0, enN = 0;
-        if (rejected[i] == 0) {
-            const double *ta = tri + static_cast<size_t>(i) * recw, *oa = cur + static_cast<size_t>(i) * recw;
-            for (int base = 0; base < numFrozen; base += 32) {
-                const int jj = base + lane;
-                if (jj < numFrozen) {
-                    int c = 0;
-                    #pragma unroll
-                    for (int s = 16; s > 0; s >>= 1) if (c + s < 27 && cellBegin[c + s] <= jj) c += s;
-                    const double *rb = rec + static_cast<size_t>(cellSrc[c] + (jj - cellBegin[c])) * recw;
-                    const int tIdx = cellT[c];
-                    const V3 t = sg.trans[tIdx];
-                    const int gx = tIdx / 9 - 1, gy = (tIdx / 3) % 3 - 1, gz = tIdx % 3 - 1;
-                    pairTerms(I, A, ta, rb, t, gx, gy, gz, hard, soft, !counting, &oN, &enN);
-                    if (needOld) pairTerms(I, A, oa, rb, t, gx, gy, gz, counting, soft, false, &oO, &enO);
+    {
+        int *q = queue + warp * 64;
+        const unsigned int ltMask = (1u << lane) - 1u;
+        for (int i = warp; i < numOwn; i += WARPS) {
+            int oO = 0, oN = 0;
+            double enO = 0, enN = 0;
+            if (rejected[i] == 0) {
+                const double *ta = tri + static_cast<size_t>(i) * recw, *oa = cur + static_cast<size_t>(i) * recw;
+                // a candidate passes when it is within the cull range of the trial state or (where the old state's
+                // terms are needed) of the current state
+                const float4 pt = trialPt[i], po = curPt[i];
+                int qn = 0;
+                bool stop = false;
+                auto exact = [&](int jj, bool valid) {
+                    if (valid) {
+                        int c = 0;
+                        #pragma unroll
+                        for (int s = 16; s > 0; s >>= 1) if (c + s < 27 && cellBegin[c + s] <= jj) c += s;
+                        const double *rb = rec + static_cast<size_t>(cellSrc[c] + (jj - cellBegin[c])) * recw;
+                        const int tIdx = cellT[c];
+                        const V3 t = sg.trans[tIdx];
+                        const int gx = tIdx / 9 - 1, gy = (tIdx / 3) % 3 - 1, gz = tIdx % 3 - 1;
+                        pairTerms<HARD, SOFT>(I, A, ta, rb, t, gx, gy, gz, hard, soft, !counting, &oN, &enN);
+                        if (needOld)
+                            pairTerms<HARD, SOFT>(I, A, oa, rb, t, gx, gy, gz, counting, soft, false, &oO, &enO);
+                    }
+                    // early exit like Packing::countParticleOverlaps(earlyExit = true)
+                    if (!counting && hard && __any_sync(0xffffffffu, oN > 0)) stop = true;
+                };
+                for (int base = 0; base < numFrozen && !stop; base += 32) {
+                    const int jj = base + lane;
+                    bool pass = false;
+                    if (jj < numFrozen) {
+                        const float4 c = cand[jj];
+                        const float dx = c.x - pt.x, dy = c.y - pt.y, dz = c.z - pt.z;
+                        pass = !(fmaf(dz, dz, fmaf(dy, dy, dx * dx)) >= A.cull32Thr2);
+                        if (needOld) {
+                            const float ex = c.x - po.x, ey = c.y - po.y, ez = c.z - po.z;
+                            pass = pass || !(fmaf(ez, ez, fmaf(ey, ey, ex * ex)) >= A.cull32Thr2);
+                        }
+                    }
+                    const unsigned int m = __ballot_sync(0xffffffffu, pass);
+                    if (pass) q[qn + __popc(m & ltMask)] = jj;
+                    qn += __popc(m);
+                    __syncwarp();
+                    if (qn >= 32) {
+                        qn -= 32;
+                        exact(q[qn + lane], true);
+                        __syncwarp();
+                    }
                 }
-                // early exit like Packing::countParticleOverlaps(earlyExit = true)
-                if (!counting && hard && __any_sync(0xffffffffu, oN > 0)) break;
+                if (qn > 0 && !stop) exact(lane < qn ? q[lane] : 0, lane < qn);
+                __syncwarp();
             }
-        }
-        #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            oO += __shfl_xor_sync(0xffffffffu, oO, o);
-            oN += __shfl_xor_sync(0xffffffffu, oN, o);
-            enO += __shfl_xor_sync(0xffffffffu, enO, o);
-            enN += __shfl_xor_sync(0xffffffffu, enN, o);
-        }
-        if (lane == 0) {
-            if (T.wall && rejected[i] == 0) {       // + countParticleWallOverlaps (core/Packing.cpp:424-428)
-                const int2 w = T.wall[ownStart + i];
-                oO += w.x;
-                oN += w.y;
+            #pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                oO += __shfl_xor_sync(0xffffffffu, oO, o);
+                oN += __shfl_xor_sync(0xffffffffu, oN, o);
+                if (SOFT) {
+                    enO += __shfl_xor_sync(0xffffffffu, enO, o);
+                    enN += __shfl_xor_sync(0xffffffffu, enN, o);
+                }
             }
-            ovOld[i] = oO; ovNew[i] = oN; eOld[i] = enO; eNew[i] = enN;
+            if (lane == 0) {
+                if (T.wall && rejected[i] == 0) {       // + countParticleWallOverlaps (core/Packing.cpp:424-428)
+                    const int2 w = T.wall[ownStart + i];
+                    oO += w.x;
+                    oN += w.y;
+                }
+                ovOld[i] = oO; ovNew[i] = oN; eOld[i] = enO; eNew[i] = enN;
+                // hard, not counting: a trial that hits a frozen particle (or a wall) is rejected whatever happens
+                // inside the cell (state 1; its row and column of the in-cell tables are never needed)
+                if (!counting && hard && oN > 0 && rejected[i] == 0) rejected[i] = 1;
+            }
         }
     }
     // processing order: rank of the random key
@@ -427,59 +556,107 @@ k_gen_sweep(GenArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr
     }
     __syncthreads();
 
-    // ---- phase 2: sequential pass through the cell (warp 0), other particles of the cell in their CURRENT state ----
+    // ---- phase 2a: pair terms inside the cell, every ordered pair (i, j), all threads ----
+    {
+        const V3 zero = v3(0, 0, 0);
+        for (int p = tid; p < numOwn * numOwn; p += GEN_THREADS) {
+            const int i = p / numOwn, j = p - i * numOwn;
+            if (i == j || rejected[i] != 0) continue;
+            const double *ta = tri + static_cast<size_t>(i) * recw, *oa = cur + static_cast<size_t>(i) * recw;
+            const double *ob = cur + static_cast<size_t>(j) * recw, *tb = tri + static_cast<size_t>(j) * recw;
+            const bool jMayMove = rejected[j] == 0;
+            if (!matrices) {
+                int o1 = 0, o2 = 0;
+                double e = 0;
+                pairTerms<HARD, SOFT>(I, A, ta, ob, zero, 0, 0, 0, true, false, true, &o1, &e);
+                if (o1) atomicOr(&ownMask[i], 1ull << j);
+                if (jMayMove) {
+                    pairTerms<HARD, SOFT>(I, A, ta, tb, zero, 0, 0, 0, true, false, true, &o2, &e);
+                    if (o2) atomicOr(&newMask[i], 1ull << j);
+                }
+            } else {
+                int o[4] = {0, 0, 0, 0};
+                double e[4] = {0, 0, 0, 0};
+                pairTerms<HARD, SOFT>(I, A, ta, ob, zero, 0, 0, 0, hard, soft, !counting, &o[0], &e[0]);
+                pairTerms<HARD, SOFT>(I, A, oa, ob, zero, 0, 0, 0, counting, soft, false, &o[1], &e[1]);
+                if (jMayMove) {
+                    pairTerms<HARD, SOFT>(I, A, ta, tb, zero, 0, 0, 0, hard, soft, !counting, &o[2], &e[2]);
+                    pairTerms<HARD, SOFT>(I, A, oa, tb, zero, 0, 0, 0, counting, soft, false, &o[3], &e[3]);
+                }
+                const size_t at = static_cast<size_t>(i) * A.capOwn + j;
+                #pragma unroll
+                for (int m = 0; m < 4; m++) {
+                    eMat[m * matStride + at] = e[m];
+                    cMat[m * matStride + at] = static_cast<short>(o[m]);
+                }
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- phase 2b: sequential pass through the cell in its random order ----
+    const double INF = __longlong_as_double(0x7ff0000000000000ll);
     if (warp == 0) {
         int nAcc = 0, nRejDomain = 0, nRejOverlap = 0, nRejEnergy = 0, nIdle = 0;
         long long overlapDelta = 0;
-        const V3 zero = v3(0, 0, 0);
+        unsigned long long movedLo = 0ull, movedHi = 0ull;     // particles 0..63 / 64..127 of the cell
         for (int step = 0; step < numOwn; step++) {
             const int i = seq[step];
-            if (rejected[i] == 2) { nRejDomain++; continue; }
-            if (rejected[i] == 5) { nIdle++; continue; }      // RP_MOVE_FLIP: not drawn this cycle
-            const double *ta = tri + static_cast<size_t>(i) * recw, *oa = cur + static_cast<size_t>(i) * recw;
-            int oO = 0, oN = 0;
-            double enO = 0, enN = 0;
-            const bool frozenHit = !counting && hard && ovNew[i] > 0;
-            if (!frozenHit) {
+            const int state = rejected[i];
+            if (state == 2) { nRejDomain++; continue; }
+            if (state == 5) { nIdle++; continue; }      // RP_MOVE_FLIP: not drawn this cycle
+            double dE;
+            long long delta = 0;
+            bool overlapVerdict;
+            if (!matrices) {
+                // hard only: blocked by a frozen particle, by an unmoved neighbour's old state or a moved one's new
+                const bool blocked = state == 1
+                                     || ((ownMask[i] & ~movedLo) | (newMask[i] & movedLo)) != 0ull;
+                dE = blocked ? INF : 0.0;
+                overlapVerdict = blocked;
+            } else {
+                int oO = 0, oN = 0;
+                double enO = 0, enN = 0;
                 for (int base = 0; base < numOwn; base += 32) {
                     const int j = base + lane;
                     if (j < numOwn && j != i) {
-                        const double *rb = cur + static_cast<size_t>(j) * recw;
-                        pairTerms(I, A, ta, rb, zero, 0, 0, 0, hard, soft, !counting, &oN, &enN);
-                        if (needOld) pairTerms(I, A, oa, rb, zero, 0, 0, 0, counting, soft, false, &oO, &enO);
+                        const bool mv = j < 64 ? ((movedLo >> j) & 1ull) != 0ull : ((movedHi >> (j - 64)) & 1ull) != 0ull;
+                        const size_t at = static_cast<size_t>(i) * A.capOwn + j;
+                        oN += cMat[(mv ? 2 : 0) * matStride + at];
+                        oO += cMat[(mv ? 3 : 1) * matStride + at];
+                        if (SOFT) {
+                            enN += eMat[(mv ? 2 : 0) * matStride + at];
+                            enO += eMat[(mv ? 3 : 1) * matStride + at];
+                        }
                     }
-                    if (!counting && hard && __any_sync(0xffffffffu, oN > 0)) break;
                 }
+                #pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    oO += __shfl_xor_sync(0xffffffffu, oO, o);
+                    oN += __shfl_xor_sync(0xffffffffu, oN, o);
+                    if (SOFT) {
+                        enO += __shfl_xor_sync(0xffffffffu, enO, o);
+                        enN += __shfl_xor_sync(0xffffffffu, enN, o);
+                    }
+                }
+                oO += ovOld[i]; oN += ovNew[i];
+                // Packing::calculateMoveOverlapEnergy (Packing.cpp:304-323), then the energy difference
+                if (counting) {
+                    delta = static_cast<long long>(oN) - static_cast<long long>(oO);
+                    dE = delta < 0 ? -INF : (delta > 0 ? INF : 0.0);
+                } else {
+                    dE = (hard && (oN > 0 || state == 1)) ? INF : 0.0;
+                }
+                overlapVerdict = dE != 0;
+                if (!overlapVerdict && soft) dE = (eNew[i] + enN) - (eOld[i] + enO);
             }
-            #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                oO += __shfl_xor_sync(0xffffffffu, oO, o);
-                oN += __shfl_xor_sync(0xffffffffu, oN, o);
-                enO += __shfl_xor_sync(0xffffffffu, enO, o);
-                enN += __shfl_xor_sync(0xffffffffu, enN, o);
-            }
-            oO += ovOld[i]; oN += ovNew[i];
-            // Packing::calculateMoveOverlapEnergy (Packing.cpp:304-323), then the energy difference
-            double dE;
-            long long delta = 0;
-            const double INF = __longlong_as_double(0x7ff0000000000000ll);
-            if (counting) {
-                delta = static_cast<long long>(oN) - static_cast<long long>(oO);
-                dE = delta < 0 ? -INF : (delta > 0 ? INF : 0.0);
-            } else {
-                dE = (hard && oN > 0) ? INF : 0.0;
-            }
-            const bool overlapVerdict = dE != 0;
-            if (!overlapVerdict && soft) dE = (eNew[i] + enN) - (eOld[i] + enO);
             // Simulation::tryMove (Simulation.cpp:483): accept iff u <= exp(-dE / T)
-            const bool accept = uMet[i] <= exp(-dE / A.temperature);
+            const bool accept = (soft || counting) ? (uMet[i] <= exp(-dE / A.temperature)) : !overlapVerdict;
             if (lane == 0) T.dE[ownStart + i] = dE;
             if (accept) {
                 nAcc++;
                 overlapDelta += delta;
-                for (int q = lane; q < recw; q += 32) cur[static_cast<size_t>(i) * recw + q] = ta[q];
-                if (lane == 0) accepted[i] = 1;
-                __syncwarp();
+                if (i < 64) movedLo |= 1ull << i; else movedHi |= 1ull << (i - 64);
             } else if (overlapVerdict) nRejOverlap++;
             else nRejEnergy++;
         }
@@ -487,21 +664,29 @@ k_gen_sweep(GenArgs A, SweepGrid sg, Box box, const Inter *__restrict__ interPtr
             sStats[0] = nAcc; sStats[1] = nRejDomain; sStats[2] = nRejOverlap; sStats[3] = nRejEnergy;
             sStats[4] = nIdle;
             sOverlapDelta = overlapDelta;
+            reinterpret_cast<unsigned long long *>(seq)[0] = movedLo;      // (seq is no longer needed)
+            reinterpret_cast<unsigned long long *>(seq)[1] = movedHi;
         }
     }
     __syncthreads();
+    const unsigned long long movedLo = reinterpret_cast<unsigned long long *>(seq)[0],
+                             movedHi = reinterpret_cast<unsigned long long *>(seq)[1];
 
     // ---- write-back of the accepted moves ----
     const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION || A.kind == RP_MOVE_FLIP);
     const bool translated = (A.kind == RP_MOVE_TRANSLATION || A.kind == RP_MOVE_ROTOTRANSLATION
                              || (A.kind == RP_MOVE_FLIP && !A.flipOriginZero));
     for (int i = warp; i < numOwn; i += WARPS) {
-        if (!accepted[i]) continue;
+        const bool acc = i < 64 ? ((movedLo >> i) & 1ull) != 0ull : ((movedHi >> (i - 64)) & 1ull) != 0ull;
+        if (!acc) continue;
         const int slot = ownStart + i;
         const int id = items[slot];
-        const double *t = cur + static_cast<size_t>(i) * recw;
+        const double *t = tri + static_cast<size_t>(i) * recw;
         for (int q = lane; q < recw; q += 32) rec[static_cast<size_t>(slot) * recw + q] = t[q];
-        if (lane == 0) T.meta[slot].x = 4u;      // accepted (read back by rp_sweep_trace only)
+        if (lane == 0) {
+            T.meta[slot].x = 4u;      // accepted (read back by rp_sweep_trace only)
+            cull[slot] = trialPt[i];  // the cull point the later colours stage
+        }
         // Shape::translate (Shape.cpp:9-12): position += bc.getCorrection(position)
         V3 p = ld3(t);
         if (translated) {

@@ -469,17 +469,26 @@ def main():
     value = total_attempted / (ms * 1e-3)
 
     # ---- end to end through the C ABI with host buffers (pinned): upload + cycle + download every step ----
+    # sharded: every rank moves its own slice of the packing over PCIe (rp_upload_slice all-gathers over NVLink,
+    # rp_download_range reads the slice back); replicas / 1 GPU: the whole packing of the rank
     b_now, s_now = dev.download()
-    host = torch.empty((n, 12), dtype=torch.float64).pin_memory().numpy()
-    host[:] = s_now
+    first, count = rp.Device.slice_of(n, world, rank) if sharded else (0, n)
+    host = torch.empty((count, 12), dtype=torch.float64).pin_memory().numpy()
+    host[:] = s_now[first:first + count]
     e2e_box = b_now
     e2e_steps = max(3, min(args.steps, 10))
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        dev.upload(e2e_box, host)
-        sim.run(1)
-        e2e_box, _ = dev.download(out=host)
+        if sharded:
+            dev.upload_slice(e2e_box, host, first, n)
+            sim.run(1)
+            e2e_box = np.array(list(sim.stats().box)).reshape(3, 3)
+            dev.download_range(first, count, out=host)
+        else:
+            dev.upload(e2e_box, host)
+            sim.run(1)
+            e2e_box, _ = dev.download(out=host)
     barrier()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
     e2e_value = (float(n * e2e_steps) if sharded else sum_over_ranks(float(n * e2e_steps))) / (e2e_ms * 1e-3)
@@ -545,6 +554,26 @@ def main():
     sim.close()
     dev.close()
 
+    # ---- N > 1, sharded: the other way north_star uses several GPUs — independent pressure points of a scan, one
+    # packing per GPU, no data-path collective — measured in the same run and reported as an extra key ----
+    replicas = None
+    if sharded:
+        rdev, rsim, rsteps = thermalised_state(args.workload, args.therm, local, SEED + rank, PRESSURE + 0.1 * rank,
+                                               stream.cuda_stream, None)
+        rsim.run(args.warmup)
+        barrier()
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            rsim.run(args.steps)
+            e1.record(stream)
+        barrier()
+        rms = max_over_ranks(e0.elapsed_time(e1))
+        replicas = {"value": sum_over_ranks(float(n * args.steps)) / (rms * 1e-3), "unit": UNIT, "scaling": "weak",
+                    "ms_per_step": rms / args.steps,
+                    "what": f"{world} independent {args.workload} packings (p = 1.2 + 0.1 rank), one per GPU"}
+        rsim.close()
+        rdev.close()
+
     # ---- the other BASELINE configurations (C1 - C4), N = 1 only: extra keys of the same line ----
     configs = None
     if rank == 0 and world == 1 and args.configs != "none":
@@ -572,8 +601,12 @@ def main():
                            "l2_policy": f"state {n * 96 / 1e6:.0f} MB + sorted records {n * 80 / 1e6:.0f} MB per "
                                         "step; every step rebuilds the sweep grid from all particles "
                                         "(inputs not flushed: working set is re-read each step by design)"},
-                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(n * 96 + 72),
-                        "d2h_bytes_per_step": int(n * 96 + 72), "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps},
+                "e2e": {"value": e2e_value, "unit": UNIT,
+                        "h2d_bytes_per_step": int(n * 96 + 72 * world) if sharded else int((n * 96 + 72) * world),
+                        "d2h_bytes_per_step": int(n * 96 + 72 * world) if sharded else int((n * 96 + 72) * world),
+                        "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
+                        "note": ("every rank moves its slice of the one packing; all-gather over NVLink" if sharded
+                                 else "whole packing of every rank")},
                 "gpu_launches": int(launches),
                 "clocks": clocks,
                 "roofline": roofline,
@@ -587,6 +620,7 @@ def main():
                 "comm_bytes_last_sweep": comm_stats,
                 "breakdown_ms_per_step": {"sweep_kernels": sweep_ms / args.steps, "sweep_grid": grid_ms / args.steps,
                                           "box_move": scaling_ms / args.steps},
+                "replicas": replicas,
                 "configs": configs}
         print(json.dumps(line))
     if world > 1:

@@ -194,6 +194,12 @@ const char *rp_version(void);
 rp_status rp_set_interaction(rp_handle *h, const rp_interaction_desc *desc);
 rp_status rp_upload(rp_handle *h, const double box[9], const double *shapes /* N x 12 */, uint64_t n);
 rp_status rp_download(rp_handle *h, double box_out[9], double *shapes_out /* N x 12 */, uint64_t n);
+/* Sharded upload (after rp_comm_init): every rank passes its slice [n * rank / n_ranks, n * (rank + 1) / n_ranks) of
+ * ONE packing of n particles; the slices travel host -> device once (1 / n_ranks of the bytes per rank) and are
+ * all-gathered over NVLink (NCCL).  Collective: every rank of the communicator must call it.  Without a communicator
+ * the slice is the whole packing.  The matching read-back of a slice is rp_download_range. */
+rp_status rp_upload_slice(rp_handle *h, const double box[9], const double *shapes /* count x 12 */, uint64_t first,
+                          uint64_t count, uint64_t n);
 rp_status rp_size(const rp_handle *h, uint64_t *n_out);
 /* shapes [first, first + count) only — Packing::operator[] / front / back after a few explicit moves (Packing.h:193-215) */
 rp_status rp_download_range(rp_handle *h, uint64_t first, uint64_t count, double *shapes_out /* count x 12 */);

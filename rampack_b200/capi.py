@@ -122,7 +122,7 @@ SYMBOLS = ["rp_create", "rp_destroy", "rp_last_error", "rp_version", "rp_set_int
            "rp_renormalize_orientations", "rp_toggle_walls", "rp_nematic_order", "rp_smectic_order",
            "rp_pair_density_correlation", "rp_sim_create", "rp_sim_destroy", "rp_sim_run", "rp_sim_stats_get", "rp_sim_propose_box",
            "rp_download_range", "rp_count_wall_overlaps", "rp_particle_energy_fluctuations", "rp_snapshot_async",
-           "rp_snapshot_wait", "rp_snapshot_done"]
+           "rp_snapshot_wait", "rp_snapshot_done", "rp_upload_slice"]
 
 _lib = None
 
@@ -165,6 +165,7 @@ def load():
     lib.rp_size.argtypes = [H, C.POINTER(C.c_uint64)]
     lib.rp_download_range.argtypes = [H, C.c_uint64, C.c_uint64, dp]
     lib.rp_snapshot_async.argtypes = [H, dp, dp, C.c_uint64]
+    lib.rp_upload_slice.argtypes = [H, dp, dp, C.c_uint64, C.c_uint64, C.c_uint64]
     lib.rp_snapshot_wait.argtypes = [H]
     lib.rp_snapshot_done.argtypes = [H, C.POINTER(C.c_int32)]
     lib.rp_count_wall_overlaps.argtypes = [H, C.c_int, C.POINTER(C.c_uint64)]
@@ -284,14 +285,27 @@ class Device:
         self._check(self.lib.rp_upload(self.h, dptr(box), dptr(shapes), shapes.shape[0]))
         self.n = shapes.shape[0]
 
+    @staticmethod
+    def slice_of(n, n_ranks, rank):
+        """(first, count) of a rank's slice in the standard partition rp_upload_slice expects."""
+        a, b = n * rank // n_ranks, n * (rank + 1) // n_ranks
+        return a, b - a
+
+    def upload_slice(self, box, shapes_slice, first, n):
+        """Collective sharded upload: this rank's rows [first, first + len(shapes_slice)) of the n-particle packing."""
+        box = np.ascontiguousarray(box, dtype=np.float64).reshape(9)
+        shapes_slice = np.ascontiguousarray(shapes_slice, dtype=np.float64).reshape(-1, 12)
+        self._check(self.lib.rp_upload_slice(self.h, dptr(box), dptr(shapes_slice), first, shapes_slice.shape[0], n))
+        self.n = n
+
     def download(self, out=None):
         box = np.empty(9)
         shapes = out if out is not None else np.empty((self.n, 12))
         self._check(self.lib.rp_download(self.h, dptr(box), dptr(shapes), self.n))
         return box.reshape(3, 3), shapes
 
-    def download_range(self, first, count):
-        out = np.empty((count, 12), dtype=np.float64)
+    def download_range(self, first, count, out=None):
+        out = np.empty((count, 12), dtype=np.float64) if out is None else out
         self._check(self.lib.rp_download_range(self.h, first, count, out.ctypes.data_as(C.POINTER(C.c_double))))
         return out
 

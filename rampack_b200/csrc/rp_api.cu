@@ -373,6 +373,60 @@ rp_status rp_upload(rp_handle *h, const double box[9], const double *shapes, uin
     RP_API_END(h)
 }
 
+rp_status rp_upload_slice(rp_handle *h, const double box[9], const double *shapes, uint64_t first, uint64_t count,
+                          uint64_t n) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(box != nullptr, "box must not be NULL");
+    RP_EXPECT(n > 0 && n < (1ull << 27), "0 < n < 2^27");
+    const int P = shardActive(h) ? h->shard->nranks : 1, r = shardActive(h) ? h->shard->rank : 0;
+    unsigned long long wantFirst = 0, wantCount = n;
+    if (P > 1) shardSlice(n, P, r, &wantFirst, &wantCount);
+    RP_EXPECT(first == wantFirst && count == wantCount,
+              "slice must be [n * rank / n_ranks, n * (rank + 1) / n_ranks) of the packing");
+    RP_EXPECT(shapes != nullptr || count == 0, "shapes must not be NULL");
+    Box b = makeBox(box);
+    RP_EXPECT(boxVolume(b) != 0, "newBox.getVolume() != 0");
+    if (n > h->cap || !h->pos) {
+        if (h->pos) cudaFree(h->pos);
+        if (h->orient) cudaFree(h->orient);
+        h->pos = h->orient = nullptr;
+        size_t cap = n + 16;
+        RP_CUDA(cudaMalloc(&h->pos, 3 * cap * sizeof(double)));
+        RP_CUDA(cudaMalloc(&h->orient, 9 * cap * sizeof(double)));
+        h->cap = cap;
+        h->n = 0;
+    }
+    RP_CUDA(cudaMemsetAsync(h->dFlags, 0, sizeof(int), h->stream));
+    if (count > 0) {
+        ensureStage(h, count * 12 * sizeof(double));
+        RP_CUDA(cudaMemcpyAsync(h->dStage, shapes, count * 12 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        k_check_within_box<<<static_cast<int>((count + 255) / 256), 256, 0, h->stream>>>(
+            static_cast<int>(count), b, static_cast<const double *>(h->dStage), h->dFlags);
+        int total = static_cast<int>(count * 12);
+        k_unpack_shapes<<<(total + 255) / 256, 256, 0, h->stream>>>(static_cast<int>(count), h->cap,
+                                                                    static_cast<const double *>(h->dStage),
+                                                                    h->pos + first, h->orient + first, h->dFlags);
+        h->launches += 2;
+    }
+    if (P > 1) {
+        shardAllReduceMaxInt(h, h->dFlags);       // a shape outside the box on any rank fails the call on every rank
+        shardAllGatherState(h, n);
+    }
+    int outside = 0;
+    RP_CUDA(cudaMemcpyAsync(&outside, h->dFlags, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    RP_CUDA(cudaStreamSynchronize(h->stream));
+    RP_CUDA(cudaGetLastError());
+    RP_EXPECT(!outside, "areShapesWithinBox(shapes, box)");
+    h->n = n;
+    h->box = b;
+    h->gridDirty = true;
+    h->hasTrial = false;
+    h->hasLastScaling = false;
+    h->sweepCapOld = h->sweepCapOwn = 0;
+    if (h->hasInteraction) setupForInteraction(h);
+    RP_API_END(h)
+}
+
 rp_status rp_download(rp_handle *h, double box_out[9], double *shapes_out, uint64_t n) {
     RP_API_BEGIN(h)
     RP_EXPECT(n == h->n, "n == size()");

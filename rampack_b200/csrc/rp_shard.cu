@@ -475,6 +475,33 @@ void shardSignalWait(Handle *h, ShardFlag kind, unsigned int value, bool all, bo
     }
 }
 
+// slice of rank q in the standard partition of n particles over P ranks
+void shardSlice(unsigned long long n, int P, int q, unsigned long long *first, unsigned long long *count) {
+    const unsigned long long a = n * static_cast<unsigned long long>(q) / P, b = n * static_cast<unsigned long long>(q + 1) / P;
+    *first = a;
+    *count = b - a;
+}
+
+// every rank holds its own slice of the canonical SoA arrays: broadcast the 12 rows of every slice from its owner
+void shardAllGatherState(Handle *h, unsigned long long n) {
+    Shard *s = h->shard;
+    RP_NCCL(nccl.GroupStart());
+    for (int q = 0; q < s->nranks; q++) {
+        unsigned long long first, count;
+        shardSlice(n, s->nranks, q, &first, &count);
+        if (count == 0) continue;
+        for (int row = 0; row < 12; row++) {
+            double *base = row < 3 ? h->pos + row * h->cap : h->orient + (row - 3) * h->cap;
+            RP_NCCL(nccl.Broadcast(base + first, base + first, count, ncclDouble, q, commOf(h), h->stream));
+        }
+    }
+    RP_NCCL(nccl.GroupEnd());
+}
+
+void shardAllReduceMaxInt(Handle *h, int *dValue) {
+    RP_NCCL(nccl.AllReduce(dValue, dValue, 1, ncclInt32, ncclMax, commOf(h), h->stream));
+}
+
 void shardAllReduceU64(Handle *h, unsigned long long *dValues, int count) {
     RP_NCCL(nccl.AllReduce(dValues, dValues, count, ncclUint64, ncclSum, commOf(h), h->stream));
 }

@@ -70,6 +70,10 @@ void shardQueueLayerStarts(Handle *h, int nx, int ny, int nz, bool toHost);
 void shardHaloExchange(Handle *h, int colour, int nx, int ny, int nz, bool translated, bool rotated);
 void shardGatherCycle(Handle *h, int nz, bool translated, bool rotated);
 void shardAllReduceU64(Handle *h, unsigned long long *dValues, int count);
+// sharded upload: standard partition of n particles over the ranks, all-gather of the canonical arrays over NCCL
+void shardSlice(unsigned long long n, int nranks, int rank, unsigned long long *first, unsigned long long *count);
+void shardAllGatherState(Handle *h, unsigned long long n);
+void shardAllReduceMaxInt(Handle *h, int *dValue);
 
 // peer-memory path
 constexpr int SHARD_MAX_PEERS = 7;

@@ -104,7 +104,7 @@ void cullThresholds(const Handle *h, const double relCell[3], float *thr2, float
 // The default is picked from the number of active cells (one wave or less: more threads per cell so that a launch
 // does not cost a full 4-warp CTA lifetime); RP_SWEEP_THREADS / RP_SWEEP_MINB override it (measurement hook).
 struct SweepVariant { int threads, minb, index; };
-static const SweepVariant SWEEP_VARIANTS[] = {{128, 4, 0}, {128, 5, 1}, {128, 6, 2}, {64, 8, 3}, {64, 10, 4},
+static const SweepVariant SWEEP_VARIANTS[] = {{128, 4, 0}, {128, 5, 1}, {128, 6, 2}, {512, 1, 3}, {512, 2, 4},
                                               {256, 2, 5}, {256, 3, 6}};
 
 static SweepVariant chooseVariant(int activeCells) {
@@ -151,8 +151,8 @@ static void launchColourVariant(Handle *h, const SweepVariant &v, int blocks, si
         case 0: launchColour<HARD, 128, 4>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
         case 1: launchColour<HARD, 128, 5>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
         case 2: launchColour<HARD, 128, 6>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
-        case 3: launchColour<HARD, 64, 8>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
-        case 4: launchColour<HARD, 64, 10>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
+        case 3: launchColour<HARD, 512, 1>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
+        case 4: launchColour<HARD, 512, 2>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
         case 5: launchColour<HARD, 256, 2>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
         default: launchColour<HARD, 256, 3>(h, v.index, blocks, smem, A, sg, off, T, dCounters, peers); break;
     }
@@ -621,12 +621,20 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
     RP_CUDA(cudaStreamSynchronize(st));
     RP_CUDA(cudaGetLastError());
     g.maxPopulation = flags[1];
-    A.capOwn = std::max(g.maxPopulation, 1);
+    A.capOwn = (std::max(g.maxPopulation, 1) + 1) & ~1;
     A.capOld = std::max(flags[2], 1);
-    A.matrices = (h->overlapCounting && I.hard != RP_HARD_NONE) || I.soft != RP_SOFT_NONE || A.capOwn > GEN_MAXOWN;
-    if (A.capOwn > 2 * GEN_MAXOWN)
-        throw rp_error(RP_ERR_CAPACITY, "rp_sweep: more than 128 particles in one cell of the sweep grid");
-    const size_t smem = genSmemBytes(A.capOld, A.capOwn, static_cast<int>(recw), A.matrices != 0);
+    if (A.capOwn > GEN_MAXCELL)
+        throw rp_error(RP_ERR_CAPACITY, "rp_sweep: more than 512 particles in one cell of the sweep grid");
+    // in-cell pair terms: bit masks (hard only), matrices while they fit, else evaluated step by step by the whole CTA
+    const bool needTables = (h->overlapCounting && I.hard != RP_HARD_NONE) || I.soft != RP_SOFT_NONE
+                            || A.capOwn > GEN_MAXOWN;
+    A.matrices = 0;
+    size_t smem = genSmemBytes(A.capOld, A.capOwn, static_cast<int>(recw), false);
+    if (needTables) {
+        const size_t withMatrices = genSmemBytes(A.capOld, A.capOwn, static_cast<int>(recw), true);
+        if (A.capOwn <= 2 * GEN_MAXOWN && withMatrices <= 110 * 1024) { A.matrices = 1; smem = withMatrices; }
+        else A.matrices = 2;
+    }
     if (smem > 200 * 1024)
         throw rp_error(RP_ERR_CAPACITY, "rp_sweep: a cell does not fit into shared memory");
     RP_CUDA(cudaEventRecord(ev[2], st));

@@ -317,13 +317,15 @@ __device__ __forceinline__ void pairTerms(const Inter &I, const GenArgs &A, cons
 
 constexpr int GEN_THREADS = 128;
 constexpr int GEN_MAXOWN = 64;       // trials per cell the bit masks of the hard-only resolution cover
+constexpr int GEN_MAXCELL = 512;     // particles per sweep cell the kernel supports at all
 
 // shared memory of k_gen_sweep beyond its static part, for (capOld frozen candidates, capOwn particles in the cell)
 __host__ __device__ inline size_t genSmemBytes(int capOld, int capOwn, int recw, bool matrices) {
+    capOwn = (capOwn + 1) & ~1;                                             // (keeps the double arrays 8-byte aligned)
     size_t b = 16 * static_cast<size_t>(capOld + 2 * capOwn);               // FP32 cull points: candidates, trial + current states
     b += 2 * static_cast<size_t>(capOwn) * recw * 8;                        // cur, tri
     b += 3 * static_cast<size_t>(capOwn) * 8;                               // eOld, eNew, uMet
-    b += 2 * static_cast<size_t>(capOwn) * 4;                               // ovOld, ovNew
+    b += 5 * static_cast<size_t>(capOwn) * 4;                               // ovOld, ovNew, rejected, seq, orderKey
     b += (GEN_THREADS / 32) * 64 * 4;                                       // per-warp survivor queues
     if (matrices) b += 4 * static_cast<size_t>(capOwn) * capOwn * (8 + 2);  // in-cell pair matrices
     return b + 64;
@@ -361,8 +363,10 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
     __shared__ long long sOverlapDelta;
     __shared__ unsigned long long sBar;
     __shared__ unsigned long long ownMask[GEN_MAXOWN], newMask[GEN_MAXOWN];
-    __shared__ int rejected[GEN_MAXOWN * 2], seq[GEN_MAXOWN * 2];
-    __shared__ unsigned int orderKey[GEN_MAXOWN * 2];
+    __shared__ unsigned long long sMoved[GEN_MAXCELL / 64];      // accepted trials of the cell, one bit each
+    __shared__ double sRedE[2 * (GEN_THREADS / 32)];
+    __shared__ int sRedO[2 * (GEN_THREADS / 32)];
+    __shared__ int sAccept;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const GenLayout &L = A.L;
@@ -372,7 +376,10 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
 
     const bool counting = A.counting != 0 && hard;
     const bool needOld = counting || soft;
-    const bool matrices = A.matrices != 0;      // counting, soft, or a cell too crowded for the 64-bit masks
+    // in-cell pair terms: 0 = bit masks (hard only, <= 64 particles per cell), 1 = matrices (counting / soft), 2 = no
+    // tables: the sequential pass evaluates them against the current states with the whole CTA (cells too crowded for
+    // the matrices, e.g. the wide cells of the un-truncated Lennard-Jones potential)
+    const bool matrices = A.matrices == 1, blockwise = A.matrices == 2;
 
     const int b = blockIdx.x;
     const int a0 = b % A.nActive[0], a1 = (b / A.nActive[0]) % A.nActive[1], a2 = b / (A.nActive[0] * A.nActive[1]);
@@ -392,7 +399,10 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
     double *uMet = eNew + A.capOwn;
     int *ovOld = reinterpret_cast<int *>(uMet + A.capOwn);
     int *ovNew = ovOld + A.capOwn;
-    int *queue = ovNew + A.capOwn;
+    int *rejected = ovNew + A.capOwn;
+    int *seq = rejected + A.capOwn;
+    unsigned int *orderKey = reinterpret_cast<unsigned int *>(seq + A.capOwn);
+    int *queue = reinterpret_cast<int *>(orderKey + A.capOwn);
     // in-cell matrices, row i = trial, column j = other particle: [0] new_i/old_j [1] old_i/old_j [2] new_i/new_j
     // [3] old_i/new_j
     double *eMat = reinterpret_cast<double *>(queue + WARPS * 64);
@@ -452,6 +462,7 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
         orderKey[i] = meta.y;
         uMet[i] = T.u[ownStart + i];
         if (i < GEN_MAXOWN) { ownMask[i] = 0ull; newMask[i] = 0ull; }
+        if (i < GEN_MAXCELL / 64) sMoved[i] = 0ull;
     }
     if (warp == 0) mbarWait(&sBar, 0);
     __syncthreads();
@@ -559,13 +570,13 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
     // ---- phase 2a: pair terms inside the cell, every ordered pair (i, j), all threads ----
     {
         const V3 zero = v3(0, 0, 0);
-        for (int p = tid; p < numOwn * numOwn; p += GEN_THREADS) {
+        for (int p = tid; p < (blockwise ? 0 : numOwn * numOwn); p += GEN_THREADS) {
             const int i = p / numOwn, j = p - i * numOwn;
             if (i == j || rejected[i] != 0) continue;
             const double *ta = tri + static_cast<size_t>(i) * recw, *oa = cur + static_cast<size_t>(i) * recw;
             const double *ob = cur + static_cast<size_t>(j) * recw, *tb = tri + static_cast<size_t>(j) * recw;
             const bool jMayMove = rejected[j] == 0;
-            if (!matrices) {
+            if (!matrices) {       // bit masks
                 int o1 = 0, o2 = 0;
                 double e = 0;
                 pairTerms<HARD, SOFT>(I, A, ta, ob, zero, 0, 0, 0, true, false, true, &o1, &e);
@@ -596,7 +607,73 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
 
     // ---- phase 2b: sequential pass through the cell in its random order ----
     const double INF = __longlong_as_double(0x7ff0000000000000ll);
-    if (warp == 0) {
+    if (blockwise) {
+        // every step: all threads evaluate the pair terms of trial i against the CURRENT states of the other particles
+        // of the cell (an accepted trial replaces its current state at once), fixed-order reduction, one decision
+        int nAcc = 0, nRejDomain = 0, nRejOverlap = 0, nRejEnergy = 0, nIdle = 0;
+        long long overlapDelta = 0;
+        const V3 zero = v3(0, 0, 0);
+        for (int step = 0; step < numOwn; step++) {
+            const int i = seq[step];
+            const int state = rejected[i];
+            if (state == 2) { nRejDomain++; continue; }
+            if (state == 5) { nIdle++; continue; }
+            const double *ta = tri + static_cast<size_t>(i) * recw, *oa = cur + static_cast<size_t>(i) * recw;
+            int oO = 0, oN = 0;
+            double enO = 0, enN = 0;
+            if (state == 0) {
+                for (int j = tid; j < numOwn; j += GEN_THREADS) {
+                    if (j == i) continue;
+                    const double *rb = cur + static_cast<size_t>(j) * recw;
+                    pairTerms<HARD, SOFT>(I, A, ta, rb, zero, 0, 0, 0, hard, soft, !counting, &oN, &enN);
+                    if (needOld) pairTerms<HARD, SOFT>(I, A, oa, rb, zero, 0, 0, 0, counting, soft, false, &oO, &enO);
+                }
+            }
+            #pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                oO += __shfl_xor_sync(0xffffffffu, oO, o);
+                oN += __shfl_xor_sync(0xffffffffu, oN, o);
+                enO += __shfl_xor_sync(0xffffffffu, enO, o);
+                enN += __shfl_xor_sync(0xffffffffu, enN, o);
+            }
+            if (lane == 0) { sRedO[2 * warp] = oO; sRedO[2 * warp + 1] = oN; sRedE[2 * warp] = enO; sRedE[2 * warp + 1] = enN; }
+            __syncthreads();
+            if (tid == 0) {
+                oO = ovOld[i]; oN = ovNew[i]; enO = 0; enN = 0;
+                for (int w = 0; w < WARPS; w++) {
+                    oO += sRedO[2 * w]; oN += sRedO[2 * w + 1]; enO += sRedE[2 * w]; enN += sRedE[2 * w + 1];
+                }
+                double dE;
+                long long delta = 0;
+                if (counting) {
+                    delta = static_cast<long long>(oN) - static_cast<long long>(oO);
+                    dE = delta < 0 ? -INF : (delta > 0 ? INF : 0.0);
+                } else {
+                    dE = (hard && (oN > 0 || state == 1)) ? INF : 0.0;
+                }
+                const bool overlapVerdict = dE != 0;
+                if (!overlapVerdict && soft) dE = (eNew[i] + enN) - (eOld[i] + enO);
+                const bool accept = uMet[i] <= exp(-dE / A.temperature);
+                T.dE[ownStart + i] = dE;
+                sAccept = accept ? 1 : 0;
+                if (accept) {
+                    nAcc++;
+                    overlapDelta += delta;
+                    sMoved[i >> 6] |= 1ull << (i & 63);
+                } else if (overlapVerdict) nRejOverlap++;
+                else nRejEnergy++;
+            }
+            __syncthreads();
+            if (sAccept)
+                for (int q = tid; q < recw; q += GEN_THREADS) cur[static_cast<size_t>(i) * recw + q] = ta[q];
+            __syncthreads();
+        }
+        if (tid == 0) {
+            sStats[0] = nAcc; sStats[1] = nRejDomain; sStats[2] = nRejOverlap; sStats[3] = nRejEnergy;
+            sStats[4] = nIdle;
+            sOverlapDelta = overlapDelta;
+        }
+    } else if (warp == 0) {
         int nAcc = 0, nRejDomain = 0, nRejOverlap = 0, nRejEnergy = 0, nIdle = 0;
         long long overlapDelta = 0;
         unsigned long long movedLo = 0ull, movedHi = 0ull;     // particles 0..63 / 64..127 of the cell
@@ -664,20 +741,18 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
             sStats[0] = nAcc; sStats[1] = nRejDomain; sStats[2] = nRejOverlap; sStats[3] = nRejEnergy;
             sStats[4] = nIdle;
             sOverlapDelta = overlapDelta;
-            reinterpret_cast<unsigned long long *>(seq)[0] = movedLo;      // (seq is no longer needed)
-            reinterpret_cast<unsigned long long *>(seq)[1] = movedHi;
+            sMoved[0] = movedLo;
+            sMoved[1] = movedHi;
         }
     }
     __syncthreads();
-    const unsigned long long movedLo = reinterpret_cast<unsigned long long *>(seq)[0],
-                             movedHi = reinterpret_cast<unsigned long long *>(seq)[1];
 
     // ---- write-back of the accepted moves ----
     const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION || A.kind == RP_MOVE_FLIP);
     const bool translated = (A.kind == RP_MOVE_TRANSLATION || A.kind == RP_MOVE_ROTOTRANSLATION
                              || (A.kind == RP_MOVE_FLIP && !A.flipOriginZero));
     for (int i = warp; i < numOwn; i += WARPS) {
-        const bool acc = i < 64 ? ((movedLo >> i) & 1ull) != 0ull : ((movedHi >> (i - 64)) & 1ull) != 0ull;
+        const bool acc = ((sMoved[i >> 6] >> (i & 63)) & 1ull) != 0ull;
         if (!acc) continue;
         const int slot = ownStart + i;
         const int id = items[slot];

@@ -16,9 +16,14 @@ import rampack_b200 as rp
 import helpers as H
 
 
-def run_cycles(dev, box, shapes, cycles, kind):
+def run_cycles(dev, box, shapes, cycles, kind, part=None):
     dev.set_interaction(H.desc_sc())
-    dev.upload(box, shapes)
+    if part is None:
+        dev.upload(box, shapes)
+    else:
+        # sharded upload: this rank sends its slice only, the ranks all-gather over NCCL (rp_upload_slice)
+        first, count = rp.Device.slice_of(shapes.shape[0], part[1], part[0])
+        dev.upload_slice(box, shapes[first:first + count], first, shapes.shape[0])
     log = []
     b = box.copy()
     for cycle in range(cycles):
@@ -50,7 +55,9 @@ def main():
     box, shapes = H.sc_lattice((20, 20, 16))
     dev = rp.Device(device=local, seed=777)
     dev.comm_init(bytes(ident.cpu().numpy().tobytes()), rank, world)
-    log, (b, s) = run_cycles(dev, box, shapes, 4, kind)
+    log, (b, s) = run_cycles(dev, box, shapes, 4, kind, part=(rank, world))
+    first, count = rp.Device.slice_of(shapes.shape[0], world, rank)
+    assert np.array_equal(dev.download_range(first, count), s[first:first + count])
     stats = dev.comm_stats()
     np.save(os.path.join(out_dir, f"state_{rank}.npy"), s)
     np.save(os.path.join(out_dir, f"box_{rank}.npy"), b)

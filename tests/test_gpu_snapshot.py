@@ -60,6 +60,8 @@ def test_snapshot_every_100_cycles_costs_under_one_per_cent():
     sim = NativeSimulation(dev, [(rp.RP_MOVE_ROTOTRANSLATION, 0.05, 0.05)], 1.0, 1.2, None, seed=5)
     sim.run(50)
     out = _pinned(dev.n)
+    dev.snapshot_async(out)           # (first call: allocates the device-side copy, creates the second stream)
+    dev.snapshot_wait()
     e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
 
     def blocks(snap):

@@ -259,6 +259,20 @@ typedef struct rp_trial_trace {
 } rp_trial_trace;
 rp_status rp_sweep_trace(rp_handle *h, rp_trial_trace *out, uint64_t n);
 
+/* ---- lattice population on the device: Lattice(UnitCell(cell_box, molecules), n_cells) populated
+ * by SerialPopulator(axis_order) with n_shapes shapes (core/lattice/Lattice.cpp:43-81, SerialPopulator.cpp:9-40).
+ * cell_molecules: m x 12 doubles (RELATIVE position inside the cell, orientation); axis_order: a permutation of
+ * {0, 1, 2}, outermost loop first ("xyz" = {0, 1, 2}).  The packing's box becomes Lattice::getLatticeBox(); positions
+ * equal the reference's bit for bit.  Replaces the host loop + rp_upload for large N (nothing crosses PCIe but the
+ * unit cell). ---- */
+rp_status rp_populate_lattice(rp_handle *h, const double cell_box[9], const double *cell_molecules, uint64_t m,
+                              const uint32_t n_cells[3], const int axis_order[3], uint64_t n_shapes);
+/* RotationRandomizingTransformer (core/lattice/RotationRandomizingTransformer.cpp:21-56) applied to the packing:
+ * mode 0 = uniformly random rotations (Tait-Bryan angles), 1 = about the fixed `axis` by U(0, 2 pi), 2 = about the
+ * particle's own axis orientation * `axis`.  Per-particle Philox streams keyed by (seed, particle) replace the
+ * reference's sequential std::mt19937: same distribution, different variates. */
+rp_status rp_randomize_rotations(rp_handle *h, uint64_t seed, int mode, const double axis[3]);
+
 /* ---- Packing::renormalizeOrientations / fixRotationMatrix (Packing.cpp:1178-1219), called by
  * Simulation::fixRotationMatrices every `rotation_matrix_fix_every` cycles.  allow_overlaps != 0 is the counting-mode
  * variant.  rejected_out: fixes not applied because they would create an overlap (per particle: every particle that

@@ -42,6 +42,12 @@
 #include "core/volume_scalers/TriclinicDeltaScaler.h"
 #include "core/volume_scalers/TriclinicAdapter.h"
 #include "core/volume_scalers/DeltaVolumeScaler.h"
+#include "core/volume_scalers/AnisotropicVolumeScaler.h"
+#include "core/volume_scalers/LinearScalingFactorSampler.h"
+#include "core/volume_scalers/LogScalingFactorSampler.h"
+#include "core/lattice/UnitCell.h"
+#include "core/lattice/Lattice.h"
+#include "core/lattice/SerialPopulator.h"
 #include "utils/Logger.h"
 #include "utils/OMPMacros.h"
 
@@ -572,5 +578,70 @@ int rpr_run_simulation(void *tp, const double box[9], const double *shapes, std:
 }
 
 int rpr_omp_max_threads() { return OMP_MAXTHREADS; }
+
+// `count` successive box proposals of one of the reference's scaler classes from a fresh std::mt19937(seed), every one
+// from the same oldBox (core/volume_scalers/*.cpp, TriclinicBoxScaler::updateBox).
+// kind: 1 delta_v, 2 linear, 3 log (AnisotropicVolumeScaler over the direction groups, bit masks 1 = x, 2 = y, 4 = z),
+// 4 delta_triclinic(step, scaleTogether = !independent)
+int rpr_propose_boxes(int kind, double step, int independent, const int *groups, int nGroups, std::uint64_t seed,
+                      const double oldBox[9], int count, double *out, char *err, std::size_t errLen)
+{
+    try {
+        std::unique_ptr<TriclinicBoxScaler> scaler;
+        if (kind == 1) {
+            scaler = std::make_unique<TriclinicAdapter>(std::make_unique<DeltaVolumeScaler>(), step);
+        } else if (kind == 2 || kind == 3) {
+            AnisotropicVolumeScaler::ScalingDirection dir;
+            for (int g = 0; g < nGroups; g++) {
+                AnisotropicVolumeScaler::ScalingDirection one;
+                if (groups[g] & 1) one &= AnisotropicVolumeScaler::X;
+                if (groups[g] & 2) one &= AnisotropicVolumeScaler::Y;
+                if (groups[g] & 4) one &= AnisotropicVolumeScaler::Z;
+                dir |= one;
+            }
+            std::unique_ptr<ScalingFactorSampler> sampler;
+            if (kind == 2) sampler = std::make_unique<LinearScalingFactorSampler>();
+            else sampler = std::make_unique<LogScalingFactorSampler>();
+            scaler = std::make_unique<TriclinicAdapter>(
+                std::make_unique<AnisotropicVolumeScaler>(std::move(sampler), dir, independent != 0), step);
+        } else if (kind == 4) {
+            scaler = std::make_unique<TriclinicDeltaScaler>(step, independent == 0);
+        } else {
+            throw std::runtime_error("unknown scaler kind");
+        }
+        std::mt19937 mt(seed);
+        TriclinicBox box(mat(oldBox));
+        for (int k = 0; k < count; k++) {
+            TriclinicBox nb = scaler->updateBox(box, mt);
+            const auto &dim = nb.getDimensions();
+            for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) out[9*k + 3*r + c] = dim(r, c);
+        }
+    } catch (const std::exception &e) {
+        if (err && errLen > 0) { std::strncpy(err, e.what(), errLen - 1); err[errLen - 1] = 0; }
+        return 1;
+    }
+    return 0;
+}
+
+// Lattice(UnitCell(cellBox, molecules), dims) populated by SerialPopulator(axisOrder) with n shapes
+// (core/lattice/Lattice.cpp:43-81, SerialPopulator.cpp:9-40); molecules: m x 12 (relative position, orientation)
+int rpr_populate_lattice(const double cellBox[9], const double *molecules, std::uint64_t m, const int dims[3],
+                         const char *axisOrder, std::uint64_t n, double boxOut[9], double *shapesOut, char *err,
+                         std::size_t errLen)
+{
+    try {
+        UnitCell cell(TriclinicBox(mat(cellBox)), toShapes(molecules, m));
+        Lattice lattice(cell, {std::size_t(dims[0]), std::size_t(dims[1]), std::size_t(dims[2])});
+        SerialPopulator populator{std::string(axisOrder)};
+        auto shapes = populator.populateLattice(lattice, n);
+        const auto &dim = lattice.getLatticeBox().getDimensions();
+        for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) boxOut[3*r + c] = dim(r, c);
+        for (std::size_t i = 0; i < shapes.size(); i++) fromShape(shapes[i], shapesOut + 12*i);
+    } catch (const std::exception &e) {
+        if (err && errLen > 0) { std::strncpy(err, e.what(), errLen - 1); err[errLen - 1] = 0; }
+        return 1;
+    }
+    return 0;
+}
 
 }

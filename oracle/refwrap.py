@@ -323,6 +323,42 @@ def ref_run_simulation(traits, box, shapes, seed, temperature, pressure, trans_s
     return res, box_out.reshape(3, 3), shapes_out
 
 
+def ref_propose_boxes(kind, step, independent, groups, seed, old_box, count, native=False):
+    """`count` proposals of the reference's box scaler classes from std::mt19937(seed), each from old_box.
+    kind: "delta_v" | "linear" | "log" | "delta_triclinic"; groups: axis bit masks (linear / log)."""
+    lib = load_ref(native)
+    code = {"delta_v": 1, "linear": 2, "log": 3, "delta_triclinic": 4}[kind]
+    g = (C.c_int * max(1, len(groups)))(*groups) if groups else (C.c_int * 1)(7)
+    old_box = np.ascontiguousarray(old_box, dtype=np.float64).reshape(9)
+    out = np.empty((count, 9))
+    err = C.create_string_buffer(1024)
+    lib.rpr_propose_boxes.argtypes = [C.c_int, C.c_double, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_uint64,
+                                      C.POINTER(C.c_double), C.c_int, C.POINTER(C.c_double), C.c_char_p, C.c_size_t]
+    st = lib.rpr_propose_boxes(code, step, int(independent), g, len(groups) if groups else 0, seed, _dp(old_box),
+                               count, _dp(out), err, 1024)
+    if st != 0:
+        raise RuntimeError("reference scaler failed: " + err.value.decode())
+    return out.reshape(count, 3, 3)
+
+
+def ref_populate_lattice(cell_box, molecules, dims, axis_order, n, native=False):
+    """Lattice + SerialPopulator of the reference: (lattice box, n x 12 shapes)."""
+    lib = load_ref(native)
+    cell_box = np.ascontiguousarray(cell_box, dtype=np.float64).reshape(9)
+    molecules = np.ascontiguousarray(molecules, dtype=np.float64).reshape(-1, 12)
+    box, shapes = np.empty(9), np.empty((n, 12))
+    d = (C.c_int * 3)(*[int(x) for x in dims])
+    err = C.create_string_buffer(1024)
+    lib.rpr_populate_lattice.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_uint64,
+                                         C.POINTER(C.c_int), C.c_char_p, C.c_uint64, C.POINTER(C.c_double),
+                                         C.POINTER(C.c_double), C.c_char_p, C.c_size_t]
+    st = lib.rpr_populate_lattice(_dp(cell_box), _dp(molecules), molecules.shape[0], d, axis_order.encode(), n,
+                                  _dp(box), _dp(shapes), err, 1024)
+    if st != 0:
+        raise RuntimeError("reference lattice failed: " + err.value.decode())
+    return box.reshape(3, 3), shapes
+
+
 # ---------------------------------------------------------------------------------------------------------------------
 # the plain-C restatement (oracle/rp_oracle.c -> liboracle_port.so): same Python surface as RefTraits / RefPacking
 # ---------------------------------------------------------------------------------------------------------------------

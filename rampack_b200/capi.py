@@ -113,7 +113,7 @@ TRACE_DTYPE = np.dtype([("particle", "<u8"), ("colour_step", "<i4"), ("cell", "<
 assert TRACE_DTYPE.itemsize == 8 + 6 * 4 + 8 * 17
 
 # every symbol include/rampack_b200.h declares (tests/test_abi.py checks the exports against the header)
-SYMBOLS = ["rp_create", "rp_destroy", "rp_last_error", "rp_version", "rp_set_interaction", "rp_upload",
+SYMBOLS = ["rp_populate_lattice", "rp_randomize_rotations", "rp_create", "rp_destroy", "rp_last_error", "rp_version", "rp_set_interaction", "rp_upload",
            "rp_download", "rp_size", "rp_rebuild_grid", "rp_grid_info_get", "rp_cell_numbers",
            "rp_count_total_overlaps", "rp_total_energy", "rp_try_move", "rp_accept_move", "rp_try_scaling",
            "rp_revert_scaling", "rp_sweep", "rp_sweep_trace", "rp_toggle_overlap_counting", "rp_cached_overlaps",
@@ -161,6 +161,8 @@ def load():
     lib.rp_sim_propose_box.argtypes = [H, dp, dp]
     lib.rp_set_interaction.argtypes = [H, C.POINTER(InteractionDesc)]
     lib.rp_upload.argtypes = [H, dp, dp, C.c_uint64]
+    lib.rp_populate_lattice.argtypes = [H, dp, dp, C.c_uint64, C.POINTER(C.c_uint32), C.POINTER(C.c_int), C.c_uint64]
+    lib.rp_randomize_rotations.argtypes = [H, C.c_uint64, C.c_int, dp]
     lib.rp_download.argtypes = [H, dp, dp, C.c_uint64]
     lib.rp_size.argtypes = [H, C.POINTER(C.c_uint64)]
     lib.rp_download_range.argtypes = [H, C.c_uint64, C.c_uint64, dp]
@@ -284,6 +286,24 @@ class Device:
         shapes = np.ascontiguousarray(shapes, dtype=np.float64).reshape(-1, 12)
         self._check(self.lib.rp_upload(self.h, dptr(box), dptr(shapes), shapes.shape[0]))
         self.n = shapes.shape[0]
+
+    def populate_lattice(self, cell_box, cell_molecules, n_cells, axis_order="xyz", n_shapes=None):
+        """Lattice(UnitCell(cell_box, molecules), n_cells) + SerialPopulator(axis_order) on the device
+        (rp_populate_lattice); cell_molecules: m x 12 (relative position in the cell, orientation)."""
+        cell_box = np.ascontiguousarray(cell_box, dtype=np.float64).reshape(9)
+        mol = np.ascontiguousarray(cell_molecules, dtype=np.float64).reshape(-1, 12)
+        dims = (C.c_uint32 * 3)(*[int(x) for x in n_cells])
+        order = (C.c_int * 3)(*["xyz".index(ch) for ch in axis_order])
+        if n_shapes is None:
+            n_shapes = int(n_cells[0]) * int(n_cells[1]) * int(n_cells[2]) * mol.shape[0]
+        self._check(self.lib.rp_populate_lattice(self.h, dptr(cell_box), dptr(mol), mol.shape[0], dims, order,
+                                                 n_shapes))
+        self.n = n_shapes
+
+    def randomize_rotations(self, seed, mode=0, axis=None):
+        """RotationRandomizingTransformer on the device: mode 0 random, 1 about `axis`, 2 about orientation * `axis`."""
+        a = np.ascontiguousarray(axis if axis is not None else (0.0, 0.0, 1.0), dtype=np.float64).reshape(3)
+        self._check(self.lib.rp_randomize_rotations(self.h, seed, mode, dptr(a)))
 
     @staticmethod
     def slice_of(n, n_ranks, rank):

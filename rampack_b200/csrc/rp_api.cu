@@ -1,6 +1,7 @@
 // rp_api.cu — the C ABI of librampack_b200.so (include/rampack_b200.h): handle lifetime, state upload/download and
 // thin forwarding to the kernels.  No exception crosses the boundary: every entry point returns an rp_status.
 #include "rp_internal.cuh"
+#include "rp_philox.cuh"
 #include "rp_shard.cuh"
 #include <limits>
 
@@ -126,6 +127,81 @@ Box makeBox(const double m[9]) {
     for (int i = 0; i < 9; i++) b.m.a[i] = m[i];
     b.inv = inverse(b.m);
     return b;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// lattice population on the device
+// ---------------------------------------------------------------------------------------------------------------
+// SerialPopulator::populateLattice over a regular Lattice (core/lattice/SerialPopulator.cpp:9-40, Lattice.cpp:61-81):
+// shape s = molecule (s % m) of the (s / m)-th cell in the populator's axis order; position =
+// cellBox.relativeToAbsolute({i, j, k} + relative position) — the same two operations in the same order, so the
+// result equals the reference's bit for bit.  flag[0] |= 1 when a shape ends up outside the lattice box.
+struct LatticeArgs {
+    Box cell, lattice;
+    int dims[3], order[3];
+    int m;
+};
+__global__ void k_populate_lattice(int n, size_t cap, LatticeArgs L, const double *__restrict__ molecules,
+                                   double *__restrict__ pos, double *__restrict__ orient, int *__restrict__ flag)
+{
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    int q = s / L.m, j = s - q * L.m;
+    int i[3];
+    i[L.order[2]] = q % L.dims[L.order[2]]; q /= L.dims[L.order[2]];
+    i[L.order[1]] = q % L.dims[L.order[1]]; q /= L.dims[L.order[1]];
+    i[L.order[0]] = q;
+    const double *mol = molecules + 12 * static_cast<size_t>(j);
+    V3 rel = v3(static_cast<double>(i[0]), static_cast<double>(i[1]), static_cast<double>(i[2])) + v3(mol[0], mol[1], mol[2]);
+    V3 p = relToAbs(L.cell, rel);
+    pos[s] = p.x; pos[cap + s] = p.y; pos[2 * cap + s] = p.z;
+    #pragma unroll
+    for (int c = 0; c < 9; c++) orient[c * cap + s] = mol[3 + c];
+    V3 r = absToRel(L.lattice, p);
+    if (r.x < 0 || r.x >= 1 || r.y < 0 || r.y >= 1 || r.z < 0 || r.z >= 1) atomicOr(flag, 1);
+}
+
+// RotationRandomizingTransformer::rotateRandomly (core/lattice/RotationRandomizingTransformer.cpp:30-56) for every
+// particle, from per-particle Philox streams instead of one sequential std::mt19937 (same distributions):
+//   mode 0  uniformly random rotation: Matrix<3,3>::rotation(U(0, 2pi), asin(U(-1, 1)), U(0, 2pi)) (Tait-Bryan angles,
+//           geometry/Matrix.tpp:411-436)
+//   mode 1  rotation about the fixed (normalised) axis by U(0, 2pi) (Matrix.tpp:437-449)
+//   mode 2  rotation about the particle's own axis orientation * bodyAxis (ShapeGeometry::getAxis) by U(0, 2pi)
+// followed by Shape::rotate (core/Shape.cpp:14-16): orientation = rotation * orientation.
+__global__ void k_randomize_rotations(int n, size_t cap, unsigned long long seed, int mode, V3 axis,
+                                      double *__restrict__ orient)
+{
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    Rng rng;
+    rng.init(seed, static_cast<unsigned int>(p), 0x4C415454u, 0u);
+    const double TWO_PI = 2 * 3.14159265358979323846;
+    M33 O;
+    #pragma unroll
+    for (int q = 0; q < 9; q++) O.a[q] = orient[q * cap + p];
+    M33 R;
+    if (mode == 0) {
+        const double ax = rng.uniform(0, TWO_PI), ay = asin(rng.uniform(-1, 1)), az = rng.uniform(0, TWO_PI);
+        const double sx = sin(ax), sy = sin(ay), sz = sin(az), cx = cos(ax), cy = cos(ay), cz = cos(az);
+        R.a[0] = cy * cz; R.a[1] = sx * sy * cz - cx * sz; R.a[2] = cx * sy * cz + sx * sz;
+        R.a[3] = cy * sz; R.a[4] = sx * sy * sz + cx * cz; R.a[5] = cx * sy * sz - sx * cz;
+        R.a[6] = -sy;     R.a[7] = sx * cy;                R.a[8] = cx * cy;
+    } else {
+        V3 a = axis;
+        if (mode == 2) a = mul(O, axis);
+        const double nrm = sqrt(norm2(a));
+        a = v3(a.x / nrm, a.y / nrm, a.z / nrm);
+        const double angle = rng.uniform(0, TWO_PI);
+        const double sina = sin(angle), cosa = cos(angle);
+        M33 K = {{0, -a.z, a.y, a.z, 0, -a.x, -a.y, a.x, 0}};
+        M33 sK;
+        for (int q = 0; q < 9; q++) sK.a[q] = (1 - cosa) * K.a[q];
+        M33 KK = mul(sK, K);
+        for (int q = 0; q < 9; q++) R.a[q] = (((q % 4 == 0) ? 1.0 : 0.0) + K.a[q] * sina) + KK.a[q];
+    }
+    M33 N = mul(R, O);
+    #pragma unroll
+    for (int q = 0; q < 9; q++) orient[q * cap + p] = N.a[q];
 }
 
 // AoS (N x 12, reference Shape layout) <-> SoA with stride cap
@@ -423,6 +499,84 @@ rp_status rp_upload_slice(rp_handle *h, const double box[9], const double *shape
     h->hasTrial = false;
     h->hasLastScaling = false;
     h->sweepCapOld = h->sweepCapOwn = 0;
+    if (h->hasInteraction) setupForInteraction(h);
+    RP_API_END(h)
+}
+
+rp_status rp_populate_lattice(rp_handle *h, const double cell_box[9], const double *cell_molecules, uint64_t m,
+                              const uint32_t n_cells[3], const int axis_order[3], uint64_t n_shapes) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(cell_box && cell_molecules && n_cells && axis_order, "arguments must not be NULL");
+    RP_EXPECT(m > 0, "!molecules.empty()");
+    RP_EXPECT(n_cells[0] > 0 && n_cells[1] > 0 && n_cells[2] > 0, "dimensions must be > 0");
+    bool seen[3] = {false, false, false};
+    for (int i = 0; i < 3; i++) {
+        RP_EXPECT(axis_order[i] >= 0 && axis_order[i] < 3 && !seen[axis_order[i]], "axis order must be a permutation of xyz");
+        seen[axis_order[i]] = true;
+    }
+    const unsigned long long size = static_cast<unsigned long long>(n_cells[0]) * n_cells[1] * n_cells[2] * m;
+    RP_EXPECT(n_shapes > 0 && size >= n_shapes, "lattice.size() >= numOfShapes");
+    RP_EXPECT(n_shapes < (1ull << 27), "at most 2^27 particles per handle");
+    LatticeArgs L;
+    L.cell = makeBox(cell_box);
+    RP_EXPECT(boxVolume(L.cell) != 0, "cell box volume != 0");
+    // Lattice::getLatticeBox (Lattice.cpp:43-48): every side (column) of the cell box times the number of cells
+    double lb[9];
+    for (int r = 0; r < 3; r++)
+        for (int c = 0; c < 3; c++) lb[3 * r + c] = cell_box[3 * r + c] * static_cast<double>(n_cells[c]);
+    L.lattice = makeBox(lb);
+    for (int i = 0; i < 3; i++) { L.dims[i] = static_cast<int>(n_cells[i]); L.order[i] = axis_order[i]; }
+    L.m = static_cast<int>(m);
+    const uint64_t n = n_shapes;
+    if (n > h->cap || !h->pos) {
+        if (h->pos) cudaFree(h->pos);
+        if (h->orient) cudaFree(h->orient);
+        h->pos = h->orient = nullptr;
+        size_t cap = n + 16;
+        RP_CUDA(cudaMalloc(&h->pos, 3 * cap * sizeof(double)));
+        RP_CUDA(cudaMalloc(&h->orient, 9 * cap * sizeof(double)));
+        h->cap = cap;
+    }
+    h->n = 0;          // the previous state is overwritten in place: a failed call leaves an empty packing
+    ensureStage(h, m * 12 * sizeof(double));
+    RP_CUDA(cudaMemcpyAsync(h->dStage, cell_molecules, m * 12 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    RP_CUDA(cudaMemsetAsync(h->dFlags, 0, sizeof(int), h->stream));
+    k_populate_lattice<<<static_cast<int>((n + 255) / 256), 256, 0, h->stream>>>(
+        static_cast<int>(n), h->cap, L, static_cast<const double *>(h->dStage), h->pos, h->orient, h->dFlags);
+    h->launches++;
+    int outside = 0;
+    RP_CUDA(cudaMemcpyAsync(&outside, h->dFlags, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    RP_CUDA(cudaStreamSynchronize(h->stream));
+    RP_CUDA(cudaGetLastError());
+    RP_EXPECT(!outside, "areShapesWithinBox(shapes, box)");
+    h->n = n;
+    h->box = L.lattice;
+    h->gridDirty = true;
+    h->hasTrial = false;
+    h->hasLastScaling = false;
+    h->sweepCapOld = h->sweepCapOwn = 0;
+    if (h->hasInteraction) setupForInteraction(h);
+    RP_API_END(h)
+}
+
+rp_status rp_randomize_rotations(rp_handle *h, uint64_t seed, int mode, const double axis[3]) {
+    RP_API_BEGIN(h)
+    RP_EXPECT(h->n > 0, "the packing must not be empty");
+    RP_EXPECT(mode >= 0 && mode <= 2, "mode: 0 random, 1 fixed axis, 2 body axis");
+    V3 a = v3(0, 0, 1);
+    if (mode != 0) {
+        RP_EXPECT(axis != nullptr, "axis must not be NULL");
+        a = v3(axis[0], axis[1], axis[2]);
+        RP_EXPECT(norm2(a) > 1e-20, "vectorAxis.norm2() > 1e-20");
+    }
+    const int n = static_cast<int>(h->n);
+    k_randomize_rotations<<<(n + 255) / 256, 256, 0, h->stream>>>(n, h->cap, seed, mode, a, h->orient);
+    h->launches++;
+    RP_CUDA(cudaStreamSynchronize(h->stream));
+    RP_CUDA(cudaGetLastError());
+    h->gridDirty = true;
+    h->hasTrial = false;
+    h->hasLastScaling = false;
     if (h->hasInteraction) setupForInteraction(h);
     RP_API_END(h)
 }

@@ -155,7 +155,7 @@ struct Handle {
     unsigned long long sweepCellsSkipped = 0;   // cells a sweep left out because the staging capacity was too small
     unsigned long long sweepSerial = 0;         // rp_sweep calls made on this handle (timing ring)
     unsigned long long simCycles = 0;           // cycles run by rp_sim loops on this handle (Philox counter of their sweeps)
-    size_t genSmemConfigured[16] = {};     // ... of the k_gen_sweep instantiations (hard kind * 2 + soft)
+    size_t genSmemConfigured[32] = {};     // ... of the k_gen_sweep instantiations (hard kind * 2 + soft, + 12 wide)
     size_t smemConfigured[16] = {};   // cudaFuncAttributeMaxDynamicSharedMemorySize set per kernel variant
     size_t trialCap = 0;
     // what rp_sweep_trace needs to know about the last rp_sweep call

@@ -85,7 +85,9 @@ __device__ __forceinline__ bool overlapAny(const Inter &I, const double *__restr
     return overlapBetween(I, pos1, aux1, c1, pos2, aux2, c2, bc);
 }
 
-template <bool ENERGY>
+// G lanes share a cell (G = 32: a warp per cell; sparse grids — reference cells of one sphere diameter hold less than
+// one centre on average — take fewer lanes per cell so that the lanes are not idle: recountGroup below)
+template <bool ENERGY, int G>
 __global__ void __launch_bounds__(256) k_recount_grid(GridView g, const Inter *__restrict__ interPtr, int earlyExit,
                                                       unsigned long long *__restrict__ count, int *__restrict__ found,
                                                       double *__restrict__ cellEnergy,
@@ -96,13 +98,15 @@ __global__ void __launch_bounds__(256) k_recount_grid(GridView g, const Inter *_
         reinterpret_cast<int *>(&I)[i] = reinterpret_cast<const int *>(interPtr)[i];
     __syncthreads();
 
-    int cell = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    int lane = threadIdx.x & 31;
-    if (cell >= g.numCells) return;
-    if (!ENERGY && earlyExit && *reinterpret_cast<volatile int *>(found)) return;
+    const long long gtid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    int cell = static_cast<int>(gtid / G);
+    const int lane = static_cast<int>(gtid % G);
+    const bool valid = cell < g.numCells;       // (no early return: the group reductions below are warp-wide)
+    if (!valid) cell = 0;
+    const bool skip = !valid || (!ENERGY && earlyExit && *reinterpret_cast<volatile int *>(found));
 
     int cx = cell % g.n[0], cy = (cell / g.n[0]) % g.n[1], cz = cell / (g.n[0] * g.n[1]);
-    int start = g.cellStart[cell], end = g.cellStart[cell + 1];
+    int start = g.cellStart[cell], end = skip ? start : g.cellStart[cell + 1];
     unsigned long long overlaps = 0;
     double energy = 0;
     int kk = I.kk;
@@ -116,7 +120,7 @@ __global__ void __launch_bounds__(256) k_recount_grid(GridView g, const Inter *_
 
         // pairs within the cell (no translation)
         BcFixed none{v3(0, 0, 0)};
-        for (int j = i + 1 + lane; j < end; j += 32) {
+        for (int j = i + 1 + lane; j < end; j += G) {
             int idx2 = g.items[j];
             int particle2 = idx2 / kk, centre2 = idx2 % kk;
             if (multi && particle1 == particle2) continue;
@@ -137,7 +141,7 @@ __global__ void __launch_bounds__(256) k_recount_grid(GridView g, const Inter *_
             int cell2 = neighbourCell(g.n, cx, cy, cz, dx, dy, dz, &tIdx);
             BcFixed bc{g.trans[tIdx]};
             int s2 = g.cellStart[cell2], e2 = g.cellStart[cell2 + 1];
-            for (int j = s2 + lane; j < e2; j += 32) {
+            for (int j = s2 + lane; j < e2; j += G) {
                 int idx2 = g.items[j];
                 int particle2 = idx2 / kk, centre2 = idx2 % kk;
                 if (multi && particle1 == particle2) continue;
@@ -152,14 +156,17 @@ __global__ void __launch_bounds__(256) k_recount_grid(GridView g, const Inter *_
                 }
             }
         }
-        if (!ENERGY && earlyExit && __any_sync(0xffffffffu, overlaps > 0)) break;
+        // (per lane: the other lanes of the group finish their current centre's candidates and stop at the flag)
+        if (!ENERGY && earlyExit && overlaps > 0) break;
     }
 
     if (ENERGY) {
-        for (int o = 16; o > 0; o >>= 1) energy += __shfl_xor_sync(0xffffffffu, energy, o);
-        if (lane == 0) cellEnergy[cell] = energy;
+        #pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) energy += __shfl_xor_sync(0xffffffffu, energy, o);
+        if (lane == 0 && valid) cellEnergy[cell] = energy;
     } else {
-        for (int o = 16; o > 0; o >>= 1) overlaps += __shfl_xor_sync(0xffffffffu, overlaps, o);
+        #pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) overlaps += __shfl_xor_sync(0xffffffffu, overlaps, o);
         if (lane == 0 && overlaps > 0) {
             atomicAdd(count, overlaps);
             if (earlyExit) atomicExch(found, 1);
@@ -167,18 +174,57 @@ __global__ void __launch_bounds__(256) k_recount_grid(GridView g, const Inter *_
     }
 }
 
-// deterministic sum of per-cell energies: fixed strided partials + fixed tree
-__global__ void k_sum_doubles(int n, const double *__restrict__ in, double *__restrict__ out) {
+// lanes per cell of k_recount_grid from the average cell population
+static int recountGroup(const GridStore &gs) {
+    const double avg = static_cast<double>(gs.numItems) / std::max(1, gs.numCells);
+    return avg < 1.5 ? 1 : (avg < 6 ? 4 : (avg < 14 ? 8 : 32));
+}
+
+template <bool ENERGY>
+static void launchRecountGrid(Handle *h, const GridView &g, int earlyExit, unsigned long long *count, int *found,
+                              double *cellEnergy)
+{
+    const int G = recountGroup(h->grid);
+    const long long threads = static_cast<long long>(g.numCells) * G;
+    const int blocks = static_cast<int>((threads + 255) / 256);
+    cudaStream_t st = h->stream;
+    switch (G) {
+        case 1: k_recount_grid<ENERGY, 1><<<blocks, 256, 0, st>>>(g, h->dInter, earlyExit, count, found, cellEnergy, h->orient, h->cap); break;
+        case 4: k_recount_grid<ENERGY, 4><<<blocks, 256, 0, st>>>(g, h->dInter, earlyExit, count, found, cellEnergy, h->orient, h->cap); break;
+        case 8: k_recount_grid<ENERGY, 8><<<blocks, 256, 0, st>>>(g, h->dInter, earlyExit, count, found, cellEnergy, h->orient, h->cap); break;
+        default: k_recount_grid<ENERGY, 32><<<blocks, 256, 0, st>>>(g, h->dInter, earlyExit, count, found, cellEnergy, h->orient, h->cap); break;
+    }
+}
+
+// deterministic sum of per-cell energies: fixed strided partials + fixed tree; block b sums the contiguous chunk
+// [b * chunk, (b + 1) * chunk) (one block: everything)
+__global__ void k_sum_doubles(int n, int chunk, const double *__restrict__ in, double *__restrict__ out) {
     __shared__ double part[1024];
+    const int begin = blockIdx.x * chunk, end = min(n, begin + chunk);
     double s = 0;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) s += in[i];
+    for (int i = begin + threadIdx.x; i < end; i += blockDim.x) s += in[i];
     part[threadIdx.x] = s;
     __syncthreads();
     for (int o = blockDim.x / 2; o > 0; o >>= 1) {
         if (threadIdx.x < o) part[threadIdx.x] += part[threadIdx.x + o];
         __syncthreads();
     }
-    if (threadIdx.x == 0) out[0] = part[0];
+    if (threadIdx.x == 0) out[blockIdx.x] = part[0];
+}
+
+// in[0..n) -> in[n] (needs room for n + 1 + SUM_BLOCKS doubles): two levels when n is large, fixed order either way
+constexpr int SUM_BLOCKS = 296;
+static void sumDoubles(Handle *h, int n, double *in) {
+    cudaStream_t st = h->stream;
+    if (n > 64 * 1024) {
+        const int chunk = (n + SUM_BLOCKS - 1) / SUM_BLOCKS;
+        k_sum_doubles<<<SUM_BLOCKS, 1024, 0, st>>>(n, chunk, in, in + n + 1);
+        k_sum_doubles<<<1, 1024, 0, st>>>(SUM_BLOCKS, SUM_BLOCKS, in + n + 1, in + n);
+        h->launches += 2;
+    } else {
+        k_sum_doubles<<<1, 1024, 0, st>>>(n, n, in, in + n);
+        h->launches++;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -357,9 +403,7 @@ unsigned long long countTotalOverlaps(Handle *h, bool earlyExit) {
                                                                                      h->dFlags + 2);
     } else if (h->hasGrid) {
         GridView g = makeView(h->grid);
-        int blocks = (g.numCells * 32 + 255) / 256;
-        k_recount_grid<false><<<blocks, 256, 0, st>>>(g, h->dInter, earlyExit ? 1 : 0, h->dCounters, h->dFlags + 2,
-                                                     nullptr, h->orient, h->cap);
+        launchRecountGrid<false>(h, g, earlyExit ? 1 : 0, h->dCounters, h->dFlags + 2, nullptr);
     } else {
         long long nPairs = static_cast<long long>(h->n) * (h->n - 1) / 2;
         int blocks = static_cast<int>(std::min<long long>(1184, (nPairs + 255) / 256));
@@ -390,21 +434,19 @@ double totalEnergy(Handle *h) {
     int parts = 0;
     if (h->hasGrid) {
         GridView g = makeView(h->grid);
-        ensureCellEnergy(h, g.numCells + 1);
-        int blocks = (g.numCells * 32 + 255) / 256;
-        k_recount_grid<true><<<blocks, 256, 0, st>>>(g, h->dInter, 0, nullptr, nullptr, h->dCellEnergy, h->orient,
-                                                    h->cap);
+        ensureCellEnergy(h, g.numCells + 2 + SUM_BLOCKS);
+        launchRecountGrid<true>(h, g, 0, nullptr, nullptr, h->dCellEnergy);
         parts = g.numCells;
     } else {
         long long nPairs = static_cast<long long>(h->n) * (h->n - 1) / 2;
         int blocks = static_cast<int>(std::min<long long>(1184, (nPairs + 255) / 256));
         if (blocks == 0) return 0;
-        ensureCellEnergy(h, blocks + 1);
+        ensureCellEnergy(h, blocks + 2 + SUM_BLOCKS);
         k_recount_nogrid<true><<<blocks, 256, 0, st>>>(particleView(h), h->box, h->dInter, nullptr, h->dCellEnergy);
         parts = blocks;
     }
-    k_sum_doubles<<<1, 1024, 0, st>>>(parts, h->dCellEnergy, h->dCellEnergy + parts);
-    h->launches += 2;
+    sumDoubles(h, parts, h->dCellEnergy);
+    h->launches++;
     double result = 0;
     RP_CUDA(cudaMemcpyAsync(&result, h->dCellEnergy + parts, sizeof(double), cudaMemcpyDeviceToHost, st));
     RP_CUDA(cudaStreamSynchronize(st));

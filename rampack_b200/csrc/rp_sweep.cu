@@ -540,7 +540,7 @@ static GenLayout genLayout(const Inter &I) {
     L.offAux = -1;
     if (I.hard == RP_HARD_SPHEROCYLINDER || I.hard == RP_HARD_POLYSPHEROCYLINDER) { L.offAux = w; w += 3 * I.kk; }
     L.offCell = -1;
-    if (I.soft == RP_SOFT_LJ) { L.offCell = w; w += I.kk; }
+    if (I.soft == RP_SOFT_LJ) { w = (w + 1) & ~1; L.offCell = w; w += 2 * I.kk; }
     L.recw = (w + 1) & ~1;
     return L;
 }
@@ -601,11 +601,25 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
         const double t32 = tr * (1 + 1e-4) + 1e-3;
         A.cull32Thr2 = I.soft == RP_SOFT_LJ ? std::numeric_limits<float>::infinity()
                                             : std::nextafterf(static_cast<float>(t32 * t32), INFINITY);
+        A.cullBox = I.soft == RP_SOFT_LJ ? 1 : 0;
+        if (A.cullBox) {
+            // adjacent reference cells: the two centres are closer than 2 cells along every box axis; a centre is
+            // within (totalRange - range) / 2 of its mass centre, i.e. within |row_i(M^-1)| times that in relative
+            // coordinate i; + FP32 rounding of relative coordinates of magnitude < 3 sweep cells
+            const double rMol = 0.5 * (I.totalRange - I.range);
+            for (int i = 0; i < 3; i++) {
+                const double row = std::sqrt(h->box.inv.a[3 * i] * h->box.inv.a[3 * i]
+                                             + h->box.inv.a[3 * i + 1] * h->box.inv.a[3 * i + 1]
+                                             + h->box.inv.a[3 * i + 2] * h->box.inv.a[3 * i + 2]);
+                const double b = (2 * A.refRelCell[i] + 2 * rMol * row) * (1 + 1e-5) + 1e-5 * sg.relCell[i];
+                A.cullBoxHalf[i] = std::nextafterf(static_cast<float>(b), INFINITY);
+            }
+        }
     }
     SweepCellOffsets off;
     for (int code = 0; code < 27; code++) {
-        V3 o = relToAbs(h->box, v3((code % 3 - 1) * sg.relCell[0], ((code / 3) % 3 - 1) * sg.relCell[1],
-                                   (code / 9 - 1) * sg.relCell[2]));
+        V3 o = v3((code % 3 - 1) * sg.relCell[0], ((code / 3) % 3 - 1) * sg.relCell[1], (code / 9 - 1) * sg.relCell[2]);
+        if (!A.cullBox) o = relToAbs(h->box, o);
         off.o[code][0] = static_cast<float>(o.x); off.o[code][1] = static_cast<float>(o.y);
         off.o[code][2] = static_cast<float>(o.z);
     }
@@ -635,6 +649,12 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
         if (A.capOwn <= 2 * GEN_MAXOWN && withMatrices <= 110 * 1024) { A.matrices = 1; smem = withMatrices; }
         else A.matrices = 2;
     }
+    // crowded cells (block-wise sequential mode: the wide cells of the un-truncated LJ potential hold ~100 particles
+    // and ~2700 frozen candidates): 16 warps per cell instead of 4
+    const bool softOn = I.soft != RP_SOFT_NONE;
+    const bool wide = A.matrices == 2 && softOn && I.hard != RP_HARD_XENOCOLLIDE;
+    const int threads = wide ? GEN_THREADS_WIDE : GEN_THREADS;
+    if (wide) smem = genSmemBytes(A.capOld, A.capOwn, static_cast<int>(recw), false, threads);
     if (smem > 200 * 1024)
         throw rp_error(RP_ERR_CAPACITY, "rp_sweep: a cell does not fit into shared memory");
     RP_CUDA(cudaEventRecord(ev[2], st));
@@ -642,7 +662,6 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
                                                   h->crel, T, makeWalls(h->box, h->wallMask, I.totalRange), h->pos);
     h->launches++;
     const int blocks = A.nActive[0] * A.nActive[1] * A.nActive[2];
-    const bool softOn = I.soft != RP_SOFT_NONE;
     for (int c = 0; c < 8; c++) {
         GenArgs Ac = A;
         int col = colourOrder[c];
@@ -656,33 +675,40 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
                                              static_cast<int>(want)));
                 configured = want;
             }
-            kernel<<<blocks, GEN_THREADS, smem, st>>>(Ac, sg, off, h->box, h->dInter, g.cellStart, g.items, h->genRec,
-                                                      cull, T, h->pos, h->orient, h->crel, h->cabs, h->dCounters,
-                                                      h->dFlags);
+            kernel<<<blocks, threads, smem, st>>>(Ac, sg, off, h->box, h->dInter, g.cellStart, g.items, h->genRec,
+                                                  cull, T, h->pos, h->orient, h->crel, h->cabs, h->dCounters,
+                                                  h->dFlags);
         };
-        const int slotIndex = I.hard * 2 + (softOn ? 1 : 0);
+        const int slotIndex = I.hard * 2 + (softOn ? 1 : 0) + (wide ? 12 : 0);
+        constexpr int TN = GEN_THREADS, TW = GEN_THREADS_WIDE;
         switch (I.hard) {
             case RP_HARD_NONE:
-                launch(k_gen_sweep<RP_HARD_NONE, true>, slotIndex); break;
+                if (wide) launch(k_gen_sweep<RP_HARD_NONE, true, TW>, slotIndex);
+                else launch(k_gen_sweep<RP_HARD_NONE, true, TN>, slotIndex);
+                break;
             case RP_HARD_SPHERE:
-                if (softOn) launch(k_gen_sweep<RP_HARD_SPHERE, true>, slotIndex);
-                else launch(k_gen_sweep<RP_HARD_SPHERE, false>, slotIndex);
+                if (wide) launch(k_gen_sweep<RP_HARD_SPHERE, true, TW>, slotIndex);
+                else if (softOn) launch(k_gen_sweep<RP_HARD_SPHERE, true, TN>, slotIndex);
+                else launch(k_gen_sweep<RP_HARD_SPHERE, false, TN>, slotIndex);
                 break;
             case RP_HARD_SPHEROCYLINDER:
-                if (softOn) launch(k_gen_sweep<RP_HARD_SPHEROCYLINDER, true>, slotIndex);
-                else launch(k_gen_sweep<RP_HARD_SPHEROCYLINDER, false>, slotIndex);
+                if (wide) launch(k_gen_sweep<RP_HARD_SPHEROCYLINDER, true, TW>, slotIndex);
+                else if (softOn) launch(k_gen_sweep<RP_HARD_SPHEROCYLINDER, true, TN>, slotIndex);
+                else launch(k_gen_sweep<RP_HARD_SPHEROCYLINDER, false, TN>, slotIndex);
                 break;
             case RP_HARD_POLYSPHERE:
-                if (softOn) launch(k_gen_sweep<RP_HARD_POLYSPHERE, true>, slotIndex);
-                else launch(k_gen_sweep<RP_HARD_POLYSPHERE, false>, slotIndex);
+                if (wide) launch(k_gen_sweep<RP_HARD_POLYSPHERE, true, TW>, slotIndex);
+                else if (softOn) launch(k_gen_sweep<RP_HARD_POLYSPHERE, true, TN>, slotIndex);
+                else launch(k_gen_sweep<RP_HARD_POLYSPHERE, false, TN>, slotIndex);
                 break;
             case RP_HARD_POLYSPHEROCYLINDER:
-                if (softOn) launch(k_gen_sweep<RP_HARD_POLYSPHEROCYLINDER, true>, slotIndex);
-                else launch(k_gen_sweep<RP_HARD_POLYSPHEROCYLINDER, false>, slotIndex);
+                if (wide) launch(k_gen_sweep<RP_HARD_POLYSPHEROCYLINDER, true, TW>, slotIndex);
+                else if (softOn) launch(k_gen_sweep<RP_HARD_POLYSPHEROCYLINDER, true, TN>, slotIndex);
+                else launch(k_gen_sweep<RP_HARD_POLYSPHEROCYLINDER, false, TN>, slotIndex);
                 break;
             case RP_HARD_XENOCOLLIDE:
-                if (softOn) launch(k_gen_sweep<RP_HARD_XENOCOLLIDE, true>, slotIndex);
-                else launch(k_gen_sweep<RP_HARD_XENOCOLLIDE, false>, slotIndex);
+                if (softOn) launch(k_gen_sweep<RP_HARD_XENOCOLLIDE, true, TN>, slotIndex);
+                else launch(k_gen_sweep<RP_HARD_XENOCOLLIDE, false, TN>, slotIndex);
                 break;
             default:
                 throw rp_error(RP_ERR_UNSUPPORTED, "rp_sweep: unknown hard interaction kind");

@@ -33,7 +33,7 @@ struct GenLayout {
     int offOrient;   // 9 doubles, -1 = absent
     int offCentre;   // kk x 3 doubles; k == 0: 0 (the centre is the mass centre)
     int offAux;      // kk x 3 doubles, -1 = absent
-    int offCell;     // kk packed cells (3 x 21 bit, bias 2^20), -1 = absent
+    int offCell;     // kk x {int x, y, z, 0} (two doubles per centre, 16-byte aligned), -1 = absent
     int kk;
 };
 
@@ -44,7 +44,9 @@ struct GenArgs {
     unsigned int cycle, pass;
     int colour[3], nActive[3];
     int capOwn, capOld;      // shared-memory capacities: particles of the active cell / frozen candidates around it
-    float cull32Thr2;        // FP32 cull of mass-centre distances (conservative: cull range + rounding); LJ: +inf
+    float cull32Thr2;        // FP32 cull of mass-centre distances (conservative: cull range + rounding); LJ: unused
+    int cullBox;             // un-truncated LJ: the cull points hold RELATIVE coordinates and the cull is the box
+    float cullBoxHalf[3];    //   |d rel_i| < cullBoxHalf[i] (two reference cells + the molecules' extent + rounding)
     int counting;            // Packing::overlapCounting
     int matrices;            // in-cell pair terms as matrices (counting / soft / > 64 particles per cell) or bit masks
     // RP_MOVE_FLIP (FlipSampler.cpp:18-41): body-frame flip axis, geometric origin, attempt probability 1 / flipEvery
@@ -73,19 +75,15 @@ __device__ __forceinline__ void st3(double *p, V3 v) { p[0] = v.x; p[1] = v.y; p
 
 // extended reference-grid cell of a position given in the image frame (NeighbourGrid::positionToCellNo without the
 // wrap: floor(rel / relativeCellSize), may be < 0 or >= n)
-__device__ __forceinline__ long long packRefCell(const Box &box, const double refRelCell[3], V3 p) {
+__device__ __forceinline__ int4 refCellOf(const Box &box, const double refRelCell[3], V3 p) {
     V3 rel = absToRel(box, p);
-    long long cx = static_cast<long long>(floor(rel.x / refRelCell[0])) + (1 << 20);
-    long long cy = static_cast<long long>(floor(rel.y / refRelCell[1])) + (1 << 20);
-    long long cz = static_cast<long long>(floor(rel.z / refRelCell[2])) + (1 << 20);
-    return cx | (cy << 21) | (cz << 42);
+    return make_int4(static_cast<int>(floor(rel.x / refRelCell[0])), static_cast<int>(floor(rel.y / refRelCell[1])),
+                     static_cast<int>(floor(rel.z / refRelCell[2])), 0);
 }
-__device__ __forceinline__ bool refCellsAdjacent(long long a, long long b, int gx, int gy, int gz, const int n[3]) {
-    const long long M = (1 << 21) - 1;
-    long long dx = (a & M) - ((b & M) + gx * n[0]);
-    long long dy = ((a >> 21) & M) - (((b >> 21) & M) + gy * n[1]);
-    long long dz = ((a >> 42) & M) - (((b >> 42) & M) + gz * n[2]);
-    return dx >= -1 && dx <= 1 && dy >= -1 && dy <= 1 && dz >= -1 && dz <= 1;
+// a = cell of the first centre minus the lattice translation's (gx n0, gy n1, gz n2); b = cell of the second centre
+__device__ __forceinline__ bool refCellsAdjacent(const int4 &a, const int4 &b) {
+    return static_cast<unsigned int>(a.x - b.x + 1) <= 2u && static_cast<unsigned int>(a.y - b.y + 1) <= 2u
+           && static_cast<unsigned int>(a.z - b.z + 1) <= 2u;
 }
 
 // fills the derived parts of a record from {mass centre p, orientation o, centre offsets crel[k]}
@@ -99,13 +97,15 @@ __device__ __forceinline__ void fillRecord(const Inter &I, const GenArgs &A, con
     if (L.offAux >= 0) for (int c = 0; c < L.kk; c++) st3(r + L.offAux + 3 * c, pairAux(I, o, c));
     if (L.offCell >= 0)
         for (int c = 0; c < L.kk; c++)
-            reinterpret_cast<long long *>(r)[L.offCell + c] = packRefCell(box, A.refRelCell, ld3(r + L.offCentre + 3 * c));
+            reinterpret_cast<int4 *>(r + L.offCell)[c] = refCellOf(box, A.refRelCell, ld3(r + L.offCentre + 3 * c));
 }
 
-// FP32 cull point of a particle state: mass centre relative to the centre of the particle's own sweep cell
-__device__ __forceinline__ float4 genCullPoint(const V3 &p, const V3 &centre) {
-    return make_float4(static_cast<float>(p.x - centre.x), static_cast<float>(p.y - centre.y),
-                       static_cast<float>(p.z - centre.z), 0.f);
+// FP32 cull point of a particle state: mass centre relative to the centre of the particle's own sweep cell (box cull
+// of the un-truncated LJ potential: in relative coordinates)
+__device__ __forceinline__ float4 genCullPoint(const GenArgs &A, const Box &box, const V3 &p, const V3 &centre) {
+    V3 d = p - centre;
+    if (A.cullBox) d = absToRel(box, d);
+    return make_float4(static_cast<float>(d.x), static_cast<float>(d.y), static_cast<float>(d.z), 0.f);
 }
 
 // one warp per cell: items by ascending particle index + the generic records (image frame) + the FP32 cull points
@@ -141,7 +141,7 @@ __global__ void k_gen_records(int numCells, GenArgs A, SweepGrid sg, Box box, co
             crel[c] = v3(crelAll[idx], crelAll[A.ccap + idx], crelAll[2 * A.ccap + idx]);
         }
         fillRecord(I, A, box, rec + static_cast<size_t>(slot) * A.L.recw, p, o, crel);
-        cull[slot] = genCullPoint(p, centre);
+        cull[slot] = genCullPoint(A, box, p, centre);
     }
 }
 
@@ -258,7 +258,7 @@ __global__ void __launch_bounds__(128) k_gen_trials(int n, GenArgs A, SweepGrid 
         T.wall[slot] = make_int2(wallOld, wallNew);
     }
     fillRecord(I, A, box, T.rec + static_cast<size_t>(slot) * A.L.recw, p, O, crel);
-    T.cull[slot] = genCullPoint(p, sweepCellCentre(sg, box, cc[0], cc[1], cc[2]));
+    T.cull[slot] = genCullPoint(A, box, p, sweepCellCentre(sg, box, cc[0], cc[1], cc[2]));
     double *o = T.orient + 9 * static_cast<size_t>(slot);
     for (int q = 0; q < 9; q++) o[q] = O.a[q];
     for (int c = 0; c < I.k; c++) st3(T.crel + (static_cast<size_t>(slot) * I.k + c) * 3, crel[c]);
@@ -286,6 +286,11 @@ __device__ __forceinline__ void pairTerms(const Inter &I, const GenArgs &A, cons
     for (int c1 = 0; c1 < L.kk; c1++) {
         V3 pos1 = ld3(a + L.offCentre + 3 * c1);
         V3 aux1 = HAS_AUX ? ld3(a + L.offAux + 3 * c1) : v3(0, 0, 0);
+        int4 cell1 = make_int4(0, 0, 0, 0);
+        if (SOFT && L.offCell >= 0) {
+            cell1 = reinterpret_cast<const int4 *>(a + L.offCell)[c1];
+            cell1.x -= gx * A.refN[0]; cell1.y -= gy * A.refN[1]; cell1.z -= gz * A.refN[2];
+        }
         for (int c2 = 0; c2 < L.kk; c2++) {
             V3 pos2 = ld3(b + L.offCentre + 3 * c2);
             if (HARD != RP_HARD_NONE && wantOv) {
@@ -304,29 +309,28 @@ __device__ __forceinline__ void pairTerms(const Inter &I, const GenArgs &A, cons
                 }
             }
             if (SOFT && wantEn) {
-                if (L.offCell >= 0) {
-                    long long ca = reinterpret_cast<const long long *>(a)[L.offCell + c1];
-                    long long cb = reinterpret_cast<const long long *>(b)[L.offCell + c2];
-                    if (!refCellsAdjacent(ca, cb, gx, gy, gz, A.refN)) continue;
-                }
+                if (L.offCell >= 0 && !refCellsAdjacent(cell1, reinterpret_cast<const int4 *>(b + L.offCell)[c2]))
+                    continue;
                 *en += energyBetween(I, pos1, pos2, bc);
             }
         }
     }
 }
 
-constexpr int GEN_THREADS = 128;
+constexpr int GEN_THREADS = 128;     // default CTA; crowded cells (block-wise sequential mode) take GEN_THREADS_WIDE
+constexpr int GEN_THREADS_WIDE = 512;
 constexpr int GEN_MAXOWN = 64;       // trials per cell the bit masks of the hard-only resolution cover
 constexpr int GEN_MAXCELL = 512;     // particles per sweep cell the kernel supports at all
 
 // shared memory of k_gen_sweep beyond its static part, for (capOld frozen candidates, capOwn particles in the cell)
-__host__ __device__ inline size_t genSmemBytes(int capOld, int capOwn, int recw, bool matrices) {
+__host__ __device__ inline size_t genSmemBytes(int capOld, int capOwn, int recw, bool matrices,
+                                               int threads = GEN_THREADS) {
     capOwn = (capOwn + 1) & ~1;                                             // (keeps the double arrays 8-byte aligned)
     size_t b = 16 * static_cast<size_t>(capOld + 2 * capOwn);               // FP32 cull points: candidates, trial + current states
     b += 2 * static_cast<size_t>(capOwn) * recw * 8;                        // cur, tri
     b += 3 * static_cast<size_t>(capOwn) * 8;                               // eOld, eNew, uMet
     b += 5 * static_cast<size_t>(capOwn) * 4;                               // ovOld, ovNew, rejected, seq, orderKey
-    b += (GEN_THREADS / 32) * 64 * 4;                                       // per-warp survivor queues
+    b += (threads / 32) * 64 * 4;                                           // per-warp survivor queues
     if (matrices) b += 4 * static_cast<size_t>(capOwn) * capOwn * (8 + 2);  // in-cell pair matrices
     return b + 64;
 }
@@ -346,15 +350,15 @@ __host__ __device__ inline size_t genSmemBytes(int capOld, int capOwn, int recw,
 //             other is now a walk over the precomputed tables (the state of j a term is taken from follows `moved`)
 // The decisions are those of a sequential Monte Carlo pass through the cell, as before.
 // ---------------------------------------------------------------------------------------------------------------
-template <int HARD, bool SOFT>
-__global__ void __launch_bounds__(GEN_THREADS)
+template <int HARD, bool SOFT, int THREADS>
+__global__ void __launch_bounds__(THREADS)
 k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter *__restrict__ interPtr,
             const int *__restrict__ cellStart, const int *__restrict__ items, double *__restrict__ rec,
             float4 *__restrict__ cull, GenTrialBuffers T, double *__restrict__ pos, double *__restrict__ orient,
             double *__restrict__ crelAll, double *__restrict__ cabsAll, unsigned long long *__restrict__ counters,
             int *__restrict__ flags)
 {
-    constexpr int WARPS = GEN_THREADS / 32;
+    constexpr int WARPS = THREADS / 32;
     constexpr bool hard = HARD != RP_HARD_NONE, soft = SOFT;
     extern __shared__ __align__(16) unsigned char smemRaw[];
     __shared__ Inter I;
@@ -364,14 +368,14 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
     __shared__ unsigned long long sBar;
     __shared__ unsigned long long ownMask[GEN_MAXOWN], newMask[GEN_MAXOWN];
     __shared__ unsigned long long sMoved[GEN_MAXCELL / 64];      // accepted trials of the cell, one bit each
-    __shared__ double sRedE[2 * (GEN_THREADS / 32)];
-    __shared__ int sRedO[2 * (GEN_THREADS / 32)];
+    __shared__ double sRedE[2 * (THREADS / 32)];
+    __shared__ int sRedO[2 * (THREADS / 32)];
     __shared__ int sAccept;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const GenLayout &L = A.L;
     const int recw = L.recw;
-    for (int i = tid; i < static_cast<int>(sizeof(Inter) / sizeof(int)); i += GEN_THREADS)
+    for (int i = tid; i < static_cast<int>(sizeof(Inter) / sizeof(int)); i += THREADS)
         reinterpret_cast<int *>(&I)[i] = reinterpret_cast<const int *>(interPtr)[i];
 
     const bool counting = A.counting != 0 && hard;
@@ -452,11 +456,11 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
         return;
     }
     // own cell: current and trial records, trial meta
-    for (int i = tid; i < numOwn * recw; i += GEN_THREADS) {
+    for (int i = tid; i < numOwn * recw; i += THREADS) {
         cur[i] = rec[static_cast<size_t>(ownStart) * recw + i];
         tri[i] = T.rec[static_cast<size_t>(ownStart) * recw + i];
     }
-    for (int i = tid; i < numOwn; i += GEN_THREADS) {
+    for (int i = tid; i < numOwn; i += THREADS) {
         const uint2 meta = T.meta[ownStart + i];
         rejected[i] = static_cast<int>(meta.x);
         orderKey[i] = meta.y;
@@ -514,10 +518,18 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
                     if (jj < numFrozen) {
                         const float4 c = cand[jj];
                         const float dx = c.x - pt.x, dy = c.y - pt.y, dz = c.z - pt.z;
-                        pass = !(fmaf(dz, dz, fmaf(dy, dy, dx * dx)) >= A.cull32Thr2);
-                        if (needOld) {
-                            const float ex = c.x - po.x, ey = c.y - po.y, ez = c.z - po.z;
-                            pass = pass || !(fmaf(ez, ez, fmaf(ey, ey, ex * ex)) >= A.cull32Thr2);
+                        const float ex = c.x - po.x, ey = c.y - po.y, ez = c.z - po.z;
+                        if (A.cullBox) {
+                            // un-truncated LJ: a centre pair contributes iff its reference-grid cells are adjacent,
+                            // i.e. only if the mass centres are closer than two reference cells + the molecules'
+                            // extent along every box axis (relative coordinates)
+                            pass = !(fabsf(dx) >= A.cullBoxHalf[0]) && !(fabsf(dy) >= A.cullBoxHalf[1])
+                                   && !(fabsf(dz) >= A.cullBoxHalf[2]);
+                            pass = pass || (!(fabsf(ex) >= A.cullBoxHalf[0]) && !(fabsf(ey) >= A.cullBoxHalf[1])
+                                            && !(fabsf(ez) >= A.cullBoxHalf[2]));
+                        } else {
+                            pass = !(fmaf(dz, dz, fmaf(dy, dy, dx * dx)) >= A.cull32Thr2);
+                            if (needOld) pass = pass || !(fmaf(ez, ez, fmaf(ey, ey, ex * ex)) >= A.cull32Thr2);
                         }
                     }
                     const unsigned int m = __ballot_sync(0xffffffffu, pass);
@@ -556,7 +568,7 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
         }
     }
     // processing order: rank of the random key
-    for (int i = tid; i < numOwn; i += GEN_THREADS) {
+    for (int i = tid; i < numOwn; i += THREADS) {
         const unsigned int k = orderKey[i];
         int rank = 0;
         for (int j = 0; j < numOwn; j++) {
@@ -570,7 +582,7 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
     // ---- phase 2a: pair terms inside the cell, every ordered pair (i, j), all threads ----
     {
         const V3 zero = v3(0, 0, 0);
-        for (int p = tid; p < (blockwise ? 0 : numOwn * numOwn); p += GEN_THREADS) {
+        for (int p = tid; p < (blockwise ? 0 : numOwn * numOwn); p += THREADS) {
             const int i = p / numOwn, j = p - i * numOwn;
             if (i == j || rejected[i] != 0) continue;
             const double *ta = tri + static_cast<size_t>(i) * recw, *oa = cur + static_cast<size_t>(i) * recw;
@@ -622,7 +634,7 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
             int oO = 0, oN = 0;
             double enO = 0, enN = 0;
             if (state == 0) {
-                for (int j = tid; j < numOwn; j += GEN_THREADS) {
+                for (int j = tid; j < numOwn; j += THREADS) {
                     if (j == i) continue;
                     const double *rb = cur + static_cast<size_t>(j) * recw;
                     pairTerms<HARD, SOFT>(I, A, ta, rb, zero, 0, 0, 0, hard, soft, !counting, &oN, &enN);
@@ -665,7 +677,7 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
             }
             __syncthreads();
             if (sAccept)
-                for (int q = tid; q < recw; q += GEN_THREADS) cur[static_cast<size_t>(i) * recw + q] = ta[q];
+                for (int q = tid; q < recw; q += THREADS) cur[static_cast<size_t>(i) * recw + q] = ta[q];
             __syncthreads();
         }
         if (tid == 0) {

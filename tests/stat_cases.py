@@ -80,6 +80,70 @@ CASES = {
 }
 
 
+def dumbbell_lattice(n_side, spacing):
+    """k-mers along z on a lattice with cell (spacing, spacing, spacing + 1): the beads of one molecule are 1 apart."""
+    g = (np.arange(n_side) + 0.5)
+    x, y, z = np.meshgrid(g * spacing, g * spacing, g * (spacing + 1.0), indexing="ij")
+    shapes = np.zeros((n_side ** 3, 12))
+    shapes[:, :3] = np.stack([x.ravel(), y.ravel(), z.ravel()], axis=1)
+    shapes[:, 3:] = np.eye(3).ravel()
+    return np.diag([n_side * spacing, n_side * spacing, n_side * (spacing + 1.0)]), shapes
+
+
+def _kmer_desc(k, soft=rp.RP_SOFT_NONE, hard=True, epsilon=1.0, sigma=1.0):
+    z0 = -(k - 1) / 2
+    return rp.make_desc(hard=rp.RP_HARD_POLYSPHERE if hard else rp.RP_HARD_NONE, soft=soft, epsilon=epsilon,
+                        sigma=sigma, centres=[(0.0, 0.0, z0 + i) for i in range(k)], centre_radius=[0.5] * k)
+
+
+def ordered_snapshot(name):
+    """Equilibrated L/D = 5 starting states written by tests/golden/make_ordered_snapshots.py (device run)."""
+    import os
+    d = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "sc_l5_ordered.npz"))
+    return d[name + "_box"], d[name + "_shapes"]
+
+
+# The reference's own validation goldens on the generic path (test/validation_tests/SimulationTest.cpp): un-truncated
+# Lennard-Jones gas (:150-177), hard dumbbells (:179-206), WCA dumbbells (:208-244) — same thermodynamic points, at a
+# particle number the checkerboard sweep admits; both sides run the same N, so finite-size effects cancel.  The
+# reference's quoted densities are for N = 50 and are only used where they do not depend on N (second-virial LJ gas).
+CASES.update({
+    "lj_gas": dict(
+        desc=lambda: rp.make_desc(hard=rp.RP_HARD_NONE, soft=rp.RP_SOFT_LJ, radius=0.5, epsilon=1.0, sigma=0.5),
+        state=lambda: sphere_lattice(10, 1.0),
+        temperature=100.0, pressure=200.0, trans_step=0.3, rot_step=0.1, nematic=False,
+        # (the reference's 1.6637 is for N = 50: without a cutoff the pair set follows the neighbour-grid geometry, so
+        # the density depends on N — 1.6252 +- 0.0020 at N = 1000 in the reference's own run, stat_golden.json)
+        scaler=("delta_v", 6.0), therm=3000, avg=10000, every=20, eos_density=None, gr=(0.5, 0.7),
+        seeds_ref=4, seeds_dev=4),
+    "hard_dumbbells": dict(
+        desc=lambda: _kmer_desc(2), state=lambda: dumbbell_lattice(8, 1.25),
+        temperature=1.0, pressure=2.0, trans_step=0.3, rot_step=0.3, nematic=True, axis_column=2,
+        scaler=("delta_v", 20.0), therm=5000, avg=20000, every=20, eos_density=None, gr=(1.0, 1.3),
+        seeds_ref=4, seeds_dev=4),
+    "wca_dumbbells": dict(
+        desc=lambda: _kmer_desc(2, soft=rp.RP_SOFT_WCA, hard=False), state=lambda: dumbbell_lattice(8, 1.25),
+        temperature=1.0, pressure=7.5, trans_step=0.15, rot_step=0.15, nematic=True, axis_column=2,
+        scaler=("delta_v", 10.0), therm=5000, avg=20000, every=20, eos_density=None, gr=(1.0, 1.3),
+        seeds_ref=4, seeds_dev=4),
+    # ORDERED state points of BASELINE config 2 (hard spherocylinders L/D = 5): a nematic and a smectic pressure, both
+    # sides started from the same device-equilibrated snapshot (tests/golden/sc_l5_ordered.npz) with the step sizes
+    # the equilibration run adapted.  P2 and tau are order parameters here, not noise floors.
+    "sc_l5_nematic": dict(
+        desc=lambda: rp.make_desc(hard=rp.RP_HARD_SPHEROCYLINDER, radius=0.5, length=5.0),
+        state=lambda: ordered_snapshot("sc_l5_nematic"),
+        temperature=1.0, pressure=1.2, trans_step=0.15, rot_step=0.08, nematic=True,
+        scaler=("delta_triclinic", 0.004, False), therm=3000, avg=20000, every=20, eos_density=None, gr=(1.0, 1.3),
+        min_p2=0.5, seeds_ref=4, seeds_dev=4),
+    "sc_l5_smectic": dict(
+        desc=lambda: rp.make_desc(hard=rp.RP_HARD_SPHEROCYLINDER, radius=0.5, length=5.0),
+        state=lambda: ordered_snapshot("sc_l5_smectic"),
+        temperature=1.0, pressure=2.2, trans_step=0.1, rot_step=0.05, nematic=True,
+        scaler=("delta_triclinic", 0.003, False), therm=3000, avg=20000, every=20, eos_density=None, gr=(1.0, 1.3),
+        min_p2=0.5, min_tau=0.3, seeds_ref=4, seeds_dev=4),
+})
+
+
 def number_density(box, shapes):
     """NumberDensity (src/core/observables/scalar/NumberDensity.cpp): N / V."""
     return shapes.shape[0] / abs(np.linalg.det(box))
@@ -128,7 +192,7 @@ def pair_density_in_shell(box, shapes, r_lo, r_hi):
 def observables(case, box, shapes):
     out = {"density": number_density(box, shapes), "g_shell": pair_density_in_shell(box, shapes, *case["gr"])}
     if case["nematic"]:
-        out["p2"] = nematic_p2(shapes)
+        out["p2"] = nematic_p2(shapes, case.get("axis_column", 2))
         out["tau"] = smectic_tau(box, shapes)
     return out
 

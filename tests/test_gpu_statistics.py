@@ -78,32 +78,36 @@ def run_device(case, loop=NativeLoop, seed=97531):
 def test_observables_agree_with_the_reference_run(name, loop):
     case = S.CASES[name]
     golden = json.load(open(GOLDEN))[name]
-    # Each comparison is a 2-sigma test, and a case holds 2-4 of them: with perfectly matching distributions one in
-    # five cases would still show some |z| > 2.  A deviation is therefore re-examined with MORE device data (the same
-    # number of fresh seeds again, at most twice): chance deviations shrink, a real bias keeps its size while the
-    # error bar shrinks, so its z grows.  The assertion is on the final, largest data set.
+    # The number of device runs is FIXED up front (seeds_dev independent seeds, no optional stopping: a sequential
+    # "re-run until it passes" test would widen the acceptance band).  Every comparison is a 2-sigma test on the
+    # combined standard error (north_star); a case holds 2-4 of them, so the assertion allows for the look-elsewhere
+    # effect in the only honest way available to a fixed-size test: z <= 2 for every observable, except that ONE
+    # observable of a case may reach z <= 3 (probability of a false alarm per case ~ 1 %).
     n_seeds = case.get("seeds_dev", 1)
-    runs, worst, report = [], 0.0, []
-    for attempt in range(3):
-        for k in range(n_seeds):
-            stats, overlaps, launches, rates = run_device(case, loop, seed=97531 + 1000 * len(runs))
-            assert overlaps == 0
-            assert launches > 10 * (case["therm"] + case["avg"])      # every cycle ran kernels of this library
-            runs.append(stats)
-        stats = S.combine_runs(runs)
-        report, worst = [], 0.0
-        for key, (mean, se) in stats.items():
-            g = golden[key]
-            combined = math.sqrt(se * se + g["se"] * g["se"])
-            z = abs(mean - g["mean"]) / combined if combined > 0 else 0.0
-            report.append(f"{key}: device {mean:.6g} +- {se:.2g}, reference {g['mean']:.6g} +- {g['se']:.2g}, "
-                          f"z = {z:.2f}")
-            worst = max(worst, z)
-        print(f"[{name}, {loop.__name__}, {len(runs)} device run(s)] move acceptance {rates[0]:.3f}, box-move "
-              f"acceptance {rates[1]:.3f}\n  " + "\n  ".join(report))
-        if worst <= TOLERANCE_SE:
-            break
-    assert worst <= TOLERANCE_SE, "\n".join(report)
+    runs = []
+    for k in range(n_seeds):
+        stats, overlaps, launches, rates = run_device(case, loop, seed=97531 + 1000 * k)
+        assert overlaps == 0
+        assert launches > 10 * (case["therm"] + case["avg"])      # every cycle ran kernels of this library
+        runs.append(stats)
+    stats = S.combine_runs(runs)
+    report, zs = [], []
+    for key, (mean, se) in stats.items():
+        g = golden[key]
+        combined = math.sqrt(se * se + g["se"] * g["se"])
+        z = abs(mean - g["mean"]) / combined if combined > 0 else 0.0
+        report.append(f"{key}: device {mean:.6g} +- {se:.2g}, reference {g['mean']:.6g} +- {g['se']:.2g}, "
+                      f"z = {z:.2f}")
+        zs.append(z)
+    print(f"[{name}, {loop.__name__}, {len(runs)} device run(s)] move acceptance {rates[0]:.3f}, box-move "
+          f"acceptance {rates[1]:.3f}\n  " + "\n  ".join(report))
+    zs.sort()
+    assert zs[-1] <= 3.0 and (len(zs) < 2 or zs[-2] <= TOLERANCE_SE), "\n".join(report)
+    # ordered state points: the order parameters are far above the 1 / sqrt(N) noise floor on BOTH sides
+    if "min_p2" in case:
+        assert stats["p2"][0] > case["min_p2"] and golden["p2"]["mean"] > case["min_p2"], report
+    if "min_tau" in case:
+        assert stats["tau"][0] > case["min_tau"] and golden["tau"]["mean"] > case["min_tau"], report
     if case["eos_density"] is not None:
         mean, se = stats["density"]
         assert abs(mean - case["eos_density"]) <= 3 * max(se, 1e-4 * mean), (mean, se, case["eos_density"])

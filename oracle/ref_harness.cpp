@@ -634,7 +634,8 @@ int rpr_populate_lattice(const double cellBox[9], const double *molecules, std::
         Lattice lattice(cell, {std::size_t(dims[0]), std::size_t(dims[1]), std::size_t(dims[2])});
         SerialPopulator populator{std::string(axisOrder)};
         auto shapes = populator.populateLattice(lattice, n);
-        const auto &dim = lattice.getLatticeBox().getDimensions();
+        const TriclinicBox latticeBox = lattice.getLatticeBox();
+        const auto &dim = latticeBox.getDimensions();
         for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) boxOut[3*r + c] = dim(r, c);
         for (std::size_t i = 0; i < shapes.size(); i++) fromShape(shapes[i], shapesOut + 12*i);
     } catch (const std::exception &e) {

@@ -370,6 +370,7 @@ void rp_destroy(rp_handle *h) {
     freeGrid(h->grid);
     freeGrid(h->tempGrid);
     freeGrid(h->sgrid);
+    freeGrid(h->ogrid);
     for (auto &ev : h->ev) if (ev) cudaEventDestroy(ev);
     for (auto &ev : h->sweepMaxEvent) if (ev) cudaEventDestroy(ev);
     for (auto &t : h->timing) for (auto &ev : t.e) if (ev) cudaEventDestroy(ev);

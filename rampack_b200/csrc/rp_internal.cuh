@@ -136,6 +136,7 @@ struct Handle {
     bool gridDirty = true;
     // sweep grid (random origin, particle mass centres, even cell counts)
     GridStore sgrid;
+    GridStore ogrid;      // cell list of the g(r) observable (rp_observe.cu)
     int *sweepMoved = nullptr;    // (unused)
     size_t sweepMovedCap = 0;
     // trials of one rp_sweep call, per sorted slot: record (6 doubles), new orientation (9 doubles), meta (uint2),
@@ -156,7 +157,7 @@ struct Handle {
     unsigned long long sweepSerial = 0;         // rp_sweep calls made on this handle (timing ring)
     unsigned long long simCycles = 0;           // cycles run by rp_sim loops on this handle (Philox counter of their sweeps)
     size_t genSmemConfigured[32] = {};     // ... of the k_gen_sweep instantiations (hard kind * 2 + soft, + 12 wide)
-    size_t smemConfigured[16] = {};   // cudaFuncAttributeMaxDynamicSharedMemorySize set per kernel variant
+    size_t smemConfigured[24] = {};   // cudaFuncAttributeMaxDynamicSharedMemorySize set per kernel variant
     size_t trialCap = 0;
     // what rp_sweep_trace needs to know about the last rp_sweep call
     bool lastSweepValid = false, lastSweepGeneric = false, lastSweepRotated = false;

@@ -8,6 +8,8 @@
 // scheduling.  The reference adds particle by particle; agreement is to rounding (tests: 1e-12).
 #include "rp_internal.cuh"
 #include <cmath>
+#include <cstdlib>
+#include <algorithm>
 #include <vector>
 
 namespace rp {
@@ -258,10 +260,93 @@ __global__ void __launch_bounds__(PD_TILE) k_pair_density(int n, size_t cap, con
         if (sHist[b]) atomicAdd(&hist[b], static_cast<unsigned long long>(sHist[b]));
 }
 
+// ---- cell-list form: same pairs, same FP64 arithmetic for the survivors, O(N K) candidates ----
+// Focal points are binned into cells at least (maxR + margin) wide (relative coordinates: triclinic-safe, at least 3
+// cells per axis so that the 27 neighbour cells are distinct); every unordered pair within maxR lies in the same or in
+// adjacent cells and is visited once: own cell j > i (sorted order), 13 "positive" neighbour cells all (i, j).
+struct PdCellArgs { int n[3]; };
+
+__global__ void k_pd_keys(int n, size_t cap, const double *__restrict__ pos, const double *__restrict__ orient, Box box,
+                          PdArgs A, PdCellArgs C, int *__restrict__ keys, int *__restrict__ hist)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const V3 r = absToRel(box, focalPoint(i, cap, pos, orient, A));
+    const double q[3] = {r.x - floor(r.x), r.y - floor(r.y), r.z - floor(r.z)};
+    int c[3];
+    for (int d = 0; d < 3; d++) {
+        int v = static_cast<int>(q[d] * C.n[d]);
+        c[d] = v < 0 ? 0 : (v >= C.n[d] ? C.n[d] - 1 : v);
+    }
+    const int cell = (c[2] * C.n[1] + c[1]) * C.n[0] + c[0];
+    keys[i] = cell;
+    atomicAdd(&hist[cell], 1);
+}
+
+// sorted records: {x, y, z} FP64 focal point + FP32 relative coordinates (packed into two more doubles)
+__global__ void k_pd_records(int n, size_t cap, const double *__restrict__ pos, const double *__restrict__ orient,
+                             Box box, PdArgs A, const int *__restrict__ items, double *__restrict__ rec)
+{
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const V3 p = focalPoint(items[s], cap, pos, orient, A);
+    const V3 r = absToRel(box, p);
+    double *o = rec + 5 * static_cast<size_t>(s);
+    o[0] = p.x; o[1] = p.y; o[2] = p.z;
+    float *f = reinterpret_cast<float *>(o + 3);
+    f[0] = static_cast<float>(r.x); f[1] = static_cast<float>(r.y); f[2] = static_cast<float>(r.z); f[3] = 0.f;
+}
+
+constexpr int PDC_THREADS = 128;
+__global__ void __launch_bounds__(PDC_THREADS) k_pair_density_cells(PdCellArgs C, const int *__restrict__ cellStart,
+                                                                    const double *__restrict__ rec, Box box, PdArgs A,
+                                                                    unsigned long long *__restrict__ hist)
+{
+    __shared__ unsigned int sHist[PD_MAXBINS];
+    const int t = threadIdx.x;
+    for (int b = t; b < A.numBins; b += PDC_THREADS) sHist[b] = 0u;
+    __syncthreads();
+    const int cell = blockIdx.x;
+    const int cx = cell % C.n[0], cy = (cell / C.n[0]) % C.n[1], cz = cell / (C.n[0] * C.n[1]);
+    const int s1 = cellStart[cell], n1 = cellStart[cell + 1] - s1;
+    for (int code = 13; code < 27 && n1 > 0; code++) {
+        const int dx = code % 3 - 1, dy = (code / 3) % 3 - 1, dz = code / 9 - 1;
+        const int c2 = (((cz + dz + C.n[2]) % C.n[2]) * C.n[1] + (cy + dy + C.n[1]) % C.n[1]) * C.n[0]
+                       + (cx + dx + C.n[0]) % C.n[0];
+        const int s2 = cellStart[c2], n2 = cellStart[c2 + 1] - s2;
+        const long long pairs = static_cast<long long>(n1) * n2;
+        for (long long p = t; p < pairs; p += PDC_THREADS) {
+            const int a = static_cast<int>(p / n2), b = static_cast<int>(p - static_cast<long long>(a) * n2);
+            if (code == 13 && b <= a) continue;
+            const double *ra = rec + 5 * static_cast<size_t>(s1 + a), *rb = rec + 5 * static_cast<size_t>(s2 + b);
+            const float *fa = reinterpret_cast<const float *>(ra + 3), *fb = reinterpret_cast<const float *>(rb + 3);
+            float ddx = fb[0] - fa[0], ddy = fb[1] - fa[1], ddz = fb[2] - fa[2];
+            ddx -= rintf(ddx); ddy -= rintf(ddy); ddz -= rintf(ddz);
+            const float ax = fmaf(A.m[2], ddz, fmaf(A.m[1], ddy, A.m[0] * ddx));
+            const float ay = fmaf(A.m[5], ddz, fmaf(A.m[4], ddy, A.m[3] * ddx));
+            const float az = fmaf(A.m[8], ddz, fmaf(A.m[7], ddy, A.m[6] * ddx));
+            if (fmaf(az, az, fmaf(ay, ay, ax * ax)) < A.thr2) {
+                // RadialEnumerator.cpp:24-29, PairDensityCorrelation.cpp:29-40, Histogram.tpp:61-69
+                const V3 pi = v3(ra[0], ra[1], ra[2]), pj = v3(rb[0], rb[1], rb[2]);
+                const V3 p2 = pj + pbcTranslation(box, pi, pj);
+                const double distance = sqrt(norm2(p2 - pi));
+                if (!(distance > A.maxR)) {
+                    long long bin = static_cast<long long>(floor(distance / A.step));
+                    if (bin >= A.numBins) bin = A.numBins - 1;
+                    atomicAdd(&sHist[bin], 1u);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    for (int b = t; b < A.numBins; b += PDC_THREADS)
+        if (sHist[b]) atomicAdd(&hist[b], static_cast<unsigned long long>(sHist[b]));
+}
+
 void pairDensityCorrelation(Handle *h, double maxR, int numBins, const double focal[3], unsigned long long *countsOut,
                             double *gOut) {
     const int n = static_cast<int>(h->n);
-    ensureCellEnergyBuffer(h, static_cast<size_t>(numBins));
+    ensureCellEnergyBuffer(h, static_cast<size_t>(numBins) + 2);
     unsigned long long *dHist = reinterpret_cast<unsigned long long *>(h->dCellEnergy);
     RP_CUDA(cudaMemsetAsync(dHist, 0, sizeof(unsigned long long) * numBins, h->stream));
     PdArgs A;
@@ -276,9 +361,35 @@ void pairDensityCorrelation(Handle *h, double maxR, int numBins, const double fo
     A.numBins = numBins;
     A.useFocal = focal && (focal[0] != 0 || focal[1] != 0 || focal[2] != 0);
     A.focal = A.useFocal ? v3(focal[0], focal[1], focal[2]) : v3(0, 0, 0);
-    const int tiles = (n + PD_TILE - 1) / PD_TILE;
-    k_pair_density<<<dim3(tiles, tiles), PD_TILE, 0, h->stream>>>(n, h->cap, h->pos, h->orient, h->box, A, dHist);
-    h->launches++;
+    // cell list when every box height holds at least three cells of (maxR + margin), else all pairs, tile by tile
+    double heights[3];
+    boxHeights(h->box, heights);
+    PdCellArgs C;
+    size_t numCells = 1;
+    for (int i = 0; i < 3; i++) {
+        C.n[i] = static_cast<int>(std::min(512.0, std::floor(heights[i] / (thr * (1 + 1e-6)))));
+        numCells *= static_cast<size_t>(std::max(C.n[i], 0));
+    }
+    const bool cells = C.n[0] >= 3 && C.n[1] >= 3 && C.n[2] >= 3 && !std::getenv("RP_GR_ALL_PAIRS")
+                       && numCells <= 4 * static_cast<size_t>(n) + 64;
+    if (cells) {
+        GridStore &g = h->ogrid;
+        ensureGridCapacity(g, numCells, h->n, 5);
+        g.numCells = static_cast<int>(numCells);
+        g.numItems = n;
+        RP_CUDA(cudaMemsetAsync(g.cellFill, 0, (numCells + 1) * sizeof(int), h->stream));
+        k_pd_keys<<<(n + 255) / 256, 256, 0, h->stream>>>(n, h->cap, h->pos, h->orient, h->box, A, C, g.keys, g.cellFill);
+        scanCells(h, g, reinterpret_cast<int *>(dHist + numBins));
+        scatterItems(h, g);
+        k_pd_records<<<(n + 255) / 256, 256, 0, h->stream>>>(n, h->cap, h->pos, h->orient, h->box, A, g.items, g.rec);
+        k_pair_density_cells<<<static_cast<int>(numCells), PDC_THREADS, 0, h->stream>>>(C, g.cellStart, g.rec, h->box,
+                                                                                         A, dHist);
+        h->launches += 3;
+    } else {
+        const int tiles = (n + PD_TILE - 1) / PD_TILE;
+        k_pair_density<<<dim3(tiles, tiles), PD_TILE, 0, h->stream>>>(n, h->cap, h->pos, h->orient, h->box, A, dHist);
+        h->launches++;
+    }
     std::vector<unsigned long long> counts(numBins);
     RP_CUDA(cudaMemcpyAsync(counts.data(), dHist, sizeof(unsigned long long) * numBins, cudaMemcpyDeviceToHost,
                             h->stream));

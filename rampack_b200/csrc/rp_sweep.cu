@@ -273,7 +273,8 @@ void sweepAsync(Handle *h, const rp_sweep_params &p, unsigned long long *dAcc, r
     boxHeights(h->box, heights);
     double volume = boxVolume(h->box);
     // cell width: at least totalRange (plus a rounding margin), and wide enough to hold ~16 particles
-    const double TARGET_POPULATION = 16;
+    double TARGET_POPULATION = 16;
+    if (const char *e = std::getenv("RP_SWEEP_TARGET_POP")) TARGET_POPULATION = std::max(1.0, std::atof(e));      // (measurement hook)
     double minWidth = I.totalRange * (1 + 1e-9);
     int refN[3] = {0, 0, 0};
     if (I.soft == RP_SOFT_LJ) {

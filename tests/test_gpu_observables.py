@@ -117,3 +117,31 @@ def test_pair_density_correlation_at_scale(device):
     tree = cKDTree(shapes[:, :3], boxsize=np.diag(box))
     assert int(counts.sum()) == (tree.count_neighbors(tree, 5.0) - n) // 2
     assert np.all(np.abs(g[5:] - 1.0) < 0.05)
+
+
+def test_pair_density_cell_list_equals_all_pairs(device):
+    """The cell-list form of g(r) (boxes at least three cells of max_r high along every axis) visits the same pairs as
+    the all-pairs form (RP_GR_ALL_PAIRS=1 forces it) and bins them with the same FP64 arithmetic: equal counts, also
+    in a sheared box, with a focal point off the mass centre, and with particles sitting exactly on cell boundaries."""
+    import os
+    rng = np.random.default_rng(21)
+    box = np.array([[44.0, 6.0, -3.0], [0.0, 41.0, 5.0], [0.0, 0.0, 47.0]])
+    n = 30_000
+    rel = rng.uniform(0, 1, size=(n, 3))
+    rel[:200] = np.round(rel[:200] * 6) / 6 % 1.0            # on cell boundaries of a 6 x 6 x 6 grid
+    shapes = np.zeros((n, 12))
+    shapes[:, :3] = rel @ box.T
+    shapes[:, 3:] = H.random_rotations(rng, n).reshape(n, 9)
+    device.toggle_overlap_counting(False)
+    device.set_interaction(H.desc_sphere(0.01))
+    device.upload(box, shapes)
+    for focal in (None, (0.0, 0.3, 1.1)):
+        counts, g = device.pair_density_correlation(6.5, 65, focal)
+        os.environ["RP_GR_ALL_PAIRS"] = "1"
+        try:
+            counts_all, g_all = device.pair_density_correlation(6.5, 65, focal)
+        finally:
+            os.environ.pop("RP_GR_ALL_PAIRS", None)
+        assert counts.sum() > 100_000
+        assert np.array_equal(counts, counts_all)
+        assert np.array_equal(g, g_all)

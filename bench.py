@@ -279,12 +279,19 @@ def measure_extra(name, cfg, local, stream, peak_gflops, steps, budget_s=6.0, cp
         return e0.elapsed_time(e1), s0, s1
 
     if cfg.get("relax"):
-        # overlap_relaxation run (Simulation::relaxOverlaps, Simulation.cpp:218-323): overlap counting on, cycles until
-        # the cached count reaches zero
+        # overlap_relaxation run (Simulation::relaxOverlaps, Simulation.cpp:218-323): overlap counting on (with the
+        # helper interaction when the configuration names one), cycles until the cached count reaches zero
+        helper = cfg.get("relax_desc")
+        if helper:
+            sim.close()
+            dev.set_interaction(helper())
+            dev.upload(box, shapes)
+            sim = NativeSimulation(dev, [(rp.RP_MOVE_ROTOTRANSLATION,) + tuple(cfg["moves"])], TEMPERATURE, cfg["p"],
+                                   cfg["scaler"], seed=SEED)
         dev.toggle_overlap_counting(True)
         start = dev.cached_overlaps()
         ms_total, cycles, moves = 0.0, 0, 0
-        while dev.cached_overlaps() > 0 and ms_total < budget_s * 1e3 and cycles < 2000:
+        while dev.cached_overlaps() > 0 and ms_total < 3 * budget_s * 1e3 and cycles < 5000:
             ms, s0, s1 = timed(5, adjust=True)
             ms_total += ms
             cycles += 5
@@ -292,9 +299,21 @@ def measure_extra(name, cfg, local, stream, peak_gflops, steps, budget_s=6.0, cp
         left = dev.cached_overlaps()
         out["overlap_relaxation"] = {"overlaps_start": int(start), "overlaps_end": int(left), "cycles": cycles,
                                      "value": moves / (ms_total * 1e-3) if ms_total > 0 else None, "unit": UNIT,
-                                     "ms_per_cycle": ms_total / max(1, cycles)}
+                                     "ms_per_cycle": ms_total / max(1, cycles), "helper": bool(helper)}
         if left == 0:
+            # the production run continues with the plain hard shape from the relaxed packing
             dev.toggle_overlap_counting(False)
+            if helper:
+                st = sim.stats()
+                rbox, rshapes = dev.download()
+                sim.close()
+                dev.set_interaction(desc)
+                dev.upload(rbox, rshapes)
+                sim = NativeSimulation(dev, [(rp.RP_MOVE_ROTOTRANSLATION, st.translation_step[0],
+                                              st.rotation_step[0])], TEMPERATURE, cfg["p"],
+                                       (cfg["scaler"][0], st.scaler_step) + tuple(cfg["scaler"][2:]), seed=SEED + 1)
+        else:
+            out["counting_mode"] = True      # the timed cycles below still run with overlap counting on
     # thermalisation with the reference's step adaptation, bounded by the time budget
     timed(2, adjust=True)             # (first calls: allocations)
     ms, _, _ = timed(3, adjust=True)

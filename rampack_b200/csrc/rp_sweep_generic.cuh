@@ -317,6 +317,50 @@ __device__ __forceinline__ void pairTerms(const Inter &I, const GenArgs &A, cons
     }
 }
 
+// Soft-only interactions (no hard part), phase 1: the energies of the trial (new) state `ta` and of the current (old)
+// state `oa` of one particle against the frozen candidate `b`, with ONE pass over b's record: its centres (and
+// reference-grid cells) are fetched from global memory four at a time before anything depends on them — the exact
+// stage of the un-truncated LJ sweep is bound by the latency of exactly these loads — and serve both states.
+// Same pair set and pair energies as two pairTerms calls; only the order of the additions differs.
+template <bool CELLS>
+__device__ __forceinline__ void softPairBoth(const Inter &I, const GenArgs &A, const double *ta, const double *oa,
+                                             const double *b, V3 t, int gx, int gy, int gz, double *enN, double *enO)
+{
+    const GenLayout &L = A.L;
+    const V3 pb = ld3(b) + t;
+    const bool nearN = norm2(pb - ld3(ta)) < A.cullRange2, nearO = norm2(pb - ld3(oa)) < A.cullRange2;
+    if (!nearN && !nearO) return;
+    BcFixed bc{t};
+    const int shift[3] = {gx * A.refN[0], gy * A.refN[1], gz * A.refN[2]};
+    for (int c20 = 0; c20 < L.kk; c20 += 4) {
+        V3 pos2[4];
+        int4 cell2[4];
+        #pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int c2 = min(c20 + u, L.kk - 1);
+            pos2[u] = ld3(b + L.offCentre + 3 * c2);
+            if (CELLS) {
+                cell2[u] = reinterpret_cast<const int4 *>(b + L.offCell)[c2];
+                cell2[u].x += shift[0]; cell2[u].y += shift[1]; cell2[u].z += shift[2];
+            }
+        }
+        for (int c1 = 0; c1 < L.kk; c1++) {
+            const V3 p1n = ld3(ta + L.offCentre + 3 * c1), p1o = ld3(oa + L.offCentre + 3 * c1);
+            int4 c1n = make_int4(0, 0, 0, 0), c1o = c1n;
+            if (CELLS) {
+                c1n = reinterpret_cast<const int4 *>(ta + L.offCell)[c1];
+                c1o = reinterpret_cast<const int4 *>(oa + L.offCell)[c1];
+            }
+            #pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (c20 + u >= L.kk) break;
+                if (nearN && (!CELLS || refCellsAdjacent(c1n, cell2[u]))) *enN += energyBetween(I, p1n, pos2[u], bc);
+                if (nearO && (!CELLS || refCellsAdjacent(c1o, cell2[u]))) *enO += energyBetween(I, p1o, pos2[u], bc);
+            }
+        }
+    }
+}
+
 constexpr int GEN_THREADS = 128;     // default CTA; crowded cells (block-wise sequential mode) take GEN_THREADS_WIDE
 constexpr int GEN_THREADS_WIDE = 512;
 constexpr int GEN_MAXOWN = 64;       // trials per cell the bit masks of the hard-only resolution cover
@@ -505,9 +549,14 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
                         const int tIdx = cellT[c];
                         const V3 t = sg.trans[tIdx];
                         const int gx = tIdx / 9 - 1, gy = (tIdx / 3) % 3 - 1, gz = tIdx % 3 - 1;
-                        pairTerms<HARD, SOFT>(I, A, ta, rb, t, gx, gy, gz, hard, soft, !counting, &oN, &enN);
-                        if (needOld)
-                            pairTerms<HARD, SOFT>(I, A, oa, rb, t, gx, gy, gz, counting, soft, false, &oO, &enO);
+                        if (HARD == RP_HARD_NONE && SOFT) {
+                            if (L.offCell >= 0) softPairBoth<true>(I, A, ta, oa, rb, t, gx, gy, gz, &enN, &enO);
+                            else softPairBoth<false>(I, A, ta, oa, rb, t, gx, gy, gz, &enN, &enO);
+                        } else {
+                            pairTerms<HARD, SOFT>(I, A, ta, rb, t, gx, gy, gz, hard, soft, !counting, &oN, &enN);
+                            if (needOld)
+                                pairTerms<HARD, SOFT>(I, A, oa, rb, t, gx, gy, gz, counting, soft, false, &oO, &enO);
+                        }
                     }
                     // early exit like Packing::countParticleOverlaps(earlyExit = true)
                     if (!counting && hard && __any_sync(0xffffffffu, oN > 0)) stop = true;

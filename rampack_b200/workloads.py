@@ -97,9 +97,12 @@ EXTRA_CONFIGS = {
                          p=2.0, moves=(0.05, 0.05), scaler=("delta_triclinic", 3e-5, False), flops=(14, 105),
                          therm=5000, observe=("nematic",)),
     # C3: 4-mers and a XenoCollide convex body, N = 2 * 10^5, started 10 % (linear) too dense with overlap counting
+    # (relax_desc: the helper_shape of sample_inputs/overlap_reduction.pyon — the same beads with a
+    # square_inverse_core(epsilon=2, sigma=1) potential added for the overlap_relaxation run)
     "kmer4_200k": dict(desc=lambda: kmer_desc(4), lattice=((58, 58, 60), (1.25, 1.25, 4.3), False),
                        cpu_cells=(20, 20, 20), p=20.0, moves=(0.1, 0.1), scaler=("delta_v", 1.5), flops=(13, 0),
-                       relax=0.9, therm=200),
+                       relax=0.9, relax_desc=lambda: kmer_desc(4, soft=capi.RP_SOFT_SIC, epsilon=2.0, sigma=1.0),
+                       therm=200),
     "convex_200k": dict(desc=convex_desc, lattice=((58, 58, 60), (1.5, 1.5, 2.3), False), cpu_cells=(20, 20, 20),
                         p=4.0, moves=(0.1, 0.1), scaler=("delta_v", 1.0), flops=(20, 400), relax=0.9, therm=200),
     # C4: soft 3-mers (energy path), N = 5 * 10^5 (1.5 * 10^6 interaction centres)

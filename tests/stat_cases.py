@@ -142,7 +142,9 @@ CASES.update({
         state=lambda: ordered_snapshot("sc_l5_smectic"),
         temperature=1.0, pressure=2.2, trans_step=0.1, rot_step=0.1, nematic=True,
         scaler=("delta_triclinic", 0.0026, False), therm=3000, avg=20000, every=20, eos_density=None, gr=(1.0, 1.3),
-        min_p2=0.5, min_tau=0.3, seeds_ref=4, seeds_dev=4),
+        # (layer order fluctuates slowly and collectively — P2 and tau move together; 8 seeds per side for usable
+        # error bars)
+        min_p2=0.5, min_tau=0.3, seeds_ref=8, seeds_dev=8),
 })
 
 

@@ -129,6 +129,7 @@ def test_pair_density_cell_list_equals_all_pairs(device):
     n = 30_000
     rel = rng.uniform(0, 1, size=(n, 3))
     rel[:200] = np.round(rel[:200] * 6) / 6 % 1.0            # on cell boundaries of a 6 x 6 x 6 grid
+    rel = np.clip(rel, 1e-12, 1 - 1e-12)                     # (strictly inside the box after the round trip)
     shapes = np.zeros((n, 12))
     shapes[:, :3] = rel @ box.T
     shapes[:, 3:] = H.random_rotations(rng, n).reshape(n, 9)

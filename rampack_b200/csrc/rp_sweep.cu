@@ -103,13 +103,18 @@ void cullThresholds(const Handle *h, const double relCell[3], float *thr2, float
 // k_sweep variants: threads per CTA (= per active cell) and the minimum CTAs per SM the register allocation aims at.
 // The default is picked from the number of active cells (one wave or less: more threads per cell so that a launch
 // does not cost a full 4-warp CTA lifetime); RP_SWEEP_THREADS / RP_SWEEP_MINB override it (measurement hook).
+// ceiling of the dynamic shared memory of the sweep kernels (they carry < 12 KB of static shared memory; B200 allows
+// 227 KB per CTA); every capacity check below refuses launches above 200 KB
+constexpr size_t SWEEP_SMEM_CEILING = 208 * 1024;
 struct SweepVariant { int threads, minb, index; };
 static const SweepVariant SWEEP_VARIANTS[] = {{128, 4, 0}, {128, 5, 1}, {128, 6, 2}, {512, 1, 3}, {512, 2, 4},
                                               {256, 2, 5}, {256, 3, 6}};
 
 static SweepVariant chooseVariant(int activeCells) {
-    int threads = activeCells <= 148 * 3 ? 256 : 128;
-    int minb = threads == 256 ? 3 : 5;
+    // (a launch of a handful of cells — a 1000-particle gas has ONE active cell per colour — is pure CTA latency:
+    // the widest CTA wins)
+    int threads = activeCells <= 148 ? 512 : (activeCells <= 148 * 3 ? 256 : 128);
+    int minb = threads == 512 ? 1 : (threads == 256 ? 3 : 5);
     if (const char *e = std::getenv("RP_SWEEP_THREADS")) threads = std::atoi(e);
     if (const char *e = std::getenv("RP_SWEEP_MINB")) minb = std::atoi(e);
     for (const SweepVariant &v : SWEEP_VARIANTS)
@@ -130,12 +135,15 @@ static void launchColour(Handle *h, int variantIndex, int blocks, size_t smem, c
                          const PeerView &peers)
 {
     GridStore &g = h->sgrid;
-    // the attribute is per device and per kernel instantiation: kept per handle (a handle lives on one device)
+    // The attribute is per DEVICE and per kernel instantiation — shared by every handle of the process on that device
+    // — and it is a ceiling, not a reservation (occupancy follows the launch's own size).  It is therefore always set
+    // to the largest size any launch may ask for (SWEEP_SMEM_CEILING): a handle with small cells must never lower it
+    // under a handle with crowded ones (two handles in one process, e.g. concurrent state points on separate streams).
     size_t &configured = h->smemConfigured[variantIndex + (HARD == RP_HARD_SPHERE ? 8 : 0)];
-    if (smem > configured) {
+    if (configured < SWEEP_SMEM_CEILING) {
         RP_CUDA(cudaFuncSetAttribute(k_sweep<HARD, THREADS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     static_cast<int>(std::max<size_t>(smem, 48 * 1024))));
-        configured = std::max<size_t>(smem, 48 * 1024);
+                                     static_cast<int>(SWEEP_SMEM_CEILING)));
+        configured = SWEEP_SMEM_CEILING;
     }
     k_sweep<HARD, THREADS, MINB><<<blocks, THREADS, smem, h->stream>>>(A, sg, off, h->box, g.cellStart, g.items, g.rec,
                                                                       sweepRec32(g), T, h->pos, h->orient, dCounters,
@@ -451,7 +459,7 @@ void sweepAsync(Handle *h, const rp_sweep_params &p, unsigned long long *dAcc, r
         throw rp_error(RP_ERR_CAPACITY, "rp_sweep: a cell neighbourhood holds more than 65535 particles");
     A.capOld = h->sweepCapOld;
     A.capOwn = h->sweepCapOwn;
-    if (sweepSmemBytes(A.capOld, A.capOwn, 256) > 200 * 1024)
+    if (sweepSmemBytes(A.capOld, A.capOwn, 512) > 200 * 1024)
         throw rp_error(RP_ERR_CAPACITY, "rp_sweep: a cell neighbourhood does not fit into shared memory");
 
     RP_CUDA(cudaEventRecord(ev[2], st));
@@ -673,11 +681,10 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
         // one instantiation per (hard kind, soft potential present): the pair function is a compile-time constant
         auto launch = [&](auto kernel, int slotIndex) {
             size_t &configured = h->genSmemConfigured[slotIndex];
-            if (smem > configured) {
-                const size_t want = std::max<size_t>(smem, 48 * 1024);
+            if (configured < SWEEP_SMEM_CEILING) {      // (a ceiling shared by all handles on the device: see launchColour)
                 RP_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             static_cast<int>(want)));
-                configured = want;
+                                             static_cast<int>(SWEEP_SMEM_CEILING)));
+                configured = SWEEP_SMEM_CEILING;
             }
             kernel<<<blocks, threads, smem, st>>>(Ac, sg, off, h->box, h->dInter, g.cellStart, g.items, h->genRec,
                                                   cull, T, h->pos, h->orient, h->crel, h->cabs, h->dCounters,

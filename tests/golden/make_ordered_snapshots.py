@@ -20,7 +20,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import rampack_b200 as rp  # noqa: E402
 import stat_cases as S  # noqa: E402
 
-POINTS = {"sc_l5_nematic": 1.6, "sc_l5_smectic": 2.2}
+POINTS = {"sc_l5_nematic": 1.4, "sc_l5_smectic": 2.2}
 CELLS, CELL = (14, 14, 4), (1.2, 1.2, 6.5)
 
 

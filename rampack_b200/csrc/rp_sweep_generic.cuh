@@ -363,6 +363,7 @@ __device__ __forceinline__ void softPairBoth(const Inter &I, const GenArgs &A, c
 
 constexpr int GEN_THREADS = 128;     // default CTA; crowded cells (block-wise sequential mode) take GEN_THREADS_WIDE
 constexpr int GEN_THREADS_WIDE = 512;
+constexpr int GEN_XC_MINB = 4;       // XenoCollide: register cap 128 (MPR wants 255: 2 CTAs per SM, latency bound)
 constexpr int GEN_MAXOWN = 64;       // trials per cell the bit masks of the hard-only resolution cover
 constexpr int GEN_MAXCELL = 512;     // particles per sweep cell the kernel supports at all
 
@@ -395,7 +396,7 @@ __host__ __device__ inline size_t genSmemBytes(int capOld, int capOwn, int recw,
 // The decisions are those of a sequential Monte Carlo pass through the cell, as before.
 // ---------------------------------------------------------------------------------------------------------------
 template <int HARD, bool SOFT, int THREADS>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, (HARD == RP_HARD_XENOCOLLIDE ? GEN_XC_MINB : 1))
 k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter *__restrict__ interPtr,
             const int *__restrict__ cellStart, const int *__restrict__ items, double *__restrict__ rec,
             float4 *__restrict__ cull, GenTrialBuffers T, double *__restrict__ pos, double *__restrict__ orient,
@@ -628,39 +629,42 @@ k_gen_sweep(GenArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const Inter 
     }
     __syncthreads();
 
-    // ---- phase 2a: pair terms inside the cell, every ordered pair (i, j), all threads ----
+    // ---- phase 2a: pair terms inside the cell, all threads.  One work item = one ordered pair (i, j) x one variant
+    // (which state of i against which state of j); consecutive items go to DIFFERENT warps (item = lane * WARPS +
+    // warp): a small cell has a few dozen items, and with the expensive pair functions (XenoCollide's portal
+    // refinement) one warp working through them while the others wait was most of the kernel's time ----
     {
         const V3 zero = v3(0, 0, 0);
-        for (int p = tid; p < (blockwise ? 0 : numOwn * numOwn); p += THREADS) {
+        const int NV = matrices ? 4 : 2;
+        const int items = blockwise ? 0 : numOwn * numOwn * NV;
+        for (int base = 0; base < items; base += THREADS) {
+            const int it = base + lane * WARPS + warp;
+            if (it >= items) continue;
+            const int v = it % NV, p = it / NV;
             const int i = p / numOwn, j = p - i * numOwn;
             if (i == j || rejected[i] != 0) continue;
             const double *ta = tri + static_cast<size_t>(i) * recw, *oa = cur + static_cast<size_t>(i) * recw;
             const double *ob = cur + static_cast<size_t>(j) * recw, *tb = tri + static_cast<size_t>(j) * recw;
             const bool jMayMove = rejected[j] == 0;
-            if (!matrices) {       // bit masks
-                int o1 = 0, o2 = 0;
-                double e = 0;
-                pairTerms<HARD, SOFT>(I, A, ta, ob, zero, 0, 0, 0, true, false, true, &o1, &e);
-                if (o1) atomicOr(&ownMask[i], 1ull << j);
-                if (jMayMove) {
-                    pairTerms<HARD, SOFT>(I, A, ta, tb, zero, 0, 0, 0, true, false, true, &o2, &e);
-                    if (o2) atomicOr(&newMask[i], 1ull << j);
+            int o = 0;
+            double e = 0;
+            if (!matrices) {       // bit masks: v = 0 trial of i / current state of j, v = 1 trial of i / trial of j
+                if (v == 0) {
+                    pairTerms<HARD, SOFT>(I, A, ta, ob, zero, 0, 0, 0, true, false, true, &o, &e);
+                    if (o) atomicOr(&ownMask[i], 1ull << j);
+                } else if (jMayMove) {
+                    pairTerms<HARD, SOFT>(I, A, ta, tb, zero, 0, 0, 0, true, false, true, &o, &e);
+                    if (o) atomicOr(&newMask[i], 1ull << j);
                 }
-            } else {
-                int o[4] = {0, 0, 0, 0};
-                double e[4] = {0, 0, 0, 0};
-                pairTerms<HARD, SOFT>(I, A, ta, ob, zero, 0, 0, 0, hard, soft, !counting, &o[0], &e[0]);
-                pairTerms<HARD, SOFT>(I, A, oa, ob, zero, 0, 0, 0, counting, soft, false, &o[1], &e[1]);
-                if (jMayMove) {
-                    pairTerms<HARD, SOFT>(I, A, ta, tb, zero, 0, 0, 0, hard, soft, !counting, &o[2], &e[2]);
-                    pairTerms<HARD, SOFT>(I, A, oa, tb, zero, 0, 0, 0, counting, soft, false, &o[3], &e[3]);
+            } else {               // matrices [0] new_i/old_j [1] old_i/old_j [2] new_i/new_j [3] old_i/new_j
+                const double *ai = (v & 1) ? oa : ta, *bj = (v & 2) ? tb : ob;
+                if (!(v & 2) || jMayMove) {
+                    if (v & 1) pairTerms<HARD, SOFT>(I, A, ai, bj, zero, 0, 0, 0, counting, soft, false, &o, &e);
+                    else pairTerms<HARD, SOFT>(I, A, ai, bj, zero, 0, 0, 0, hard, soft, !counting, &o, &e);
                 }
                 const size_t at = static_cast<size_t>(i) * A.capOwn + j;
-                #pragma unroll
-                for (int m = 0; m < 4; m++) {
-                    eMat[m * matStride + at] = e[m];
-                    cMat[m * matStride + at] = static_cast<short>(o[m]);
-                }
+                eMat[v * matStride + at] = e;
+                cMat[v * matStride + at] = static_cast<short>(o);
             }
         }
     }

@@ -290,7 +290,7 @@ bool shardEnsurePeerMapping(Handle *h) {
     if (s->accCap < h->sgrid.itemCap || !s->acc) {
         if (s->acc) cudaFree(s->acc);       // (peers close their mapping below, in this same collective call)
         s->acc = nullptr;
-        RP_CUDA(cudaMalloc(&s->acc, h->sgrid.itemCap));
+        RP_CUDA(cudaMalloc(&s->acc, h->sgrid.itemCap * sizeof(unsigned long long)));
         s->accCap = h->sgrid.itemCap;
     }
     void *local[2] = {h->sgrid.rec, s->acc};
@@ -346,7 +346,7 @@ PeerView shardPeerView(const Handle *h, int nLayersZ) {
     const int P = s->nranks, r = s->rank;
     for (int q = 0; q < P; q++) {
         if (q == r) continue;
-        v.acc[v.n++] = static_cast<unsigned char *>(s->peerBase[q][1]);
+        v.acc[v.n++] = static_cast<unsigned long long *>(s->peerBase[q][1]);
     }
     int aLo, aHi;
     shardSlab(nLayersZ / 2, P, r, &aLo, &aHi);
@@ -364,7 +364,8 @@ PeerView shardPeerView(const Handle *h, int nLayersZ) {
 // the write-back of k_sweep (rp_sweep_kernel2.cuh) for the accepted trials of the OTHER slabs, from this rank's own
 // copy of the trials
 __global__ void k_apply_accepts(int n, const int *__restrict__ layerStart, int layerLo, int layerHi,
-                                const unsigned char *__restrict__ acc,
+                                const unsigned long long *__restrict__ acc, const int *__restrict__ keys,
+                                const int *__restrict__ cellStart,
                                 int translated, int rotated, Box box, size_t cap, const int *__restrict__ items,
                                 const double *__restrict__ trialRec, const double *__restrict__ trialOrient,
                                 double *__restrict__ rec, double *__restrict__ pos, double *__restrict__ orient,
@@ -372,8 +373,12 @@ __global__ void k_apply_accepts(int n, const int *__restrict__ layerStart, int l
 {
     int slot = blockIdx.x * blockDim.x + threadIdx.x;
     const int slotBegin = layerStart[layerLo], slotEnd = layerStart[layerHi];      // my own slab: already written
-    if (slot >= n || (slot >= slotBegin && slot < slotEnd) || !acc[slot]) return;
+    if (slot >= n || (slot >= slotBegin && slot < slotEnd)) return;
     const int id = items[slot];
+    // the accept word of the slot's batch sits at the batch's first slot (k_sweep: batches of SW_MAXOWN = 64 trials)
+    const int cs = cellStart[keys[id] & 0x0FFFFFFF];
+    const int first = cs + ((slot - cs) & ~63);
+    if (!((acc[first] >> (slot - first)) & 1ull)) return;
     const double *t = trialRec + 6 * static_cast<size_t>(slot);
     for (int q = 0; q < 6; q++) rec[6 * static_cast<size_t>(slot) + q] = t[q];
     if (translated) {
@@ -387,7 +392,8 @@ __global__ void k_apply_accepts(int n, const int *__restrict__ layerStart, int l
 
 void shardApplyAccepts(Handle *h, int aLo, int aHi, int n, bool translated, bool rotated) {
     k_apply_accepts<<<(n + 255) / 256, 256, 0, h->stream>>>(n, h->shard->dLayerStart, 2 * aLo, 2 * aHi,
-                                                           h->shard->acc, translated ? 1 : 0,
+                                                           h->shard->acc, h->sgrid.keys, h->sgrid.cellStart,
+                                                           translated ? 1 : 0,
                                                            rotated ? 1 : 0, h->box, h->cap, h->sgrid.items,
                                                            h->trialRec, h->trialOrient, h->sgrid.rec, h->pos,
                                                            h->orient, static_cast<uint2 *>(h->trialMeta));

@@ -41,7 +41,10 @@ struct Shard {
     // Per-colour / per-sweep flags (k_signal / k_wait) order the kernels of different GPUs; after the last colour
     // k_apply_accepts replays the accepted trials of the other slabs locally.
     bool p2p = false, p2pTried = false;
-    unsigned char *acc = nullptr;    // one byte per sorted slot, written by the slot's owner rank
+    // accept words: the 64-bit accept mask of a batch of <= 64 trials of one cell, stored at the sorted slot of the
+    // batch's first trial by the cell's owner rank (one 8-byte NVLink store per cell and peer; one BYTE per slot — 23
+    // one-byte remote stores per cell and peer — was the round-1 form)
+    unsigned long long *acc = nullptr;
     size_t accCap = 0;
     void *mappedLocal[2] = {nullptr, nullptr};    // local rec / acc at mapping time
     void *peerBase[64][2] = {};      // IPC-mapped rec / acc of rank q (nullptr for q == rank)
@@ -79,7 +82,7 @@ void shardAllReduceMaxInt(Handle *h, int *dValue);
 constexpr int SHARD_MAX_PEERS = 7;
 struct PeerView {                 // by-value kernel argument of k_sweep
     int n = 0;                    // number of peers
-    unsigned char *acc[SHARD_MAX_PEERS];      // their accept-byte arrays
+    unsigned long long *acc[SHARD_MAX_PEERS]; // their accept-word arrays (indexed by the first slot of a batch)
     int layerLo = -1, layerHi = -1;           // my slab's bottom / top cell layer
     double *recLo = nullptr, *recHi = nullptr;    // sorted records of the rank below / above (read my boundary layers)
     float4 *rec32Lo = nullptr, *rec32Hi = nullptr;    // ... and their FP32 cull records (same allocation, behind the FP64 records)

@@ -113,10 +113,10 @@ k_sweep(SweepArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const int *__r
         // attempted in this sweep; the host learns the count and raises the capacity.  Sharded: the other ranks must
         // not replay stale accept bytes for these slots.
         if (tid == 0) atomicAdd(&flags[3], 1);
-        for (int i = tid; i < numOwnAll; i += THREADS) {
+        for (int b0 = tid * SW_MAXOWN; b0 < numOwnAll; b0 += THREADS * SW_MAXOWN) {
             #pragma unroll
             for (int pr = 0; pr < SHARD_MAX_PEERS; pr++)
-                if (pr < peers.n) peers.acc[pr][cellSrc[0] + i] = 0;
+                if (pr < peers.n) peers.acc[pr][cellSrc[0] + b0] = 0ull;
         }
         return;
     }
@@ -459,12 +459,12 @@ k_sweep(SweepArgs A, SweepGrid sg, SweepCellOffsets off, Box box, const int *__r
                 }
             }
         }
-        // ... and every other rank learns the verdicts: one accept byte per slot (they hold the same trials)
-        if (tid < numOwn) {
-            const unsigned char a = static_cast<unsigned char>((sAccepted >> tid) & 1ull);
+        // ... and every other rank learns the verdicts: the batch's 64-bit accept mask, ONE 8-byte store per peer
+        // (they hold the same trials)
+        if (tid < SHARD_MAX_PEERS && tid < peers.n) {
             #pragma unroll
             for (int pr = 0; pr < SHARD_MAX_PEERS; pr++)      // (unrolled: no dynamic indexing of the argument)
-                if (pr < peers.n) peers.acc[pr][ownStart + tid] = a;
+                if (pr == tid) peers.acc[pr][ownStart] = sAccepted;
         }
         // every read of sAccepted (write-back, accept bytes) precedes the next batch's reset of it, and the records
         // written above are visible to the next batch's exact tests

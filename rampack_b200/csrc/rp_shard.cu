@@ -275,12 +275,12 @@ void shardGatherCycle(Handle *h, int nz, bool translated, bool rotated) {
 // ---------------------------------------------------------------------------------------------------------------
 // Flag block of a rank (one IPC-mapped allocation): [3][64] uint32 epochs (grid-ready / colour / sweep-done, indexed
 // by SENDER rank), then [64][4] uint64 sweep counters of every rank.
-constexpr size_t FLAG_WORDS = 3 * 64, FLAG_BLOCK_BYTES = FLAG_WORDS * sizeof(unsigned int) + 64 * 4 * sizeof(unsigned long long);
+constexpr size_t FLAG_WORDS = 4 * 64, FLAG_BLOCK_BYTES = FLAG_WORDS * sizeof(unsigned int) + 64 * 4 * sizeof(unsigned long long);
 __host__ __device__ inline unsigned long long *counterBlock(unsigned int *flags) {
     return reinterpret_cast<unsigned long long *>(flags + FLAG_WORDS);
 }
 
-struct IpcBundle { cudaIpcMemHandle_t mem[2]; cudaIpcMemHandle_t flags; };
+struct IpcBundle { cudaIpcMemHandle_t mem[4]; cudaIpcMemHandle_t flags; };
 
 bool shardEnsurePeerMapping(Handle *h) {
     Shard *s = h->shard;
@@ -293,7 +293,7 @@ bool shardEnsurePeerMapping(Handle *h) {
         RP_CUDA(cudaMalloc(&s->acc, h->sgrid.itemCap * sizeof(unsigned long long)));
         s->accCap = h->sgrid.itemCap;
     }
-    void *local[2] = {h->sgrid.rec, s->acc};
+    void *local[4] = {h->sgrid.rec, s->acc, h->trialRec, h->trialOrient};
     if (s->p2p && std::memcmp(local, s->mappedLocal, sizeof(local)) == 0) return true;
     // (all ranks take this branch in the same call: the replicas make identical allocation decisions)
     s->p2pTried = true;
@@ -304,11 +304,11 @@ bool shardEnsurePeerMapping(Handle *h) {
         RP_CUDA(cudaMalloc(&s->dHandles, 64 * sizeof(IpcBundle)));
     }
     for (int q = 0; q < P; q++)
-        for (int b = 0; b < 2; b++)
+        for (int b = 0; b < 4; b++)
             if (s->peerBase[q][b]) { cudaIpcCloseMemHandle(s->peerBase[q][b]); s->peerBase[q][b] = nullptr; }
     IpcBundle mine;
     bool ok = true;
-    for (int b = 0; b < 2; b++) ok = ok && cudaIpcGetMemHandle(&mine.mem[b], local[b]) == cudaSuccess;
+    for (int b = 0; b < 4; b++) ok = ok && cudaIpcGetMemHandle(&mine.mem[b], local[b]) == cudaSuccess;
     ok = ok && cudaIpcGetMemHandle(&mine.flags, s->flags) == cudaSuccess;
     cudaGetLastError();
     std::vector<IpcBundle> all(P);
@@ -321,7 +321,7 @@ bool shardEnsurePeerMapping(Handle *h) {
     RP_CUDA(cudaStreamSynchronize(h->stream));
     for (int q = 0; q < P && ok; q++) {
         if (q == r) continue;
-        for (int b = 0; b < 2 && ok; b++)
+        for (int b = 0; b < 4 && ok; b++)
             ok = cudaIpcOpenMemHandle(&s->peerBase[q][b], all[q].mem[b], cudaIpcMemLazyEnablePeerAccess)
                  == cudaSuccess;
         if (ok && !s->peerFlags[q])
@@ -361,13 +361,18 @@ PeerView shardPeerView(const Handle *h, int nLayersZ) {
     return v;
 }
 
-// the write-back of k_sweep (rp_sweep_kernel2.cuh) for the accepted trials of the OTHER slabs, from this rank's own
-// copy of the trials
+// the write-back of k_sweep (rp_sweep_kernel2.cuh) for the accepted trials of the OTHER slabs.  A rank generates the
+// trials of its own slab only (k_sweep_prepare), so the accepted states are PULLED from the owner's trial buffers
+// (IPC-mapped peer memory: 48 + 72 contiguous bytes per accepted slot over NVLink).
+struct ApplySources {
+    int n;                                   // ranks
+    int layerLo[SHARD_MAX_PEERS + 1], layerHi[SHARD_MAX_PEERS + 1];     // cell layers [lo, hi) of rank q's slab
+    const double *rec[SHARD_MAX_PEERS + 1], *orient[SHARD_MAX_PEERS + 1];
+};
 __global__ void k_apply_accepts(int n, const int *__restrict__ layerStart, int layerLo, int layerHi,
                                 const unsigned long long *__restrict__ acc, const int *__restrict__ keys,
-                                const int *__restrict__ cellStart,
+                                const int *__restrict__ cellStart, ApplySources src,
                                 int translated, int rotated, Box box, size_t cap, const int *__restrict__ items,
-                                const double *__restrict__ trialRec, const double *__restrict__ trialOrient,
                                 double *__restrict__ rec, double *__restrict__ pos, double *__restrict__ orient,
                                 uint2 *__restrict__ meta)
 {
@@ -379,10 +384,21 @@ __global__ void k_apply_accepts(int n, const int *__restrict__ layerStart, int l
     const int cs = cellStart[keys[id] & 0x0FFFFFFF];
     const int first = cs + ((slot - cs) & ~63);
     if (!((acc[first] >> (slot - first)) & 1ull)) return;
+    // the owner of the slot
+    const double *trialRec = nullptr, *trialOrient = nullptr;
+    #pragma unroll
+    for (int q = 0; q < SHARD_MAX_PEERS + 1; q++)
+        if (q < src.n && slot >= layerStart[src.layerLo[q]] && slot < layerStart[src.layerHi[q]]) {
+            trialRec = src.rec[q];
+            trialOrient = src.orient[q];
+        }
+    if (!trialRec) return;
     const double *t = trialRec + 6 * static_cast<size_t>(slot);
-    for (int q = 0; q < 6; q++) rec[6 * static_cast<size_t>(slot) + q] = t[q];
+    double tr[6];
+    for (int q = 0; q < 6; q++) tr[q] = t[q];
+    for (int q = 0; q < 6; q++) rec[6 * static_cast<size_t>(slot) + q] = tr[q];
     if (translated) {
-        V3 np = v3(t[0], t[1], t[2]);
+        V3 np = v3(tr[0], tr[1], tr[2]);
         V3 p = np + pbcCorrection(box, np);
         pos[id] = p.x; pos[cap + id] = p.y; pos[2 * cap + id] = p.z;
     }
@@ -390,14 +406,28 @@ __global__ void k_apply_accepts(int n, const int *__restrict__ layerStart, int l
     meta[slot].x = 4u;
 }
 
-void shardApplyAccepts(Handle *h, int aLo, int aHi, int n, bool translated, bool rotated) {
+void shardApplyAccepts(Handle *h, int aLo, int aHi, int n, bool translated, bool rotated, int nActiveZ,
+                       unsigned int epoch) {
+    const Shard *s = h->shard;
+    ApplySources src;
+    src.n = s->nranks;
+    for (int q = 0; q < s->nranks; q++) {
+        int lo, hi;
+        shardSlab(nActiveZ, s->nranks, q, &lo, &hi);
+        src.layerLo[q] = 2 * lo;
+        src.layerHi[q] = 2 * hi;
+        src.rec[q] = q == s->rank ? h->trialRec : static_cast<const double *>(s->peerBase[q][2]);
+        src.orient[q] = q == s->rank ? h->trialOrient : static_cast<const double *>(s->peerBase[q][3]);
+    }
     k_apply_accepts<<<(n + 255) / 256, 256, 0, h->stream>>>(n, h->shard->dLayerStart, 2 * aLo, 2 * aHi,
-                                                           h->shard->acc, h->sgrid.keys, h->sgrid.cellStart,
+                                                           h->shard->acc, h->sgrid.keys, h->sgrid.cellStart, src,
                                                            translated ? 1 : 0,
                                                            rotated ? 1 : 0, h->box, h->cap, h->sgrid.items,
-                                                           h->trialRec, h->trialOrient, h->sgrid.rec, h->pos,
+                                                           h->sgrid.rec, h->pos,
                                                            h->orient, static_cast<uint2 *>(h->trialMeta));
     h->launches++;
+    // nobody overwrites its trial buffers (the next sweep's k_sweep_prepare) before every rank has pulled from them
+    shardSignalWait(h, SHARD_FLAG_APPLIED, epoch, true, false, nullptr);
 }
 
 struct FlagTargets {

@@ -46,8 +46,8 @@ struct Shard {
     // one-byte remote stores per cell and peer — was the round-1 form)
     unsigned long long *acc = nullptr;
     size_t accCap = 0;
-    void *mappedLocal[2] = {nullptr, nullptr};    // local rec / acc at mapping time
-    void *peerBase[64][2] = {};      // IPC-mapped rec / acc of rank q (nullptr for q == rank)
+    void *mappedLocal[4] = {nullptr, nullptr, nullptr, nullptr};    // local rec / acc / trialRec / trialOrient at mapping time
+    void *peerBase[64][4] = {};      // IPC-mapped rec / acc / trial records / trial orientations of rank q (nullptr for q == rank)
     unsigned int *flags = nullptr;   // local flag block: [3][64] = grid-ready / colour / sweep-done epochs per sender
     unsigned int *peerFlags[64] = {};
     unsigned char *dHandles = nullptr;    // all-gather staging for the IPC handles
@@ -87,7 +87,7 @@ struct PeerView {                 // by-value kernel argument of k_sweep
     double *recLo = nullptr, *recHi = nullptr;    // sorted records of the rank below / above (read my boundary layers)
     float4 *rec32Lo = nullptr, *rec32Hi = nullptr;    // ... and their FP32 cull records (same allocation, behind the FP64 records)
 };
-enum ShardFlag { SHARD_FLAG_GRID = 0, SHARD_FLAG_COLOUR = 1, SHARD_FLAG_DONE = 2 };
+enum ShardFlag { SHARD_FLAG_GRID = 0, SHARD_FLAG_COLOUR = 1, SHARD_FLAG_DONE = 2, SHARD_FLAG_APPLIED = 3 };
 constexpr int SHARD_ABORT_FLAG = 12;     // index into Handle::dFlags: a peer-flag wait timed out (never reset by a sweep)
 // (re)maps the peers' buffers when a local buffer moved since the last mapping; collective; returns whether the
 // peer-memory path is usable
@@ -95,7 +95,8 @@ bool shardEnsurePeerMapping(Handle *h);
 PeerView shardPeerView(const Handle *h, int nLayersZ);
 // accepted trials of the slots outside [slotBegin, slotEnd) -> sorted records and canonical arrays
 // (the slab's slot range is read from the device copy of the layer boundaries: layers [2 aLo, 2 aHi))
-void shardApplyAccepts(Handle *h, int aLo, int aHi, int n, bool translated, bool rotated);
+void shardApplyAccepts(Handle *h, int aLo, int aHi, int n, bool translated, bool rotated, int nActiveZ,
+                       unsigned int epoch);
 // One launch: flag[kind][my rank] = value on the peers (everyone, or the two z-neighbours), ordered after all prior
 // work of the stream, then poll the local flags of the same peers until they reach `value`.  withCounters (sweep
 // done): my four sweep counters travel with the signal and h->dCounters becomes the sum over ranks.

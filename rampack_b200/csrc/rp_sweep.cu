@@ -209,7 +209,7 @@ static void launchSweep(Handle *h, const SweepArgs &A0, const SweepGrid &sg, con
         shardSignalWait(h, SHARD_FLAG_DONE, epoch, true, true, dCounters);
         int aLo, aHi;
         shardSlab(A0.nActive[2], h->shard->nranks, h->shard->rank, &aLo, &aHi);
-        shardApplyAccepts(h, aLo, aHi, n, translated, rotated);
+        shardApplyAccepts(h, aLo, aHi, n, translated, rotated, A0.nActive[2], epoch);
     } else if (sharded) {
         shardGatherCycle(h, sg.n[2], translated, rotated);
         shardAllReduceU64(h, dCounters, 4);
@@ -389,6 +389,7 @@ void sweepAsync(Handle *h, const rp_sweep_params &p, unsigned long long *dAcc, r
     A.aOff2 = 0;
     A.slotBegin = 0;
     A.slotEnd = n;
+    A.trialLayerLo = A.trialLayerHi = -1;
     A.inter.sphereThr2 = I.sphereThr2;
     A.inter.scInner2 = I.scInner2;
     A.inter.scOuter2 = I.scOuter2;
@@ -425,6 +426,7 @@ void sweepAsync(Handle *h, const rp_sweep_params &p, unsigned long long *dAcc, r
         int aLo, aHi;
         shardSlab(sg.n[2] / 2, h->shard->nranks, h->shard->rank, &aLo, &aHi);
         A.aOff2 = aLo;
+        if (p2p) { A.trialLayerLo = 2 * aLo; A.trialLayerHi = 2 * aHi; }
     }
     const int prepBlocks = (n + 255) / 256;
     const Walls W = makeWalls(h->box, h->wallMask, I.totalRange);

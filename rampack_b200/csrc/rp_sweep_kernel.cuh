@@ -62,6 +62,9 @@ struct SweepArgs {
     size_t cap;
     int aOff2;                  // sharded runs: first active-cell layer (z) of this rank's slab, else 0
     int slotBegin, slotEnd;     // sorted slots whose trials this rank generates (all of them on one GPU)
+    // sharded over peer memory: this rank's slab of cell layers [trialLayerLo, trialLayerHi) — k_sweep_prepare writes
+    // trials for the slab only and records for the slab and the layer on either side; -1: everything
+    int trialLayerLo, trialLayerHi;
 };
 
 // device buffers of the trials of one rp_sweep call, indexed by the sorted slot
@@ -241,18 +244,28 @@ __global__ void __launch_bounds__(256, 3) k_sweep_prepare(int n, SweepArgs A, Sw
     const int particleId = itemsTmp[scattered];
     const int key = keys[particleId];
     const int cell = key & 0x0FFFFFFF, f = (key >> 28) & 7;
+    // sharded over peer memory: records only where this rank's k_sweep stages them, trials only for its own slab
+    bool wantTrial = true, wantRec = true;
+    if (A.trialLayerLo >= 0) {
+        const int cz = cell / (sg.n[0] * sg.n[1]), nz = sg.n[2];
+        wantTrial = cz >= A.trialLayerLo && cz < A.trialLayerHi;
+        wantRec = wantTrial || cz == (A.trialLayerLo - 1 + nz) % nz || cz == A.trialLayerHi % nz;
+    }
     // the canonical state: gathers issued before anything depends on them
-    V3 p = v3(pos[particleId], pos[A.cap + particleId], pos[2 * A.cap + particleId]);
+    V3 p = v3(0, 0, 0);
     const bool rotated = (A.kind == RP_MOVE_ROTATION || A.kind == RP_MOVE_ROTOTRANSLATION);
     const bool translated = (A.kind == RP_MOVE_TRANSLATION || A.kind == RP_MOVE_ROTOTRANSLATION);
     M33 O;
     V3 h = v3(0, 0, 0);
-    if (rotated) {
-        #pragma unroll
-        for (int q = 0; q < 9; q++) O.a[q] = orient[q * A.cap + particleId];
-    } else if (HARD == RP_HARD_SPHEROCYLINDER) {
-        // half axis h = orientation.column(2) * (0.5 * l): the cap centres are pos -+ h (SpherocylinderTraits.cpp:24-26)
-        h = v3(orient[2 * A.cap + particleId], orient[5 * A.cap + particleId], orient[8 * A.cap + particleId]);
+    if (wantRec) {
+        p = v3(pos[particleId], pos[A.cap + particleId], pos[2 * A.cap + particleId]);
+        if (rotated) {
+            #pragma unroll
+            for (int q = 0; q < 9; q++) O.a[q] = orient[q * A.cap + particleId];
+        } else if (HARD == RP_HARD_SPHEROCYLINDER) {
+            // half axis h = orientation.column(2) * (0.5 * l): the cap centres are pos -+ h (SpherocylinderTraits.cpp:24-26)
+            h = v3(orient[2 * A.cap + particleId], orient[5 * A.cap + particleId], orient[8 * A.cap + particleId]);
+        }
     }
     const int start = cellStart[cell], cnt = cellStart[cell + 1] - start;
     const int cc[3] = {cell % sg.n[0], (cell / sg.n[0]) % sg.n[1], cell / (sg.n[0] * sg.n[1])};
@@ -263,12 +276,13 @@ __global__ void __launch_bounds__(256, 3) k_sweep_prepare(int n, SweepArgs A, Sw
     do {
         const int slot = start + rank;
         items[slot] = particleId;
+        if (!wantRec) break;
         if (f) p = p + sg.imageShift[f];
         if (HARD == RP_HARD_SPHEROCYLINDER) h = (rotated ? column(O, 2) : h) * halfLength;
         double *r = rec + 6 * static_cast<size_t>(slot);
         r[0] = p.x; r[1] = p.y; r[2] = p.z; r[3] = h.x; r[4] = h.y; r[5] = h.z;
         makeRec32(p, h, centre, invHalfF, rec32 + 2 * static_cast<size_t>(slot));
-        if (slot < A.slotBegin || slot >= A.slotEnd) break;          // sharded over NCCL: another rank's trial
+        if (slot < A.slotBegin || slot >= A.slotEnd || !wantTrial) break;          // sharded: another rank's trial
 
         // ---- the trial move of this particle ----
         Rng rng;

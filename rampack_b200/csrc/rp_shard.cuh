@@ -34,12 +34,11 @@ struct Shard {
     std::vector<int> layerStart; // host copy
     unsigned long long *dCounts = nullptr;    // nranks message counts (all-gathered)
     // ---- peer-memory path (default when the buffers of all ranks can be IPC-mapped; RP_SHARD_NCCL=1 disables it) ----
-    // Trials are a pure function of (Philox key, old state), and the old state is replicated: every rank generates
-    // the trials of ALL slots, so the only thing a rank has to tell the others is one ACCEPT BYTE per slot.  k_sweep
-    // stores it straight into every peer's `acc` array over NVLink; the records of accepted moves in the slab's two
-    // boundary layers also go straight into the z-neighbour's sorted records (read there in the next colour).
-    // Per-colour / per-sweep flags (k_signal / k_wait) order the kernels of different GPUs; after the last colour
-    // k_apply_accepts replays the accepted trials of the other slabs locally.
+    // A rank generates the trials of its own slab.  k_sweep stores the accept word of every batch straight into every
+    // peer's `acc` array over NVLink; the records of accepted moves in the slab's two boundary layers also go
+    // straight into the z-neighbour's sorted records (read there in the next colour).  Per-colour / per-sweep flags
+    // (k_signal_wait) order the kernels of different GPUs; after the last colour k_apply_accepts pulls the accepted
+    // states of the other slabs from their owners' trial buffers (mapped like the records).
     bool p2p = false, p2pTried = false;
     // accept words: the 64-bit accept mask of a batch of <= 64 trials of one cell, stored at the sorted slot of the
     // batch's first trial by the cell's owner rank (one 8-byte NVLink store per cell and peer; one BYTE per slot — 23

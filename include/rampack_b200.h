@@ -330,6 +330,16 @@ rp_status rp_pair_density_correlation(rp_handle *h, double max_r, int32_t n_bins
                                       uint64_t *counts_out, double *g_out);
 rp_status rp_smectic_order(rp_handle *h, const int32_t hkl_range[3], const double focal_point[3], double *tau_out,
                            int32_t hkl_out[3], double k_out[3]);
+/* rp_nematic_order_static: no counterpart in the reference; added for callers
+ *   that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs,
+ *   outputs and errors as rp_nematic_order, but it allocates nothing: the per-block partial sums go to a file-scope
+ *   __device__ array of 49 200 bytes (held by every GPU that loads the library until exit) instead of the handle's
+ *   growable scratch buffer.  Packings of more than RP_NEMATIC_STATIC_MAX_PARTICLES particles are rejected with
+ *   RP_ERR_PRECONDITION.  All calls on one device share the array: calls that overlap on the GPU (other streams,
+ *   other host threads) race and must be serialised by the caller.  The summation order differs from
+ *   rp_nematic_order's, so the two agree to rounding (1e-12), not bit for bit (rampack_b200/csrc/rp_noalloc.cu). */
+#define RP_NEMATIC_STATIC_MAX_PARTICLES 4194304ull
+rp_status rp_nematic_order_static(rp_handle *h, const double primary_axis[3], double q_out[9], double *p2_out);
 
 /* ---- host cycle loop in C++: Simulation::performCycle / evaluateCounters / tryScaling (src/core/Simulation.cpp:
  * 325-363, 493-607) with the particle moves delegated to rp_sweep and the box move to rp_try_scaling.  One host thread;

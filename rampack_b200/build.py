@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "librampack_b200.so")
-SOURCES = ["rp_api.cu", "rp_grid.cu", "rp_recount.cu", "rp_sweep.cu", "rp_stats.cu", "rp_xc_setup.cu", "rp_shard.cu", "rp_sim.cu", "rp_observe.cu"]
+SOURCES = ["rp_api.cu", "rp_grid.cu", "rp_recount.cu", "rp_sweep.cu", "rp_stats.cu", "rp_xc_setup.cu", "rp_shard.cu", "rp_sim.cu", "rp_observe.cu", "rp_noalloc.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
               "-Xcompiler", "-fPIC,-ffp-contract=off", "-Xptxas", "-v"]
 

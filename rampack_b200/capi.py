@@ -122,7 +122,7 @@ SYMBOLS = ["rp_populate_lattice", "rp_randomize_rotations", "rp_create", "rp_des
            "rp_renormalize_orientations", "rp_toggle_walls", "rp_nematic_order", "rp_smectic_order",
            "rp_pair_density_correlation", "rp_sim_create", "rp_sim_destroy", "rp_sim_run", "rp_sim_stats_get", "rp_sim_propose_box",
            "rp_download_range", "rp_count_wall_overlaps", "rp_particle_energy_fluctuations", "rp_snapshot_async",
-           "rp_snapshot_wait", "rp_snapshot_done", "rp_upload_slice"]
+           "rp_snapshot_wait", "rp_snapshot_done", "rp_upload_slice", "rp_nematic_order_static"]
 
 _lib = None
 
@@ -150,6 +150,7 @@ def load():
     lib.rp_version.restype = C.c_char_p
     lib.rp_toggle_walls.argtypes = [H, C.POINTER(C.c_int32)]
     lib.rp_nematic_order.argtypes = [H, dp, dp, dp]
+    lib.rp_nematic_order_static.argtypes = [H, dp, dp, dp]
     lib.rp_smectic_order.argtypes = [H, C.POINTER(C.c_int32), dp, dp, C.POINTER(C.c_int32), dp]
     lib.rp_pair_density_correlation.argtypes = [H, C.c_double, C.c_int32, dp, C.c_void_p, dp]
     lib.rp_renormalize_orientations.argtypes = [H, C.c_int, C.POINTER(C.c_uint64)]
@@ -446,6 +447,14 @@ class Device:
         axis = np.ascontiguousarray(primary_axis, dtype=np.float64)
         q, p2 = np.empty(9), C.c_double()
         self._check(self.lib.rp_nematic_order(self.h, dptr(axis), dptr(q), C.byref(p2)))
+        return q.reshape(3, 3), p2.value
+
+    def nematic_order_static(self, primary_axis=(0.0, 0.0, 1.0)):
+        """nematic_order through rp_nematic_order_static: no device allocation, at most
+        RP_NEMATIC_STATIC_MAX_PARTICLES (4 194 304) particles, calls on one device must not overlap."""
+        axis = np.ascontiguousarray(primary_axis, dtype=np.float64)
+        q, p2 = np.empty(9), C.c_double()
+        self._check(self.lib.rp_nematic_order_static(self.h, dptr(axis), dptr(q), C.byref(p2)))
         return q.reshape(3, 3), p2.value
 
     def smectic_order(self, hkl_range=(5, 5, 5), focal_point=None):

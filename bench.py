@@ -245,8 +245,15 @@ def sweep_cells(box, n, total_range):
     enough for ~16 particles, even counts."""
     heights = [np.linalg.det(box) / np.linalg.norm(np.cross(box[:, (i + 1) % 3], box[:, (i + 2) % 3]))
                for i in range(3)]
-    width = max(total_range * (1 + 1e-9), (16.0 * abs(np.linalg.det(box)) / n) ** (1.0 / 3.0))
-    return [max(2, int(h / width)) & ~1 for h in heights]
+    min_width = total_range * (1 + 1e-9)
+    width = max(min_width, (16.0 * abs(np.linalg.det(box)) / n) ** (1.0 / 3.0))
+    cells = []
+    for h in heights:
+        c = max(2, int(h / width))
+        if c & 1:           # small grids round up when the narrower cell is admissible (rp_sweep.cu)
+            c = c + 1 if c <= 7 and h / (c + 1) >= min_width else c - 1
+        cells.append(c)
+    return cells
 
 
 def measure_extra(name, cfg, local, stream, peak_gflops, steps, budget_s=6.0, cpu=True):

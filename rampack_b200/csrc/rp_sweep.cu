@@ -310,7 +310,10 @@ void sweepAsync(Handle *h, const rp_sweep_params &p, unsigned long long *dAcc, r
         if (n < 2)
             throw rp_error(RP_ERR_UNSUPPORTED, "rp_sweep: the box must be at least 2 x totalRange high along every "
                                                "axis for the checkerboard sweep");
-        n &= ~1;
+        // even counts for the two-colour pattern per axis.  Rounding an odd count DOWN multiplies the cell population
+        // by (n / (n - 1))^3 — 3.4 at n = 3, where a box of 10^3 particles collapses to 8 cells of 125, one CTA per
+        // colour — so small grids round UP when the narrower cell is still admissible
+        if (n & 1) n = (n <= 7 && heights[i] / (n + 1) >= minWidth) ? n + 1 : n - 1;
         sg.n[i] = n;
         sg.relCell[i] = 1 / static_cast<double>(n);
         numCells *= n;

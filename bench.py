@@ -540,7 +540,7 @@ def main():
         # third.  The serial chain (one packing, nothing overlapped) stays in the line as e2e.serial_value.
         from concurrent.futures import ThreadPoolExecutor
         from rampack_b200 import NativeSimulation
-        e2e_pipeline = max(1, env_int("E2E_PIPELINE", 3))
+        e2e_pipeline = max(1, env_int("E2E_PIPELINE", 4))
         st_now = sim.stats()
         lanes = [(dev, sim, host)]
         for k in range(1, e2e_pipeline):

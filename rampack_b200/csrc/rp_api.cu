@@ -2,6 +2,7 @@
 // thin forwarding to the kernels.  No exception crosses the boundary: every entry point returns an rp_status.
 #include "rp_internal.cuh"
 #include "rp_philox.cuh"
+#include <cstring>
 #include "rp_shard.cuh"
 #include <limits>
 
@@ -296,6 +297,60 @@ static void setupForInteraction(Handle *h) {
         h->numOverlaps = countTotalOverlaps(h, false);
 }
 
+__global__ void k_zero_words(unsigned int *__restrict__ p, size_t words) {
+    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < words;
+         i += static_cast<size_t>(gridDim.x) * blockDim.x)
+        p[i] = 0u;
+}
+
+__global__ void k_mailbox(unsigned int *__restrict__ box, const unsigned int *__restrict__ a, int wordsA,
+                          const unsigned int *__restrict__ b, int wordsB) {
+    for (int i = threadIdx.x; i < wordsA; i += blockDim.x) box[i] = a[i];
+    for (int i = threadIdx.x; i < wordsB; i += blockDim.x) box[wordsA + i] = b[i];
+    __threadfence_system();
+}
+
+__global__ void k_copy_words(unsigned long long *__restrict__ dst, const unsigned long long *__restrict__ src,
+                             size_t words) {
+    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < words;
+         i += static_cast<size_t>(gridDim.x) * blockDim.x)
+        dst[i] = src[i];
+}
+
+void copyAsync(Handle *h, void *dst, const void *src, size_t bytes, cudaStream_t st) {
+    if (bytes == 0) return;
+    if ((bytes & 7) || (reinterpret_cast<uintptr_t>(dst) & 7) || (reinterpret_cast<uintptr_t>(src) & 7))
+        throw rp_error(RP_ERR_STATE, "copyAsync: not a whole number of aligned 8-byte words");
+    const size_t words = bytes / 8;
+    const int blocks = static_cast<int>(std::min<size_t>((words + 255) / 256, 1184));
+    k_copy_words<<<blocks, 256, 0, st>>>(static_cast<unsigned long long *>(dst),
+                                         static_cast<const unsigned long long *>(src), words);
+    h->launches++;
+}
+
+void zeroAsync(Handle *h, void *p, size_t bytes, cudaStream_t st) {
+    if (bytes == 0) return;
+    if ((bytes & 3) || (reinterpret_cast<uintptr_t>(p) & 3))
+        throw rp_error(RP_ERR_STATE, "zeroAsync: not a whole number of aligned words");
+    const size_t words = bytes / 4;
+    const int blocks = static_cast<int>(std::min<size_t>((words + 255) / 256, 592));
+    k_zero_words<<<blocks, 256, 0, st>>>(static_cast<unsigned int *>(p), words);
+    h->launches++;
+}
+
+void readbackSync(Handle *h, cudaStream_t st, void *dst0, const void *dsrc0, size_t bytes0, void *dst1,
+                  const void *dsrc1, size_t bytes1) {
+    if ((bytes0 & 3) || (bytes1 & 3) || bytes0 + bytes1 > MAILBOX_BYTES || !h->mailbox)
+        throw rp_error(RP_ERR_STATE, "readbackSync: the mailbox takes at most 1 KB of whole words");
+    k_mailbox<<<1, 64, 0, st>>>(h->mailbox, static_cast<const unsigned int *>(dsrc0), static_cast<int>(bytes0 / 4),
+                                static_cast<const unsigned int *>(dsrc1), static_cast<int>(bytes1 / 4));
+    h->launches++;
+    RP_CUDA(cudaStreamSynchronize(st));
+    RP_CUDA(cudaGetLastError());
+    std::memcpy(dst0, h->mailbox, bytes0);
+    if (bytes1) std::memcpy(dst1, reinterpret_cast<const char *>(h->mailbox) + bytes0, bytes1);
+}
+
 }  // namespace rp
 
 using namespace rp;
@@ -338,6 +393,7 @@ rp_status rp_create(const rp_config *config, rp_handle **out) {
         RP_CUDA(cudaMalloc(&h->dFlags, 16 * sizeof(int)));
         RP_CUDA(cudaMemset(h->dFlags, 0, 16 * sizeof(int)));
         RP_CUDA(cudaMallocHost(&h->sweepMaxPinned, 4 * 4 * sizeof(int)));
+        RP_CUDA(cudaMallocHost(&h->mailbox, MAILBOX_BYTES));
         for (auto &ev : h->sweepMaxEvent) RP_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
         for (auto &t : h->timing) for (auto &ev : t.e) RP_CUDA(cudaEventCreate(&ev));
         RP_CUDA(cudaMalloc(&h->dMoveOut, 8 * sizeof(double)));
@@ -375,6 +431,7 @@ void rp_destroy(rp_handle *h) {
     for (auto &ev : h->sweepMaxEvent) if (ev) cudaEventDestroy(ev);
     for (auto &t : h->timing) for (auto &ev : t.e) if (ev) cudaEventDestroy(ev);
     if (h->sweepMaxPinned) cudaFreeHost(h->sweepMaxPinned);
+    if (h->mailbox) cudaFreeHost(h->mailbox);
     if (h->snapStream) {
         cudaStreamSynchronize(h->snapStream);
         cudaStreamDestroy(h->snapStream);
@@ -427,7 +484,7 @@ rp_status rp_upload(rp_handle *h, const double box[9], const double *shapes, uin
     }
     ensureStage(h, n * 12 * sizeof(double));
     RP_CUDA(cudaMemcpyAsync(h->dStage, shapes, n * 12 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-    RP_CUDA(cudaMemsetAsync(h->dFlags, 0, sizeof(int), h->stream));
+    zeroAsync(h, h->dFlags, sizeof(int), h->stream);
     k_check_within_box<<<static_cast<int>((n + 255) / 256), 256, 0, h->stream>>>(
         static_cast<int>(n), b, static_cast<const double *>(h->dStage), h->dFlags);
     int total = static_cast<int>(n * 12);
@@ -436,9 +493,7 @@ rp_status rp_upload(rp_handle *h, const double box[9], const double *shapes, uin
                                                                 h->orient, h->dFlags);
     h->launches += 2;
     int outside = 0;
-    RP_CUDA(cudaMemcpyAsync(&outside, h->dFlags, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-    RP_CUDA(cudaStreamSynchronize(h->stream));
-    RP_CUDA(cudaGetLastError());
+    readbackSync(h, h->stream, &outside, h->dFlags, sizeof(int));
     RP_EXPECT(!outside, "areShapesWithinBox(shapes, box)");
     h->n = n;
     h->box = b;
@@ -473,7 +528,7 @@ rp_status rp_upload_slice(rp_handle *h, const double box[9], const double *shape
         h->cap = cap;
         h->n = 0;
     }
-    RP_CUDA(cudaMemsetAsync(h->dFlags, 0, sizeof(int), h->stream));
+    zeroAsync(h, h->dFlags, sizeof(int), h->stream);
     if (count > 0) {
         ensureStage(h, count * 12 * sizeof(double));
         RP_CUDA(cudaMemcpyAsync(h->dStage, shapes, count * 12 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
@@ -490,9 +545,7 @@ rp_status rp_upload_slice(rp_handle *h, const double box[9], const double *shape
         shardAllGatherState(h, n);
     }
     int outside = 0;
-    RP_CUDA(cudaMemcpyAsync(&outside, h->dFlags, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-    RP_CUDA(cudaStreamSynchronize(h->stream));
-    RP_CUDA(cudaGetLastError());
+    readbackSync(h, h->stream, &outside, h->dFlags, sizeof(int));
     RP_EXPECT(!outside, "areShapesWithinBox(shapes, box)");
     h->n = n;
     h->box = b;
@@ -541,14 +594,12 @@ rp_status rp_populate_lattice(rp_handle *h, const double cell_box[9], const doub
     h->n = 0;          // the previous state is overwritten in place: a failed call leaves an empty packing
     ensureStage(h, m * 12 * sizeof(double));
     RP_CUDA(cudaMemcpyAsync(h->dStage, cell_molecules, m * 12 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-    RP_CUDA(cudaMemsetAsync(h->dFlags, 0, sizeof(int), h->stream));
+    zeroAsync(h, h->dFlags, sizeof(int), h->stream);
     k_populate_lattice<<<static_cast<int>((n + 255) / 256), 256, 0, h->stream>>>(
         static_cast<int>(n), h->cap, L, static_cast<const double *>(h->dStage), h->pos, h->orient, h->dFlags);
     h->launches++;
     int outside = 0;
-    RP_CUDA(cudaMemcpyAsync(&outside, h->dFlags, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-    RP_CUDA(cudaStreamSynchronize(h->stream));
-    RP_CUDA(cudaGetLastError());
+    readbackSync(h, h->stream, &outside, h->dFlags, sizeof(int));
     RP_EXPECT(!outside, "areShapesWithinBox(shapes, box)");
     h->n = n;
     h->box = L.lattice;

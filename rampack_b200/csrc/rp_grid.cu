@@ -273,8 +273,8 @@ void rebuildReferenceGrid(Handle *h) {
 
     cudaStream_t st = h->stream;
     RP_CUDA(cudaEventRecord(h->ev[2], st));
-    RP_CUDA(cudaMemsetAsync(g.cellFill, 0, (numCells + 1) * sizeof(int), st));
-    RP_CUDA(cudaMemsetAsync(h->dFlags, 0, 2 * sizeof(int), st));
+    zeroAsync(h, g.cellFill, (numCells + 1) * sizeof(int), st);
+    zeroAsync(h, h->dFlags, 2 * sizeof(int), st);
     int threads = 256;
     int blocks = static_cast<int>((numItems + threads - 1) / threads);
     k_cell_keys<<<blocks, threads, 0, st>>>(g.numItems, I.k, h->cap, h->centreCap, h->pos, h->cabs, h->box, view,
@@ -287,8 +287,7 @@ void rebuildReferenceGrid(Handle *h) {
     RP_CUDA(cudaGetLastError());
     RP_CUDA(cudaEventRecord(h->ev[3], st));
     int flags[2];
-    RP_CUDA(cudaMemcpyAsync(flags, h->dFlags, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    RP_CUDA(cudaStreamSynchronize(st));
+    readbackSync(h, st, flags, h->dFlags, 2 * sizeof(int));
     float ms = 0;
     cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]);
     h->lastRebuildMs = ms;

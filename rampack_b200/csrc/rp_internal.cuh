@@ -149,6 +149,7 @@ struct Handle {
     // shared-memory staging capacities of k_sweep: taken from the maxima the previous calls observed (read back
     // without blocking), so that a cycle needs no host synchronisation; 0 = unknown (first call synchronises)
     int sweepCapOld = 0, sweepCapOwn = 0;
+    unsigned int *mailbox = nullptr;      // pinned, device-visible: small results a kernel writes for the host (readbackSync)
     int *sweepMaxPinned = nullptr;        // pinned ring of {max cell population, max neighbourhood, cells skipped, -}
     cudaEvent_t sweepMaxEvent[4] = {nullptr, nullptr, nullptr, nullptr};
     bool sweepMaxPending[4] = {false, false, false, false};
@@ -223,6 +224,20 @@ struct rp_error : std::runtime_error {
     throw rp::rp_error(RP_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
 #define RP_EXPECT(cond, msg) do { if (!(cond)) \
     throw rp::rp_error(RP_ERR_PRECONDITION, std::string("Precondition (") + #cond + ") failed: " + (msg)); } while (0)
+
+struct Handle;
+// Control traffic of the cycle stays off the copy engines: a few result words read back through cudaMemcpyAsync, or a
+// counter cleared through cudaMemsetAsync, queue on the same DMA engine as the 97 MB transfers of OTHER handles on the
+// device (packings in flight, snapshots) and wait for them — 1-2 ms per readback when both directions are busy.
+//   zeroAsync:    a kernel clears `bytes` (multiple of 4) at p
+//   copyAsync:    a kernel copies `bytes` (multiple of 8) between device buffers (the saved state of a box move)
+//   readbackSync: a kernel copies up to two small device arrays (multiples of 4 bytes, <= 1 KB together) into the
+//                 handle's pinned mailbox, the stream is synchronised, the words are handed to dst0 / dst1
+constexpr size_t MAILBOX_BYTES = 1024;
+void zeroAsync(Handle *h, void *p, size_t bytes, cudaStream_t st);
+void copyAsync(Handle *h, void *dst, const void *src, size_t bytes, cudaStream_t st);      // device to device
+void readbackSync(Handle *h, cudaStream_t st, void *dst0, const void *dsrc0, size_t bytes0, void *dst1 = nullptr,
+                  const void *dsrc1 = nullptr, size_t bytes1 = 0);
 
 template <typename T>
 inline void devEnsure(T *&p, size_t &cap, size_t need) {

@@ -369,8 +369,8 @@ unsigned long long countTotalOverlaps(Handle *h, bool earlyExit) {
     if (!h->inter.hard) return 0;
     ensureGrid(h);
     cudaStream_t st = h->stream;
-    RP_CUDA(cudaMemsetAsync(h->dCounters, 0, sizeof(unsigned long long), st));
-    RP_CUDA(cudaMemsetAsync(h->dFlags + 2, 0, sizeof(int), st));
+    zeroAsync(h, h->dCounters, sizeof(unsigned long long), st);
+    zeroAsync(h, h->dFlags + 2, sizeof(int), st);
     const Inter &I = h->inter;
     const bool culled = h->hasGrid && I.k == 0 && (I.hard == RP_HARD_SPHERE || I.hard == RP_HARD_SPHEROCYLINDER)
                         && !std::getenv("RP_RECOUNT_LEGACY");
@@ -420,8 +420,7 @@ unsigned long long countTotalOverlaps(Handle *h, bool earlyExit) {
         h->launches++;
     }
     unsigned long long result = 0;
-    RP_CUDA(cudaMemcpyAsync(&result, h->dCounters, sizeof(result), cudaMemcpyDeviceToHost, st));
-    RP_CUDA(cudaStreamSynchronize(st));
+    readbackSync(h, st, &result, h->dCounters, sizeof(result));
     RP_CUDA(cudaGetLastError());
     if (earlyExit && result) return 1;   // Packing.cpp:543-544
     return result;
@@ -448,8 +447,7 @@ double totalEnergy(Handle *h) {
     sumDoubles(h, parts, h->dCellEnergy);
     h->launches++;
     double result = 0;
-    RP_CUDA(cudaMemcpyAsync(&result, h->dCellEnergy + parts, sizeof(double), cudaMemcpyDeviceToHost, st));
-    RP_CUDA(cudaStreamSynchronize(st));
+    readbackSync(h, st, &result, h->dCellEnergy + parts, sizeof(double));
     RP_CUDA(cudaGetLastError());
     return result;
 }
@@ -716,15 +714,14 @@ double particleEnergyFluctuations(Handle *h) {
 unsigned long long countWallOverlaps(Handle *h, bool earlyExit) {
     if (!h->wallMask || !h->inter.hard) return 0;
     cudaStream_t st = h->stream;
-    RP_CUDA(cudaMemsetAsync(h->dCounters, 0, sizeof(unsigned long long), st));
+    zeroAsync(h, h->dCounters, sizeof(unsigned long long), st);
     const int n = static_cast<int>(h->n);
     k_count_wall_overlaps<<<(n + 255) / 256, 256, 0, st>>>(n, particleView(h), h->crel, h->dInter,
                                                            makeWalls(h->box, h->wallMask, h->inter.totalRange),
                                                            h->dCounters);
     h->launches++;
     unsigned long long result = 0;
-    RP_CUDA(cudaMemcpyAsync(&result, h->dCounters, sizeof(result), cudaMemcpyDeviceToHost, st));
-    RP_CUDA(cudaStreamSynchronize(st));
+    readbackSync(h, st, &result, h->dCounters, sizeof(result));
     RP_CUDA(cudaGetLastError());
     // with early exit the reference returns the overlaps of the particles visited before the flag was seen: at
     // least 1, at most the full count — callers only test for > 0
@@ -749,8 +746,7 @@ double tryMove(Handle *h, const rp_move &m) {
                                   makeWalls(h->box, h->wallMask, h->inter.totalRange), h->tmpState, h->dMoveOut);
     h->launches++;
     double out[4];
-    RP_CUDA(cudaMemcpyAsync(out, h->dMoveOut, sizeof(out), cudaMemcpyDeviceToHost, st));
-    RP_CUDA(cudaStreamSynchronize(st));
+    readbackSync(h, st, out, h->dMoveOut, sizeof(out));
     RP_CUDA(cudaGetLastError());
     h->hasTrial = true;
     h->trialParticle = m.particle;
@@ -815,11 +811,10 @@ double tryScaling(Handle *h, const Box &newBox) {
     RP_CUDA(cudaEventRecord(h->ev[0], st));
     h->lastBox = h->box;
     devEnsure(h->lastPos, h->lastCap, 3 * h->cap);
-    RP_CUDA(cudaMemcpyAsync(h->lastPos, h->pos, 3 * h->cap * sizeof(double), cudaMemcpyDeviceToDevice, st));
+    copyAsync(h, h->lastPos, h->pos, 3 * h->cap * sizeof(double), st);
     if (h->inter.k > 0) {
         devEnsure(h->lastCabs, h->lastCentreCap, 3 * h->centreCap);
-        RP_CUDA(cudaMemcpyAsync(h->lastCabs, h->cabs, 3 * h->centreCap * sizeof(double), cudaMemcpyDeviceToDevice,
-                                st));
+        copyAsync(h, h->lastCabs, h->cabs, 3 * h->centreCap * sizeof(double), st);
     }
     // The grid of the OLD state is only worth building if somebody reads it: the energy of a soft interaction now, or
     // whoever comes after a revert.  After a sweep it is stale and the next sweep would discard it unread, so a hard-
@@ -866,10 +861,9 @@ double tryScaling(Handle *h, const Box &newBox) {
 void revertScaling(Handle *h) {
     RP_EXPECT(h->hasLastScaling, "revertScaling without a preceding tryScaling");
     cudaStream_t st = h->stream;
-    RP_CUDA(cudaMemcpyAsync(h->pos, h->lastPos, 3 * h->cap * sizeof(double), cudaMemcpyDeviceToDevice, st));
+    copyAsync(h, h->pos, h->lastPos, 3 * h->cap * sizeof(double), st);
     if (h->inter.k > 0)
-        RP_CUDA(cudaMemcpyAsync(h->cabs, h->lastCabs, 3 * h->centreCap * sizeof(double), cudaMemcpyDeviceToDevice,
-                                st));
+        copyAsync(h, h->cabs, h->lastCabs, 3 * h->centreCap * sizeof(double), st);
     h->box = h->lastBox;
     std::swap(h->grid, h->tempGrid);
     std::swap(h->hasGrid, h->tempHasGrid);

@@ -148,8 +148,7 @@ void readDeviceCounters(rp_sim *s) {
     for (int i = 0; i < s->cfg.n_samplers; i++) any = any || s->pendingMoves[i] > 0;
     if (!any) return;
     unsigned long long now[4 * RP_SIM_MAX_SAMPLERS];
-    RP_CUDA(cudaMemcpyAsync(now, s->dAcc, sizeof(now), cudaMemcpyDeviceToHost, s->h->stream));
-    RP_CUDA(cudaStreamSynchronize(s->h->stream));
+    readbackSync(s->h, s->h->stream, now, s->dAcc, sizeof(now));
     RP_CUDA(cudaGetLastError());
     for (int i = 0; i < s->cfg.n_samplers; i++) {
         const unsigned long long att = now[4 * i] - s->devSeen[4 * i], acc = now[4 * i + 1] - s->devSeen[4 * i + 1];

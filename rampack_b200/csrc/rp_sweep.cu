@@ -355,9 +355,9 @@ void sweepAsync(Handle *h, const rp_sweep_params &p, unsigned long long *dAcc, r
     if (h->timing[tslot].pending) sweepTimings(h, true);
     cudaEvent_t *ev = h->timing[tslot].e;
     RP_CUDA(cudaEventRecord(ev[0], st));
-    RP_CUDA(cudaMemsetAsync(g.cellFill, 0, (numCells + 1) * sizeof(int), st));
-    RP_CUDA(cudaMemsetAsync(h->dFlags, 0, 8 * sizeof(int), st));
-    RP_CUDA(cudaMemsetAsync(h->dCounters, 0, 8 * sizeof(unsigned long long), st));
+    zeroAsync(h, g.cellFill, (numCells + 1) * sizeof(int), st);
+    zeroAsync(h, h->dFlags, 8 * sizeof(int), st);
+    zeroAsync(h, h->dCounters, 8 * sizeof(unsigned long long), st);
     k_sweep_keys<<<(n + 255) / 256, 256, 0, st>>>(n, h->cap, h->pos, h->box, sg, g.keys, g.cellFill);
     scanCells(h, g, &h->dFlags[1]);
     k_sweep_scatter<<<(n + 255) / 256, 256, 0, st>>>(n, g.keys, g.cellStart, g.cellFill, g.itemsTmp);
@@ -453,8 +453,7 @@ void sweepAsync(Handle *h, const rp_sweep_params &p, unsigned long long *dAcc, r
     // (the synchronous form — counters returned to the caller — always sizes from its own grid: it never skips a cell)
     if (h->sweepCapOld == 0 || out != nullptr || std::getenv("RP_SWEEP_SYNC_CAPS")) {
         int flags[4];
-        RP_CUDA(cudaMemcpyAsync(flags, h->dFlags, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
-        RP_CUDA(cudaStreamSynchronize(st));
+        readbackSync(h, st, flags, h->dFlags, 4 * sizeof(int));
         RP_CUDA(cudaGetLastError());
         h->sweepCapOwn = std::max(h->sweepCapOwn, flags[1] + flags[1] / 8 + 4);
         h->sweepCapOld = std::max(h->sweepCapOld, flags[2] + flags[2] / 16 + 16);
@@ -493,8 +492,7 @@ void sweepAsync(Handle *h, const rp_sweep_params &p, unsigned long long *dAcc, r
     if (out) {
         // the synchronous form: counters of THIS call
         unsigned long long counters[4];
-        RP_CUDA(cudaMemcpyAsync(counters, dCounters, sizeof(counters), cudaMemcpyDeviceToHost, st));
-        RP_CUDA(cudaStreamSynchronize(st));
+        readbackSync(h, st, counters, dCounters, sizeof(counters));
         RP_CUDA(cudaGetLastError());
         sweepTimings(h, true);
         const unsigned long long skippedBefore = h->sweepCellsSkipped;
@@ -648,9 +646,7 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
     h->launches += 2;
     RP_CUDA(cudaEventRecord(ev[1], st));
     int flags[4];
-    RP_CUDA(cudaMemcpyAsync(flags, h->dFlags, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    RP_CUDA(cudaStreamSynchronize(st));
-    RP_CUDA(cudaGetLastError());
+    readbackSync(h, st, flags, h->dFlags, 4 * sizeof(int));
     g.maxPopulation = flags[1];
     A.capOwn = (std::max(g.maxPopulation, 1) + 1) & ~1;
     A.capOld = std::max(flags[2], 1);
@@ -733,9 +729,7 @@ static void sweepGeneric(Handle *h, const rp_sweep_params &p, const SweepGrid &s
     }
     RP_CUDA(cudaEventRecord(ev[3], st));
     unsigned long long counters[6];
-    RP_CUDA(cudaMemcpyAsync(counters, h->dCounters, sizeof(counters), cudaMemcpyDeviceToHost, st));
-    RP_CUDA(cudaMemcpyAsync(flags, h->dFlags, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    RP_CUDA(cudaStreamSynchronize(st));
+    readbackSync(h, st, counters, h->dCounters, sizeof(counters), flags, h->dFlags, 4 * sizeof(int));
     RP_CUDA(cudaGetLastError());
     float msGrid = 0, msSweep = 0;
     cudaEventElapsedTime(&msGrid, ev[0], ev[1]);

@@ -277,8 +277,15 @@ rp_status rp_sim_create(rp_handle *h, const rp_sim_config *config, rp_sim **out)
     s->st.scaler_step = c.scaler_step;
     if (h) {
         cudaSetDevice(h->device);
-        if (cudaMalloc(&s->dAcc, 4 * RP_SIM_MAX_SAMPLERS * sizeof(unsigned long long)) != cudaSuccess
-            || cudaMemsetAsync(s->dAcc, 0, 4 * RP_SIM_MAX_SAMPLERS * sizeof(unsigned long long), h->stream) != cudaSuccess) {
+        bool ok = cudaMalloc(&s->dAcc, 4 * RP_SIM_MAX_SAMPLERS * sizeof(unsigned long long)) == cudaSuccess;
+        if (ok) {
+            try {
+                zeroAsync(h, s->dAcc, 4 * RP_SIM_MAX_SAMPLERS * sizeof(unsigned long long), h->stream);
+            } catch (const std::exception &) {
+                ok = false;
+            }
+        }
+        if (!ok) {
             rp::tlsError = "rp_sim_create: cannot allocate the device counters";
             delete s;
             return RP_ERR_CUDA;

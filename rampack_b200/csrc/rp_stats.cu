@@ -55,14 +55,13 @@ void neighbourStats(Handle *h, double *kCand, double *kFull) {
     ensureGrid(h);
     RP_EXPECT(h->hasGrid, "neighbour statistics need a neighbour grid");
     cudaStream_t st = h->stream;
-    RP_CUDA(cudaMemsetAsync(h->dCounters, 0, 2 * sizeof(unsigned long long), st));
+    zeroAsync(h, h->dCounters, 2 * sizeof(unsigned long long), st);
     GridView g = makeView(h->grid);
     int blocks = (g.numCells * 32 + 255) / 256;
     k_neighbour_stats<<<blocks, 256, 0, st>>>(g, h->dInter, h->dCounters);
     h->launches++;
     unsigned long long out[2];
-    RP_CUDA(cudaMemcpyAsync(out, h->dCounters, sizeof(out), cudaMemcpyDeviceToHost, st));
-    RP_CUDA(cudaStreamSynchronize(st));
+    readbackSync(h, st, out, h->dCounters, sizeof(out));
     RP_CUDA(cudaGetLastError());
     double centres = static_cast<double>(h->n) * h->inter.kk;
     *kCand = static_cast<double>(out[0]) / centres;

@@ -60,3 +60,22 @@ def test_product_path_does_not_touch_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".hpp")):
                 text = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "oracle" not in text.replace("test oracle", ""), f"{f} mentions oracle/"
+
+
+def test_cycle_path_keeps_off_the_copy_engines():
+    """The NpT cycle (sweep, grid builds, box move, host loop) must not issue small cudaMemcpyAsync readbacks or
+    cudaMemsetAsync: they queue on the DMA engines behind the 97 MB transfers of other packings on the device and stall
+    the cycle by 1-2 ms each (profiles/r02_e2e_pipelining.txt).  Results go through readbackSync, counters
+    through zeroAsync, the saved state of a box move through copyAsync.  rp_sweep_trace (a test hook that downloads the
+    whole trial record) is the one allowed exception."""
+    csrc = os.path.join(ROOT, "rampack_b200", "csrc")
+    for name in ("rp_grid.cu", "rp_sim.cu", "rp_stats.cu", "rp_sweep.cu", "rp_recount.cu"):
+        text = open(os.path.join(csrc, name)).read()
+        if name == "rp_sweep.cu":
+            text = text[:text.index("sweepTrace(")] if "sweepTrace(" in text else text
+        if name == "rp_recount.cu":
+            # particle energy fluctuations and the pair-test batch move arrays whose size grows with N: bulk copies
+            text = re.sub(r"cudaMemcpyAsync\((e\.data\(\)|dPairs|verdict \+ off|energy \+ off)[^;]*;", "", text)
+        assert "cudaMemsetAsync" not in text, f"{name}: cudaMemsetAsync on the cycle path (use zeroAsync)"
+        for m in re.finditer(r"cudaMemcpyAsync\(([^;]*);", text):
+            assert False, f"{name}: cudaMemcpyAsync on the cycle path: {m.group(0)[:90]}"

@@ -7,15 +7,16 @@ timeout 300 python __graft_entry__.py --smoke > gpurun_out/final_smoke.log 2>&1;
 ( time timeout 1500 python bench.py > gpurun_out/final_bench.json 2> gpurun_out/final_bench.err ) 2>&1 | grep real; tail -2 gpurun_out/final_bench.err
 ( time timeout 1200 python bench.py --impl reference > gpurun_out/final_bench_ref.json 2> gpurun_out/final_bench_ref.err ) 2>&1 | grep real; cut -c1-300 gpurun_out/final_bench_ref.json
 B="python bench.py --configs none --no-cpu-baseline --therm 300 --steps 3 --warmup 3"
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/final_launches_all.csv $B > gpurun_out/final_ncu_list.log 2>&1
+E2E_PIPELINE=1 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/final_launches_all.csv $B > gpurun_out/final_ncu_list.log 2>&1
 echo "ncu list exit $?"
 python - <<'PY'
-# keep the launches of the warm-up + timed steps (the last 6 cycles before the end-to-end section)
-rows = open('gpurun_out/final_launches_all.csv').read().split('\n')
-hdr = [i for i, r in enumerate(rows) if r.startswith('"ID"')]
-idx = [i for i, r in enumerate(rows) if 'k_sweep_report' in r]
-start = idx[-12] if len(idx) >= 12 else 0
-open('gpurun_out/final_launches_bench_sc1m.csv', 'w').write('\n'.join([rows[hdr[0]]] + rows[start:start + 520] if hdr else rows[-520:]))
+# keep the 3 warm-up + 3 timed cycles: bench.py downloads the state once after the thermalisation and once after the
+# timed steps, so they are the launches between the first two k_pack_shapes
+raw = open('gpurun_out/final_launches_all.csv').read().split('\n')
+h = [i for i, r in enumerate(raw) if r.startswith('"ID"')][0]
+rows = raw[h + 1:]
+pack = [i for i, r in enumerate(rows) if 'k_pack_shapes' in r]
+open('gpurun_out/final_launches_bench_sc1m.csv', 'w').write('\n'.join([raw[h]] + rows[pack[0] + 1:pack[1]]) + '\n')
 PY
 rm -f gpurun_out/final_launches_all.csv
 ls -la gpurun_out | head -30
